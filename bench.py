@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""Benchmark contract of the round driver.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU path (oracle port)
+
+Workload (BASELINE.json metric "DAT frames/sec @1080p"): DAT (configs/DAT.yaml, nf=72) inference on synthetic
+1080p frame pairs, replicate-padded to 1088x1920 as the reference's InputPadder does; `--pairs` pairs per GPU
+per step (weak scaling: every rank processes its own pairs, no collective on the data path).  One JSON line on
+rank 0.  `value` = device-resident throughput; `e2e` = host buffers in, host frame out (H2D/D2H inside the
+timed region); `roofline` = the dominant vfi_b200 kernel of the step (fused deformable attention at 1/2 res),
+timed with CUDA events inside the timed region; `microbench` = warp + splat GB/s on the 1080p flow pyramid.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+METRIC = "DAT frames/sec @1080p"
+UNIT = "frames/s"
+H_RAW, W_RAW = 1080, 1920
+CPU_SAMPLE_HW = (256, 448)        # BASELINE.json configs[0]: the reference's own CPU-runnable case
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="vfi_b200", choices=["vfi_b200", "reference"])
+    ap.add_argument("--pairs", type=int, default=1, help="frame pairs per GPU per step")
+    ap.add_argument("--height", type=int, default=H_RAW)
+    ap.add_argument("--width", type=int, default=W_RAW)
+    ap.add_argument("--no-micro", action="store_true", help="skip the warp/splat micro-benchmark")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--tf32", type=int, default=1, help="allow TF32 in the cuDNN convs around the hot path (PyTorch default)")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU every 100 ms while running (NVML)."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_ev = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4),
+                 "hw_power_brake": getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80)}
+        while not self._stop_ev.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop_ev.wait(0.1)
+
+    def stop(self):
+        self._stop_ev.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def dist_env(n_gpus: int):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's CPU path = oracle port with the library ops the reference itself calls
+# ------------------------------------------------------------------------------------------------
+def cpu_dat_setup(seed=0):
+    import oracle
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.workloads import init_dat_weights, seed_for
+    torch.manual_seed(seed)
+    net = init_dat_weights(v.DATwConstantnCv1(v.default_args()))          # host-side module only supplies the weights
+    sd = {k: w.detach().clone() for k, w in net.state_dict().items()}
+    g = torch.Generator().manual_seed(seed_for(1, 0))
+    h, w = CPU_SAMPLE_HW
+    x0, x1 = torch.rand(1, 3, h, w, generator=g), torch.rand(1, 3, h, w, generator=g)
+    t = torch.full((1, 1, 1, 1), 0.5)
+    return oracle, sd, x0, x1, t
+
+
+def cpu_dat_step(oracle, sd, x0, x1, t):
+    with torch.no_grad(), oracle.library_ops():
+        return oracle.dat_forward(sd, x0, x1, t)
+
+
+def cpu_scale(height, width):
+    """1080p-equivalent frames/s from a CPU_SAMPLE_HW forward: the model is fully convolutional, cost ~ pixels."""
+    ph, pw = -(-height // 16) * 16, -(-width // 16) * 16
+    return (CPU_SAMPLE_HW[0] * CPU_SAMPLE_HW[1]) / float(ph * pw)
+
+
+def cpu_sample_text(cores):
+    return (f"oracle port of DATwConstantnCv1.inference (torch CPU grid_sample / torchvision deform_conv2d, fp32, {cores} threads) "
+            f"on one {CPU_SAMPLE_HW[1]}x{CPU_SAMPLE_HW[0]} pair (BASELINE configs[0]); frames/s scaled by pixel count to "
+            f"1088x1920 (the 1080p forward itself needs ~40 GB for the reference's materialised kv tensors)")
+
+
+def run_reference(args):
+    rank, world, _ = dist_env(args.gpus)
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    oracle, sd, x0, x1, t = cpu_dat_setup()
+    for _ in range(args.warmup):
+        cpu_dat_step(oracle, sd, x0, x1, t)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_dat_step(oracle, sd, x0, x1, t)
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    value = cpu_scale(args.height, args.width) / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args), "pairs_per_gpu": args.pairs},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_sample_text(cores)},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(args):
+    ph, pw = -(-args.height // 16) * 16, -(-args.width // 16) * 16
+    return (f"DAT (configs/DAT.yaml, nf=72) inference on synthetic {args.width}x{args.height} frame pairs replicate-padded to "
+            f"{pw}x{ph}, sharded by frame pair (BASELINE configs[3] shape, live DAT model)")
+
+
+# ------------------------------------------------------------------------------------------------
+# warp + splat micro-benchmark (BASELINE configs[1]): 1080p 4-level pyramid, C = 3..64
+# ------------------------------------------------------------------------------------------------
+def time_op(fn, iters, flush):
+    fn()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ts = sorted(x.elapsed_time(y) for x, y in evs)
+    return ts[len(ts) // 2]
+
+
+def microbench(dev, hbm_peak):
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.workloads import bytes_bwarp, bytes_splat, make_flow, seed_for
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+    res = {"flow": "smooth", "l2_flush": "256 MiB memset between iterations", "cases": []}
+    for li in range(4):
+        H, W = H_RAW >> li, W_RAW >> li
+        for C in (3, 16, 32, 64):
+            g = torch.Generator().manual_seed(seed_for(2, li * 10 + C))
+            img = torch.rand(1, C, H, W, generator=g).to(dev)
+            metric = torch.randn(1, 1, H, W, generator=g).to(dev)
+            row = {"level": li, "C": C, "H": H, "W": W}
+            for kind in ("smooth", "iid"):
+                if kind == "iid" and not (li == 0 and C in (3, 64)):
+                    continue
+                flow = make_flow(1, H, W, 8.0 / (1 << li), g, kind=kind, device=dev)
+                sfx = "" if kind == "smooth" else "_iid"
+                ms = time_op(lambda: v.bwarp(img, flow), 10, flush)
+                row["bwarp_gbs" + sfx] = bytes_bwarp(1, C, H, W) / ms / 1e6
+                ms = time_op(lambda: v.softsplat(img, flow, metric, "soft"), 10, flush)
+                row["softsplat_gbs" + sfx] = bytes_splat(1, C, H, W) / ms / 1e6
+            res["cases"].append(row)
+    big = [r for r in res["cases"] if r["level"] == 0 and r["C"] == 64][0]
+    res["bwarp_1080p_C64_frac_of_hbm"] = big["bwarp_gbs"] / hbm_peak
+    res["softsplat_1080p_C64_frac_of_hbm"] = big["softsplat_gbs"] / hbm_peak
+    return res
+
+
+# ------------------------------------------------------------------------------------------------
+# this repo's arm
+# ------------------------------------------------------------------------------------------------
+def run_vfi(args):
+    import torch.distributed as dist
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200 import _lib
+    from videoframeinterpolation_b200.workloads import bytes_dattn, init_dat_weights, seed_for
+
+    rank, world, local = dist_env(args.gpus)
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback in the product path)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert _lib.lib().vfi_device_supported() == 1, "libvfi_b200.so targets sm_100a"
+    torch.backends.cudnn.allow_tf32 = bool(args.tf32)
+    torch.backends.cuda.matmul.allow_tf32 = bool(args.tf32)
+    torch.backends.cudnn.benchmark = True
+
+    torch.manual_seed(0)
+    net = init_dat_weights(v.DATwConstantnCv1(v.default_args())).to(dev).eval()
+    P, H, W = args.pairs, args.height, args.width
+    g = torch.Generator().manual_seed(seed_for(4, rank))
+    h_x0 = torch.rand(P, 3, H, W, generator=g).pin_memory()
+    h_x1 = torch.rand(P, 3, H, W, generator=g).pin_memory()
+    h_out = torch.empty(P, 3, H, W).pin_memory()
+    t = torch.full((P, 1, 1, 1), 0.5, device=dev)
+    padder = v.InputPadder((H, W), divisor=16)
+    d_x0, d_x1 = padder.pad(h_x0.to(dev), h_x1.to(dev))
+
+    def step_device():
+        return net.inference(d_x0, d_x1, t)
+
+    def step_e2e():
+        a, b = padder.pad(h_x0.to(dev, non_blocking=True), h_x1.to(dev, non_blocking=True))
+        h_out.copy_(padder.unpad(net.inference(a, b, t)), non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, timer=None):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        if timer is not None:
+            with timer:
+                for _ in range(steps):
+                    fn()
+        else:
+            for _ in range(steps):
+                fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    with torch.no_grad():
+        for _ in range(max(args.warmup, 3)):
+            step_device()
+        clock = ClockSampler(local)
+        clock.start()
+        _lib.reset_launch_count()
+        tm = _lib.OpTimer()
+        total_ms = timed(step_device, args.steps, tm)
+        launches = _lib.launch_count()
+        clocks = clock.stop()
+        ops = tm.summary()
+        dattn_events = tm.records.get("vfi_dattn_f32", [])
+        for _ in range(2):
+            step_e2e()
+        e2e_ms = timed(step_e2e, args.steps)
+
+    ms_per_step = total_ms / args.steps
+    value = world * P / (ms_per_step / 1e3)
+    e2e_value = world * P / (e2e_ms / args.steps / 1e3)
+    hbm_peak, peak_src = peaks()
+
+    # dominant vfi_b200 kernel: fused deformable attention at 1/2 resolution (3rd vfi_dattn_f32 call of each step)
+    ph, pw = d_x0.shape[-2:]
+    lv1 = [a.elapsed_time(b) for i, (a, b) in enumerate(dattn_events) if i % 3 == 2]
+    lv1_ms = sum(lv1) / max(len(lv1), 1)
+    alg = bytes_dattn(P, 72, ph // 2, pw // 2, 8, 32)
+    achieved = alg / lv1_ms / 1e6 if lv1_ms > 0 else 0.0
+    roofline = {"kernel": "dattn_kernel<9,8> (fused sampler+attention, 1/2 res)", "bound": "hbm", "achieved": achieved,
+                "peak": hbm_peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "algorithmic_bytes_per_launch": alg, "ms_per_launch": lv1_ms,
+                "note": "per-pixel work is ~170 kFLOP of fp32 FMA (no fp32 tensor path): bounded by max(HBM, FP32 FMA)"}
+    op_ms = {k: {"calls_per_step": c / args.steps, "ms_per_step": ms / args.steps} for k, (c, ms) in ops.items()}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args), "pairs_per_gpu": P, "global_pairs_per_step": P * world,
+                       "parallelism": f"frame-pair sharding x{world}, no collective", "conv_math": "tf32" if args.tf32 else "fp32",
+                       "l2": "inputs + activations per step (>1 GB) exceed the 126 MB L2"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * h_x0.numel() * 4, "d2h_bytes_per_step": h_out.numel() * 4,
+                    "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "vfi_ops_ms": op_ms}
+
+    if rank == 0:
+        if not args.no_micro:
+            with torch.no_grad():
+                line["microbench"] = microbench(dev, hbm_peak)
+        if not args.no_cpu and world == 1:
+            cores = os.cpu_count() or 1
+            torch.set_num_threads(cores)
+            oracle, sd, x0, x1, tt = cpu_dat_setup()
+            cpu_dat_step(oracle, sd, x0, x1, tt)
+            t0 = time.perf_counter()
+            n = 2
+            for _ in range(n):
+                cpu_dat_step(oracle, sd, x0, x1, tt)
+            dt = (time.perf_counter() - t0) / n
+            line["cpu_baseline"] = {"value": cpu_scale(H, W) / dt, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": cpu_sample_text(cores), "sec_per_sample_forward": dt}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_vfi(args)
+
+
+if __name__ == "__main__":
+    main()

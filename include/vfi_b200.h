@@ -1,0 +1,150 @@
+/* vfi_b200 -- C ABI of the B200-native flow-warping / deformable-sampling library (libvfi_b200.so).
+ *
+ * The reference (Euiyeon-Kim/VideoFrameInterpolation) has no FFI layer: its boundary for this path is a
+ * set of Python functions plus three library calls.  Each entry point below names the
+ * reference interface it stands behind (file:line relative to the reference checkout).  The Python
+ * drop-ins in videoframeinterpolation_b200/ bind these with ctypes; INTEGRATION.md shows the stub a
+ * reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 (VFI_OK) or a vfi_status / cudaError-derived code; it never throws,
+ *     never allocates or frees caller memory, never synchronises the device or the stream;
+ *   - all data pointers are DEVICE pointers to fp32 unless said otherwise; strides are in ELEMENTS;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - scratch memory is supplied by the caller (`workspace`), sized by the matching *_workspace_bytes;
+ *   - safe to capture in a CUDA graph.
+ */
+#ifndef VFI_B200_H_
+#define VFI_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VFI_B200_VERSION 100 /* major*10000 + minor*100 + patch */
+
+typedef enum vfi_status {
+    VFI_OK = 0,
+    VFI_ERR_INVALID_ARGUMENT = 1,
+    VFI_ERR_UNSUPPORTED = 2,
+    VFI_ERR_CUDA = 3
+} vfi_status;
+
+/* weight applied to each source pixel before it is splatted (modules/warp.py:26-33, 69-71) */
+typedef enum vfi_splat_weight {
+    VFI_SPLAT_W_NONE = 0,     /* 'sum'   : w = 1, no weight channel                                   */
+    VFI_SPLAT_W_ONES = 1,     /* 'avg'   : w = 1, weight channel splatted                             */
+    VFI_SPLAT_W_LINEAR = 2,   /* 'linear': w = metric                                                 */
+    VFI_SPLAT_W_SOFT = 3,     /* 'soft'  : w = exp(metric)                                            */
+    VFI_SPLAT_W_SOFT_CLIP_T = 4 /* two-frame / M2M: w = t[b] * exp(clip(metric, -20, 20))             */
+} vfi_splat_weight;
+
+/* how the splatted weight channel becomes the divisor (modules/warp.py:39-56, 76-83) */
+typedef enum vfi_splat_eps {
+    VFI_EPS_ADD = 0,  /* den + eps_value (default '' and '-addeps': eps_value = 1e-7)                   */
+    VFI_EPS_ZERO = 1, /* '-zeroeps': den == 0 -> 1                                                      */
+    VFI_EPS_CLIP = 2  /* '-clipeps': max(den, eps_value)                                                */
+} vfi_splat_eps;
+
+int vfi_version(void);
+/* Human-readable description of the last non-zero status returned on the calling thread. */
+const char* vfi_last_error_string(void);
+/* 1 if the current device is compute capability 10.x (the only target this library is built for). */
+int vfi_device_supported(void);
+
+/* ---- a1: bwarp(img, flow) -- modules/warp.py:7-15 -------------------------------------------------
+ * out[b,c,y,x] = bilinear(img[b,c], clamp(ix,0,W-1), clamp(iy,0,H-1)) where ix, iy replay the reference's
+ * fp32 normalise -> F.grid_sample(align_corners=True, padding_mode='border') unnormalise round trip:
+ *   gx = lin_x[x] + flow_x / ((W-1)/2);  ix = ((gx + 1) / 2) * (W-1)          (same for y)
+ * lin_x (W floats) / lin_y (H floats) are torch.linspace(-1, 1, W/H) exactly as the reference builds them.
+ * img/out may be NCHW-contiguous or channels-last (any strides with stride_w == 1 or stride_c == 1 run
+ * the vectorised paths; other stridings run the generic path).  flow is (B,2,H,W) with arbitrary strides.
+ */
+int vfi_bwarp_f32(const float* img, const float* flow, const float* lin_x, const float* lin_y, float* out,
+                  int B, int C, int H, int W,
+                  const int64_t img_strides[4], const int64_t flow_strides[4], const int64_t out_strides[4],
+                  void* stream);
+
+/* ---- a2-a5: forward splatting -- modules/softsplat.py:237-360, modules/warp.py:18-114 -------------
+ * One call = pre-scale (weight mode) + summation splat of `in` (B,C,H,W) and of the weight channel.
+ *   num (B,C,H,W) += splat(in * w);   den (B,1,H,W) += splat(w)   (den may be NULL for VFI_SPLAT_W_NONE)
+ * accumulate == 0: num/den are zero-filled by this call first; accumulate != 0: added into (two-frame and
+ * multi-branch callers, modules/warp.py:76-80, 106-111).  metric (B,1,H,W) or NULL; t (B floats) or NULL.
+ * Non-finite targets are skipped and corners are bounds-tested one by one, as the reference kernel does
+ * (modules/softsplat.py:306-307, 325-339).  All tensors contiguous NCHW here; the Python wrapper makes
+ * non-contiguous views contiguous (the reference bakes strides into its NVRTC source instead).
+ */
+int vfi_splat_f32(const float* in, const float* flow, const float* metric, const float* t,
+                  float* num, float* den, int B, int C, int H, int W,
+                  int weight_mode, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
+size_t vfi_splat_workspace_bytes(int B, int C, int H, int W);
+
+/* out = num / f(den) per eps_mode; blank_mask (B,1,H,W) uint8, optional: f(den) < blank_threshold
+ * (modules/warp.py:83,114 use 1e-5).  `out` may alias `num`. */
+int vfi_splat_normalize_f32(const float* num, const float* den, float* out, uint8_t* blank_mask,
+                            int B, int C, int H, int W, int eps_mode, float eps_value, float blank_threshold,
+                            void* stream);
+
+/* Fused single-call form of softsplat(tenIn, tenFlow, tenMetric, strMode) for avg/linear/soft:
+ * tiled gather-form splat that owns each output tile, so the divide happens in the same kernel and no
+ * zero-fill / normalise passes touch HBM.  Same results as vfi_splat_f32 + vfi_splat_normalize_f32 up to
+ * fp32 summation order. */
+int vfi_splat_fused_f32(const float* in, const float* flow, const float* metric, float* out,
+                        int B, int C, int H, int W, int weight_mode, int eps_mode, float eps_value,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- a8 / a10: grouped multi-point sampler -- modules/deformable_attn.py:88-101, modules/madat.py:161-174
+ * feat (B,C,H,W) viewed as (B*nG, C/nG, H, W); coords (B, nG*nS, 2, H, W) = absolute displacement in pixels
+ * (channel 0 = x, 1 = y).  out (B, C, nS, H*W).  grid_out (B, nG*nS, H*W, 2) optional (madat.py:174).
+ * Coordinates replay the reference: gx = lin_x[x] + (dx / (W-1)) / 2   (sic, deformable_attn.py:94),
+ * gy = lin_y[y] + dy / ((H-1)/2), F.grid_sample(align_corners=True, padding_mode='zeros').
+ */
+int vfi_dsample_f32(const float* feat, const float* coords, const float* lin_x, const float* lin_y,
+                    float* out, float* grid_out, int B, int C, int H, int W, int nG, int nS, void* stream);
+
+/* ---- a9 / a11: Attn.forward(q, kv) on a materialised kv -- modules/deformable_attn.py:26-40, madat.py:86-115
+ * q (B,C,H,W) un-projected; kv (B,C,S,H*W); weights (C,C) row-major [out][in], biases (C).
+ * out (B,C,H,W).  score0/score1 (B*nH, S/2, H*W) optional = softmax over each half of the scaled logits.
+ */
+int vfi_attn_f32(const float* q, const float* kv, const float* Wq, const float* bq, const float* Wk,
+                 const float* bk, const float* Wv, const float* bv, float* out, float* score0, float* score1,
+                 int B, int C, int H, int W, int S, int nH, void* stream);
+
+/* ---- a8+a9 fused (both frames): sampler + projections + softmax + weighted sum, kv never materialised.
+ * offs0/offs1 (B, nG*nS*2, H, W): if coords_final == 0 these are the RAW conv_res_offset outputs and the
+ * kernel applies offset_scale * tanh(.) + ft (modules/deformable_attn.py:81-86); if coords_final != 0 they
+ * are already absolute displacements and ft0/ft1 are ignored.  ft0/ft1 (B,2,H,W) with strides ft_strides.
+ * Requires nG == nH (true for every block the reference instantiates; madat.py:121 asserts it).
+ */
+int vfi_dattn_f32(const float* q, const float* feat0, const float* feat1, const float* offs0, const float* offs1,
+                  const float* ft0, const float* ft1, const int64_t ft_strides[4],
+                  const float* Wq, const float* bq, const float* Wk, const float* bk, const float* Wv,
+                  const float* bv, const float* lin_x, const float* lin_y, float* out, float* score0,
+                  float* score1, int B, int C, int H, int W, int nG, int nS, int nH, float offset_scale,
+                  int coords_final, void* stream);
+
+/* ---- a6 / a7: modulated deformable convolution -- torchvision.ops.deform_conv2d semantics
+ * (call sites modules/dcnv2.py:60-66, models/archive/DCNDAT.py:71-77).
+ * x (B,Cin,H,W); offset (B, OG*2*kh*kw, Ho, Wo) interleaved (dy,dx); mask (B, OG*kh*kw, Ho, Wo) or NULL;
+ * weight (Cout, Cin/WG, kh, kw); bias (Cout) or NULL; out (B,Cout,Ho,Wo).  No im2col buffer in HBM.
+ * algo: 0 = auto, 1 = SIMT fp32 FFMA, 2 = tcgen05 3xTF32 (3x3/s1/p1/d1, Cin/WG in {8,9,16}).
+ */
+int vfi_dcn_f32(const float* x, const float* offset, const float* mask, const float* weight, const float* bias,
+                float* out, int B, int Cin, int Cout, int H, int W, int kh, int kw, int stride, int pad, int dil,
+                int n_weight_grps, int n_offset_grps, int algo, void* workspace, size_t workspace_bytes,
+                void* stream);
+size_t vfi_dcn_workspace_bytes(int B, int Cin, int Cout, int H, int W, int kh, int kw, int n_weight_grps,
+                               int n_offset_grps, int algo);
+
+/* Number of kernel launches issued by this library on the calling thread since the last reset
+ * (bench.py reports it as gpu_launches). */
+int64_t vfi_launch_count(void);
+void vfi_launch_count_reset(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VFI_B200_H_ */

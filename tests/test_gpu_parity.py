@@ -1,0 +1,123 @@
+"""GPU parity: the CUDA path (through the C ABI) vs the golden fixtures and vs the oracle on seeded inputs."""
+import pytest
+import torch
+
+import _det as det
+import golden_cases as gc
+import oracle
+from oracle.torch_oracle import _P
+from _util import assert_close, rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5          # warp / DCN / sampler / attention (north_star)
+TOL_SPLAT = 1e-4    # splat: summation order differs
+
+
+@pytest.fixture(scope="module")
+def vfi():
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200 import _lib
+    assert _lib.lib().vfi_device_supported() == 1, "needs an sm_100 device"
+    return v
+
+
+def cu(*ts):
+    r = tuple(None if t is None else t.cuda() for t in ts)
+    return r if len(r) > 1 else r[0]
+
+
+# ---- bwarp -----------------------------------------------------------------------------------
+def test_bwarp_golden(vfi, golden):
+    g = golden("bwarp")
+    for key, (img, flow) in gc.bwarp_cases().items():
+        assert_close(vfi.bwarp(*cu(img, flow)), g[key], TOL, f"bwarp[{key}]")
+
+
+@pytest.mark.parametrize("shape", [(1, 3, 270, 480), (2, 64, 68, 120), (1, 7, 33, 65), (1, 1, 16, 16)])
+def test_bwarp_vs_oracle(vfi, shape):
+    B, C, H, W = shape
+    img = det.normal(f"bwo.{shape}", shape)
+    flow = det.flow_field(f"bwo.f.{shape}", B, H, W, sigma=4.0)
+    assert_close(vfi.bwarp(*cu(img, flow)), oracle.bwarp(img, flow), TOL, f"bwarp{shape}")
+
+
+def test_bwarp_channels_last_and_strided_flow(vfi):
+    B, C, H, W = 2, 72, 34, 60
+    img = det.normal("bwcl.img", (B, C, H, W))
+    big = det.flow_field("bwcl.flow", B, H, W, sigma=3.0)
+    packed = torch.cat((det.normal("bwcl.pad", (B, 5, H, W)), big), 1)        # flow as a channel slice (models/DAT.py:82)
+    ref = oracle.bwarp(img, big)
+    out_cl = vfi.bwarp(img.cuda().contiguous(memory_format=torch.channels_last), packed.cuda()[:, 5:7])
+    assert out_cl.is_contiguous(memory_format=torch.channels_last)
+    assert_close(out_cl, ref, TOL, "bwarp channels_last")
+    assert_close(vfi.bwarp(img.cuda(), packed.cuda()[:, 5:7]), ref, TOL, "bwarp strided flow")
+
+
+def test_bwarp_identity_and_idempotence_1080p(vfi):
+    """Size-independent properties at BASELINE size: zero flow is the identity; integer shifts commute with slicing."""
+    img = torch.rand(1, 16, 1080, 1920, device="cuda")
+    zero = torch.zeros(1, 2, 1080, 1920, device="cuda")
+    assert rel_err(vfi.bwarp(img, zero), img) <= 2e-6
+    shift = zero.clone()
+    shift[:, 0] = 3.0
+    shift[:, 1] = -2.0
+    out = vfi.bwarp(img, shift)
+    # away from the borders an integer flow is an exact shift up to the fp32 round trip of the coordinates
+    assert rel_err(out[..., 8:-8, 8:-8], img[..., 6:-10, 11:-5]) <= 2e-3
+    lin = oracle.bwarp(img[:, :2].cpu(), shift.cpu())
+    assert_close(out[:, :2], lin, TOL, "bwarp 1080p vs oracle (2 channels)")
+
+
+# ---- splat -------------------------------------------------------------------------------------
+def test_splat_golden(vfi, golden):
+    g = golden("splat")
+    for key, (x, fl) in gc.splat_sum_cases().items():
+        assert_close(vfi.softsplat_func.apply(*cu(x, fl)), g[key], TOL_SPLAT, f"splat_sum[{key}]")
+    for key, (x, fl, metric, mode) in gc.fwarp_cases().items():
+        assert_close(vfi.fwarp(*cu(x, fl, metric), mode), g[key], TOL_SPLAT, f"fwarp[{key}]")
+        assert_close(vfi.softsplat(*cu(x, fl, metric), mode), g[key], TOL_SPLAT, f"softsplat[{key}]")
+    for key, args in gc.two_frame_cases().items():
+        o, m = vfi.fwarp_using_two_frames(*cu(*args))
+        assert_close(o, g[key + "_out"], TOL_SPLAT, key)
+        assert m.dtype == torch.bool and (m.cpu().to(torch.uint8) != g[key + "_mask"]).float().mean() < 0.01
+    for key, args in gc.mframes_cases().items():
+        o, m = vfi.fwarp_mframes(*cu(*args))
+        assert_close(o, g[key + "_out"], TOL_SPLAT, key)
+        assert (m.cpu().to(torch.uint8) != g[key + "_mask"]).float().mean() < 0.01
+
+
+@pytest.mark.parametrize("mode", ["sum", "avg", "linear", "soft", "soft-zeroeps", "linear-clipeps"])
+@pytest.mark.parametrize("shape", [(1, 3, 135, 240), (2, 16, 67, 121)])
+def test_splat_vs_oracle(vfi, mode, shape):
+    B, C, H, W = shape
+    x = det.normal(f"spo.{shape}", shape)
+    fl = det.flow_field(f"spo.f.{shape}", B, H, W, sigma=3.0, nonfinite_frac=0.001)
+    head = mode.split("-")[0]
+    metric = None if head in ("sum", "avg") else (det.normal(f"spo.m.{shape}", (B, 1, H, W)) if head == "soft"
+                                                  else det.uniform(f"spo.m.{shape}", (B, 1, H, W), lo=0.01, hi=1.0))
+    assert_close(vfi.fwarp(*cu(x, fl, metric), mode), oracle.fwarp(x, fl, metric, mode), TOL_SPLAT, f"fwarp {mode} {shape}")
+
+
+def test_splat_rejects_cpu_and_bad_modes(vfi):
+    x, fl = torch.zeros(1, 1, 4, 4), torch.zeros(1, 2, 4, 4)
+    with pytest.raises(Exception):
+        vfi.softsplat_func.apply(x, fl)                      # CPU tensors: no fallback (reference asserts False)
+    with pytest.raises(AssertionError):
+        vfi.fwarp(x.cuda(), fl.cuda(), None, "soft")         # soft needs a metric
+    with pytest.raises(AssertionError):
+        vfi.fwarp(x.cuda(), fl.cuda(), x.cuda(), "avg")      # avg takes none
+    with pytest.raises(AssertionError):
+        vfi.fwarp(x.cuda(), fl.cuda(), None, "median")
+
+
+def test_splat_mass_conservation_1080p(vfi):
+    """Linearity / conservation at full size: with flows that stay inside the frame, sum(splat(x)) == sum(x)."""
+    H, W = 1080, 1920
+    x = torch.rand(1, 3, H, W, device="cuda")
+    fl = torch.randn(1, 2, H, W, device="cuda") * 2.0
+    fl[..., :8, :] = 0; fl[..., -8:, :] = 0; fl[..., :, :8] = 0; fl[..., :, -8:] = 0
+    out = vfi.softsplat(x, fl, None, "sum")
+    assert abs(float(out.double().sum() / x.double().sum()) - 1.0) < 1e-5
+    out2 = vfi.softsplat(2.0 * x, fl, None, "sum")
+    assert rel_err(out2, 2.0 * out) < 1e-5

@@ -1,0 +1,188 @@
+"""GPU parity for DCNv2, the grouped sampler, attention (unfused and fused), and the DAT forward."""
+import pytest
+import torch
+
+import _det as det
+import golden_cases as gc
+import oracle
+from oracle.torch_oracle import _P
+from _util import assert_close, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def vfi():
+    import videoframeinterpolation_b200 as v
+    torch.backends.cudnn.allow_tf32 = False          # dense convs in fp32 for model-level parity
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return v
+
+
+def cu(*ts):
+    r = tuple(None if t is None else t.cuda() for t in ts)
+    return r if len(r) > 1 else r[0]
+
+
+def cu_kw(kw):
+    return {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in kw.items()}
+
+
+def load_sd(module, sd):
+    module.load_state_dict({k: v.clone() for k, v in sd.items()}, strict=True)
+    return module.cuda().eval()
+
+
+# ---- DCNv2 -----------------------------------------------------------------------------------
+@pytest.mark.parametrize("algo", ["simt"])
+def test_dcn_op_golden(vfi, golden, algo):
+    g = golden("dcn")
+    for key, kw in gc.dcn_op_cases().items():
+        k = cu_kw(kw)
+        out = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=k["stride"], padding=k["padding"],
+                                dilation=k["dilation"], mask=k["mask"], algo=algo)
+        assert_close(out, g[key], TOL, f"dcn[{key}]")
+
+
+def test_dcn_module_golden(vfi, golden):
+    from test_oracle_golden import _module_sd_dcn
+    g = golden("dcn")
+    C = gc.DCN_MODULE_C
+    mod = load_sd(vfi.DeformableConv2d(C, C), _module_sd_dcn())
+    x, mv = gc.dcn_module_inputs()
+    with torch.no_grad():
+        out, flow = mod(*cu(x, mv))
+    assert_close(flow, g["module_flow"], TOL, "dcn module flow")
+    assert_close(out, g["module_out"], 2e-5, "dcn module out")
+    kw = gc.dcn_given_offset_case()
+    m2 = vfi.DeformableConv2dGivenOffset(16, 16)
+    m2.load_state_dict({"regular_conv.weight": kw["weight"], "regular_conv.bias": kw["bias"]})
+    with torch.no_grad():
+        assert_close(m2.cuda()(*cu(kw["x"], kw["offset"], kw["mask"])), g["given_offset"], TOL, "dcn given offset")
+
+
+def test_dcn_vs_oracle_dim64(vfi):
+    kw = gc._dcn_op("big", 2, 64, 64, 24, 40, WG=8, OG=8)
+    with oracle.library_ops():
+        ref = oracle.deform_conv2d(**kw)
+    k = cu_kw(kw)
+    out = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"])
+    assert_close(out, ref, TOL, "dcn dim64")
+    # zero offsets + unit mask == ordinary grouped convolution
+    z = torch.zeros_like(k["offset"])
+    out0 = vfi.deform_conv2d(k["x"], z, k["weight"], k["bias"], stride=1, padding=1, mask=torch.ones_like(k["mask"]))
+    ref0 = torch.nn.functional.conv2d(k["x"], k["weight"], k["bias"], padding=1, groups=8)
+    assert_close(out0, ref0, TOL, "dcn zero offsets == grouped conv")
+
+
+# ---- sampler / attention -------------------------------------------------------------------------
+def test_dsample_golden(vfi, golden):
+    from videoframeinterpolation_b200.deformable_attn import grouped_sample
+    g = golden("dat_block")
+    cfg = gc.DAT_BLOCK
+    feat, flow = gc.dsample_case()
+    assert_close(grouped_sample(*cu(feat, flow), cfg["n_groups"], cfg["n_samples"]), g["dsample"], TOL, "dsample")
+
+
+def test_dat_block_golden(vfi, golden):
+    from test_oracle_golden import dat_block_sd
+    g = golden("dat_block")
+    cfg = gc.DAT_BLOCK
+    blk = load_sd(vfi.CrossDeformableAttentionBlockwFlow(cfg["c"], cfg["c"], n_samples=cfg["n_samples"], n_groups=cfg["n_groups"],
+                                                         n_heads=cfg["n_heads"], mlp_ratio=2, offset_scale=cfg["offset_scale"]),
+                  dat_block_sd(cfg["c"], cfg["n_samples"], cfg["n_groups"]))
+    feat_t, feat0, feat1, ft0, ft1 = cu(*gc.dat_block_inputs())
+    with torch.no_grad():
+        mv0 = blk._get_movement_feats(feat_t, feat0, ft0)
+        coords0 = blk._get_ref_coords(feat_t, ft0, mv0)
+        kv0 = blk._get_ref_feats(feat0, coords0)
+        mv1 = blk._get_movement_feats(feat_t, feat1, ft1)
+        kv1 = blk._get_ref_feats(feat1, blk._get_ref_coords(feat_t, ft1, mv1))
+        assert_close(coords0, g["coords0"], TOL, "coords0")
+        assert_close(kv0, g["kv0"], TOL, "kv0")
+        assert_close(blk.attn(feat_t, torch.cat((kv0, kv1), dim=2)), g["attn"], TOL, "Attn (materialised kv)")
+        out, u0, u1 = blk(feat_t, feat0, feat1, ft0, ft1)          # fused path
+    assert_close(out, g["block_out"], 2e-5, "block out (fused)")
+    assert_close(u0, g["up_ft0"], TOL, "up_ft0")
+    assert_close(u1, g["up_ft1"], TOL, "up_ft1")
+
+
+@pytest.mark.parametrize("cfg", [dict(c=72, nG=8, nS=32, scale=8.0, H=20, W=28), dict(c=72, nG=4, nS=8, scale=2.0, H=17, W=23),
+                                 dict(c=64, nG=8, nS=9, scale=2.0, H=12, W=16), dict(c=64, nG=4, nS=9, scale=2.0, H=12, W=16)])
+def test_fused_dattn_vs_oracle(vfi, cfg):
+    from videoframeinterpolation_b200.deformable_attn import fused_deformable_attention
+    c, nG, nS, H, W, B = cfg["c"], cfg["nG"], cfg["nS"], cfg["H"], cfg["W"], 2
+    tag = f"fd.{c}.{nG}.{nS}"
+    q, f0, f1 = (det.normal(f"{tag}.{n}", (B, c, H, W)) for n in ("q", "f0", "f1"))
+    raw0, raw1 = (det.normal(f"{tag}.{n}", (B, nG * nS * 2, H, W)) for n in ("r0", "r1"))
+    ft0, ft1 = det.flow_field(f"{tag}.ft0", B, H, W, sigma=2.0), det.flow_field(f"{tag}.ft1", B, H, W, sigma=2.0)
+    names = ("q_proj", "k_proj", "v_proj")
+    sd = gc.fill({f"{n}.{k}": torch.empty(*s) for n in names for k, s in (("weight", (c, c, 1, 1)), ("bias", (c,)))})
+    with oracle.library_ops():
+        kv = torch.cat((oracle.dsample(f0, oracle.ref_coords(raw0, ft0, nG, nS, cfg["scale"]), nG, nS),
+                        oracle.dsample(f1, oracle.ref_coords(raw1, ft1, nG, nS, cfg["scale"]), nG, nS)), dim=2)
+    ref = oracle.attn(_P(sd), q, kv, nG)
+    w = [sd[f"{n}.{k}"].cuda() for n in names for k in ("weight", "bias")]
+    out = fused_deformable_attention(*cu(q, f0, f1, raw0, raw1, ft0, ft1), *w, n_groups=nG, n_samples=nS, n_heads=nG,
+                                     offset_scale=cfg["scale"])
+    assert_close(out, ref, TOL, f"fused dattn {cfg}")
+
+
+def test_madat_golden(vfi, golden):
+    g = golden("madat")
+    cfg = gc.MADAT
+    m = vfi.DATwithMotionEstimation(cfg["c"], cfg["c"], n_samples=cfg["n_samples"], n_groups=cfg["n_groups"], n_heads=cfg["n_heads"])
+    sd = gc.fill(m.state_dict())
+    m = load_sd(m, sd)
+    feat, flow, q, kv = cu(*gc.madat_inputs())
+    with torch.no_grad():
+        s, grid = m._get_ref_feats(feat, flow)
+        a, s0, s1 = m.attn(q, kv)
+    assert_close(s, g["samples"], TOL, "madat samples")
+    assert_close(grid, g["grid"], 1e-6, "madat grid")
+    assert_close(a, g["attn_out"], TOL, "madat attn")
+    assert_close(s0, g["score0"], TOL, "madat score0")
+    assert_close(s1, g["score1"], TOL, "madat score1")
+
+
+def test_madat_fused_scores_match_unfused(vfi):
+    cfg = gc.MADAT
+    m = vfi.DATwithMotionEstimation(cfg["c"], cfg["c"], n_samples=cfg["n_samples"], n_groups=cfg["n_groups"], n_heads=cfg["n_heads"])
+    m = load_sd(m, gc.fill(m.state_dict()))
+    B, c, H, W = 2, cfg["c"], 8, 10
+    feat_t, feat0, feat1 = cu(det.normal("mf.t", (B, c, H, W)), det.normal("mf.0", (B, c, H, W)), det.normal("mf.1", (B, c, H, W)))
+    ft0, ft1 = cu(det.flow_field("mf.ft0", B, H, W, sigma=1.5), det.flow_field("mf.ft1", B, H, W, sigma=1.5))
+    with torch.no_grad():
+        a, s0, s1 = m.attend(feat_t, feat0, feat1, ft0, ft1)
+        mv0, mv1 = m._get_movement_feats(feat_t, feat0, ft0), m._get_movement_feats(feat_t, feat1, ft1)
+        kv0, _ = m._get_ref_feats(feat0, m._get_ref_flow(feat_t, ft0, mv0))
+        kv1, _ = m._get_ref_feats(feat1, m._get_ref_flow(feat_t, ft1, mv1))
+        a_ref, s0_ref, s1_ref = m.attn(m._norm_c(feat_t), torch.cat((kv0, kv1), dim=2))
+    assert_close(a, a_ref, TOL, "madat fused out")
+    assert_close(s0, s0_ref, TOL, "madat fused score0")
+    assert_close(s1, s1_ref, TOL, "madat fused score1")
+
+
+# ---- whole model -------------------------------------------------------------------------------
+def test_dat_model_golden(vfi, golden):
+    g = golden("dat_model")
+    args = vfi.default_args(**gc.DAT_SMALL_ARGS)
+    net = vfi.DATwConstantnCv1(args)
+    net = load_sd(net, gc.fill(net.state_dict()))
+    x0, x1, t = cu(*gc.dat_model_inputs())
+    assert_close(net.inference(x0, x1, t), g["pred"], 5e-5, "DAT small vs reference")
+
+
+def test_dat_full_width_golden_and_oracle(vfi, golden):
+    g = golden("dat_model_full")
+    net = vfi.DATwConstantnCv1(vfi.default_args())
+    sd = gc.fill(net.state_dict(), seed=1)
+    net = load_sd(net, sd)
+    x0, x1, t = gc.dat_model_inputs(H=64, W=64, seed=1)
+    assert_close(net.inference(*cu(x0, x1, t)), g["pred"], 5e-5, "DAT nf=72 vs reference")
+    # configs[0]: one 448x256 Vimeo90K-shaped triplet against the oracle
+    x0, x1, t = gc.dat_model_inputs(H=256, W=448, seed=2)
+    with oracle.library_ops():
+        ref = oracle.dat_forward({k: v.cpu() for k, v in sd.items()}, x0, x1, t)
+    assert_close(net.inference(*cu(x0, x1, t)), ref, 5e-5, "DAT 448x256 vs oracle")

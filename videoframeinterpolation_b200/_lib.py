@@ -1,0 +1,172 @@
+"""ctypes binding of libvfi_b200.so (C ABI: include/vfi_b200.h).
+
+There is NO fallback: if the shared library is missing or a tensor is not on a CUDA device the
+call raises (the reference's splat likewise refuses CPU tensors, modules/softsplat.py:352-353).
+PyTorch is used only for device memory and the current stream.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_float, c_int, c_int64, c_size_t, c_void_p
+from pathlib import Path
+from typing import Dict, Optional, Tuple
+
+import torch
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = Path(os.environ.get("VFI_B200_LIB", _PKG / "libvfi_b200.so"))
+
+_I64x4 = c_int64 * 4
+_lib: Optional[ctypes.CDLL] = None
+
+# name -> (restype, argtypes); every entry is declared in include/vfi_b200.h
+SIGNATURES = {
+    "vfi_version": (c_int, []),
+    "vfi_last_error_string": (ctypes.c_char_p, []),
+    "vfi_device_supported": (c_int, []),
+    "vfi_bwarp_f32": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p] * 3 + [c_void_p]),
+    "vfi_splat_f32": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_int, c_int, c_void_p, c_size_t, c_void_p]),
+    "vfi_splat_workspace_bytes": (c_size_t, [c_int] * 4),
+    "vfi_splat_normalize_f32": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_int, c_float, c_float, c_void_p]),
+    "vfi_splat_fused_f32": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_int, c_int, c_float, c_void_p, c_size_t, c_void_p]),
+    "vfi_dsample_f32": (c_int, [c_void_p] * 6 + [c_int] * 6 + [c_void_p]),
+    "vfi_attn_f32": (c_int, [c_void_p] * 11 + [c_int] * 6 + [c_void_p]),
+    "vfi_dattn_f32": (c_int, [c_void_p] * 19 + [c_int] * 7 + [c_float, c_int, c_void_p]),
+    "vfi_dcn_f32": (c_int, [c_void_p] * 6 + [c_int] * 13 + [c_void_p, c_size_t, c_void_p]),
+    "vfi_dcn_workspace_bytes": (c_size_t, [c_int] * 10),
+    "vfi_launch_count": (c_int64, []),
+    "vfi_launch_count_reset": (None, []),
+}
+
+
+class VfiError(RuntimeError):
+    pass
+
+
+def lib() -> ctypes.CDLL:
+    """Load (once) and return the shared library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise VfiError(f"{LIB_PATH} not found: build it with `python -m videoframeinterpolation_b200.build` "
+                           "(there is no CPU or PyTorch fallback)")
+        handle = ctypes.CDLL(str(LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = handle
+    return _lib
+
+
+def check(status: int, what: str) -> None:
+    if status != 0:
+        raise VfiError(f"{what} failed with status {status}: {lib().vfi_last_error_string().decode()}")
+
+
+def require_cuda(*tensors: Optional[torch.Tensor]) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise VfiError("vfi_b200 ops need CUDA tensors (no CPU fallback)")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise VfiError(f"tensors on different devices: {dev} vs {t.device}")
+    if dev is None:
+        raise VfiError("no tensor given")
+    return dev
+
+
+def f32c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """fp32 + contiguous (the splat reference also forces fp32: modules/softsplat.py:284)."""
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def f32(t: torch.Tensor) -> torch.Tensor:
+    return t if t.dtype == torch.float32 else t.float()
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def strides4(t: torch.Tensor):
+    return _I64x4(*t.stride())
+
+
+def stream_ptr(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+_lin_cache: Dict[Tuple[int, str], torch.Tensor] = {}
+
+
+def linspace_m11(n: int, dev: torch.device) -> torch.Tensor:
+    """torch.linspace(-1, 1, n) built on the CPU exactly as the reference does (modules/warp.py:9-10),
+    cached on the device so the per-call H2D copy of the reference disappears."""
+    key = (n, str(dev))
+    t = _lin_cache.get(key)
+    if t is None:
+        t = torch.linspace(-1.0, 1.0, n).to(dev)
+        _lin_cache[key] = t
+    return t
+
+
+def launch_count() -> int:
+    return int(lib().vfi_launch_count())
+
+
+def reset_launch_count() -> None:
+    lib().vfi_launch_count_reset()
+
+
+class OpTimer:
+    """Collects CUDA-event timings of every C-ABI call made while active (bench.py's per-kernel numbers).
+
+        with OpTimer() as tm: ...   ;   torch.cuda.synchronize()   ;   tm.summary() -> {name: (calls, total_ms)}
+    Events are recorded on the stream the call is launched on.
+    """
+
+    def __init__(self):
+        self.records = {}
+
+    def __enter__(self):
+        global _timer
+        self._prev, _timer = _timer, self
+        return self
+
+    def __exit__(self, *exc):
+        global _timer
+        _timer = self._prev
+        return False
+
+    def summary(self):
+        out = {}
+        for name, evs in self.records.items():
+            out[name] = (len(evs), sum(a.elapsed_time(b) for a, b in evs))
+        return out
+
+
+_timer: Optional[OpTimer] = None
+
+
+def call(name: str, dev: torch.device, *args, tag: Optional[str] = None) -> None:
+    """Invoke one C-ABI entry point on the current stream of ``dev`` and raise on a non-zero status."""
+    fn = getattr(lib(), name)
+    if _timer is None:
+        check(fn(*args), name)
+        return
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stream = torch.cuda.current_stream(dev)
+    start.record(stream)
+    status = fn(*args)
+    end.record(stream)
+    check(status, name)
+    _timer.records.setdefault(tag or name, []).append((start, end))

@@ -1,0 +1,109 @@
+"""Dense conv stacks that surround the hot path (cuDNN through PyTorch; out of scope as kernels).
+
+Only the parameter layout is shared with the reference (``modules/basic_blocks.py``, ``modules/cnn_encoders.py``,
+``modules/generator.py``) so that its state dicts load unchanged.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+def conv_prelu(cin: int, cout: int, stride: int = 1) -> nn.Sequential:
+    return nn.Sequential(nn.Conv2d(cin, cout, 3, stride, 1), nn.PReLU(cout))
+
+
+class ResBlocknoBN(nn.Module):
+    """x + conv2(prelu(conv1(x)))  (state-dict keys conv1 / conv2 / prelu)."""
+
+    def __init__(self, nf: int = 64):
+        super().__init__()
+        self.conv1 = nn.Conv2d(nf, nf, 3, 1, 1)
+        self.conv2 = nn.Conv2d(nf, nf, 3, 1, 1)
+        self.prelu = nn.PReLU(nf)
+        for conv in (self.conv1, self.conv2):      # kaiming * 0.1, zero bias (modules/basic_blocks.py:27)
+            nn.init.kaiming_normal_(conv.weight, a=0, mode="fan_in")
+            conv.weight.data.mul_(0.1)
+            nn.init.zeros_(conv.bias)
+
+    def forward(self, x):
+        return x + self.conv2(self.prelu(self.conv1(x)))
+
+
+class HalfChannelConv5ResBlock(nn.Module):
+    """IFRNet-style 5-conv residual block whose even convs touch only the last ``side_c`` channels."""
+
+    def __init__(self, in_c: int, side_c: int):
+        super().__init__()
+        self.side_c = side_c
+        self.conv1, self.conv2 = conv_prelu(in_c, in_c), conv_prelu(side_c, side_c)
+        self.conv3, self.conv4 = conv_prelu(in_c, in_c), conv_prelu(side_c, side_c)
+        self.conv5 = nn.Conv2d(in_c, in_c, 3, 1, 1)
+        self.prelu = nn.PReLU(in_c)
+
+    def _side(self, t, conv):
+        keep = t.shape[1] - self.side_c
+        return torch.cat((t[:, :keep], conv(t[:, keep:])), dim=1)
+
+    def forward(self, x):
+        t = self._side(self.conv1(x), self.conv2)
+        t = self._side(self.conv3(t), self.conv4)
+        return self.prelu(x + self.conv5(t))
+
+
+class FeadForward(nn.Module):
+    """1x1-conv MLP with GELU (keys fc1 / fc2; the reference's spelling of the class name is kept)."""
+
+    def __init__(self, in_dim, hidden_dim=None, out_dim=None):
+        super().__init__()
+        hidden_dim, out_dim = int(hidden_dim or in_dim), int(out_dim or in_dim)
+        self.fc1 = nn.Conv2d(in_dim, hidden_dim, 1)
+        self.act = nn.GELU()
+        self.fc2 = nn.Conv2d(hidden_dim, out_dim, 1)
+
+    def forward(self, x):
+        return self.fc2(self.act(self.fc1(x)))
+
+
+class SameChannelResEncoder(nn.Module):
+    """4-level feature pyramid at 1/2, 1/4, 1/8, 1/16 resolution, nf channels each."""
+
+    def __init__(self, nf: int, n_res_block: int):
+        super().__init__()
+        self.projection = nn.Sequential(nn.Conv2d(3, nf, 3, 1, 1), nn.PReLU(nf), nn.Conv2d(nf, nf, 3, 2, 1), nn.PReLU(nf),
+                                        *[ResBlocknoBN(nf) for _ in range(n_res_block)])
+
+        def down():
+            return nn.Sequential(nn.Conv2d(nf, nf, 3, 2, 1), nn.PReLU(nf), nn.Conv2d(nf, nf, 3, 1, 1), nn.PReLU(nf))
+        self.fea_L2_conv, self.fea_L3_conv, self.fea_L4_conv = down(), down(), down()
+
+    def forward(self, x):
+        f1 = self.projection(x)
+        f2 = self.fea_L2_conv(f1)
+        f3 = self.fea_L3_conv(f2)
+        return f1, f2, f3, self.fea_L4_conv(f3)
+
+
+class BasicResPixelShuffleGenerator(nn.Module):
+    """Residual trunk -> pixel-shuffle x2 -> RGB, clamp(out + mean, 0, 1)."""
+
+    def __init__(self, nf: int, num_res_blocks: int):
+        super().__init__()
+        self.nf = nf
+        self.reconstruction = nn.Sequential(*[ResBlocknoBN(nf) for _ in range(num_res_blocks)])
+        self.upconv1 = nn.Conv2d(nf, nf * 4, 3, 1, 1)
+        self.prelu1 = nn.PReLU(nf)
+        self.pixel_shuffle = nn.PixelShuffle(2)
+        self.HRconv = nn.Conv2d(nf, nf, 3, 1, 1)
+        self.prelu2 = nn.PReLU(nf)
+        self.conv_last = nn.Conv2d(nf, 3, 3, 1, 1)
+
+    def forward(self, feat, m):
+        t = self.prelu1(self.pixel_shuffle(self.upconv1(self.reconstruction(feat))))
+        return torch.clamp(self.conv_last(self.prelu2(self.HRconv(t))) + m, 0, 1)
+
+
+def resize(x, scale_factor):
+    """``BaseModel.resize`` (models/BaseModel.py:19-22)."""
+    return F.interpolate(x, scale_factor=scale_factor, recompute_scale_factor=False, mode="bilinear", align_corners=True)

@@ -1,0 +1,86 @@
+// Shared helpers for the vfi_b200 kernels (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/vfi_b200.h"
+
+namespace vfi {
+
+constexpr int kNumSMs = 148;  // B200
+
+void set_error(const char* fmt, ...);
+void note_launch();
+
+#define VFI_REQUIRE(cond, ...)                         \
+    do {                                               \
+        if (!(cond)) {                                 \
+            ::vfi::set_error(__VA_ARGS__);             \
+            return VFI_ERR_INVALID_ARGUMENT;           \
+        }                                              \
+    } while (0)
+
+#define VFI_UNSUPPORTED(...)                           \
+    do {                                               \
+        ::vfi::set_error(__VA_ARGS__);                 \
+        return VFI_ERR_UNSUPPORTED;                    \
+    } while (0)
+
+// Check the launch that was just issued (no synchronisation).
+#define VFI_CHECK_LAUNCH(name)                                                        \
+    do {                                                                              \
+        ::vfi::note_launch();                                                         \
+        cudaError_t e__ = cudaGetLastError();                                         \
+        if (e__ != cudaSuccess) {                                                     \
+            ::vfi::set_error("%s: launch failed: %s", name, cudaGetErrorString(e__)); \
+            return VFI_ERR_CUDA;                                                      \
+        }                                                                             \
+    } while (0)
+
+#define VFI_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            ::vfi::set_error("%s failed: %s", #call, cudaGetErrorString(e__));           \
+            return VFI_ERR_CUDA;                                                         \
+        }                                                                                \
+    } while (0)
+
+static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline int64_t min64(int64_t a, int64_t b) { return a < b ? a : b; }
+
+// ---- device helpers ---------------------------------------------------------------------------
+
+// streaming (read-once / write-once) accesses: keep them out of L1
+__device__ __forceinline__ float ld_stream(const float* p) {
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float4 ld_stream4(const float* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_stream(float* p, float v) {
+    asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void st_stream4(float* p, float4 v) {
+    asm volatile("st.global.cs.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+// gather loads through the read-only path (cached in L1: neighbouring lanes share lines)
+__device__ __forceinline__ float ld_gather(const float* p) { return __ldg(p); }
+
+// Replay of the reference's normalise -> grid_sample unnormalise round trip, fp32, no FMA contraction
+// (reference: modules/warp.py:9-13 + ATen grid_sampler unnormalize, align_corners=True).
+//   g = lin + d / half_extent ;  i = ((g + 1) / 2) * (size - 1)
+__device__ __forceinline__ float replay_coord(float lin, float d_scaled, float size_m1) {
+    const float g = __fadd_rn(lin, d_scaled);
+    return __fmul_rn(__fmul_rn(__fadd_rn(g, 1.0f), 0.5f), size_m1);
+}
+
+}  // namespace vfi

@@ -1,0 +1,170 @@
+"""Drop-in for the reference's ``modules/deformable_attn.py``.
+
+    Attn(in_c, out_c, n_samples, n_heads).forward(q, kv)                          lines 10-40
+    CrossDeformableAttentionBlockwFlow(...).forward(feat_t, feat0, feat1, ft0, ft1)   lines 43-124
+        ._get_movement_feats / ._get_ref_coords / ._get_ref_feats                 lines 77-101
+
+``forward`` never materialises the (B, C, 2nS, H*W) sample tensor: one fused kernel (csrc/dattn.cu) takes the
+raw ``conv_res_offset`` outputs and does tanh/scale/+flow, sampling of both frames, q/k/v projections, softmax
+and the weighted sum.  The piecewise methods keep the reference's signatures and go through the materialising
+kernels (csrc/dsample.cu, csrc/attn.cu).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .blocks import FeadForward, HalfChannelConv5ResBlock, conv_prelu, resize
+from .warp import bwarp
+
+__all__ = ["Attn", "CrossDeformableAttentionBlockwFlow", "grouped_sample", "attention_over_samples", "fused_deformable_attention"]
+
+
+def grouped_sample(feat: torch.Tensor, flow: torch.Tensor, n_groups: int, n_samples: int, want_grid: bool = False):
+    """feat (b,c,h,w), flow (b, nG*nS, 2, h, w) absolute displacement -> samples (b, c, nS, h*w) [, grid (b,nG*nS,h*w,2)]."""
+    dev = _lib.require_cuda(feat, flow)
+    feat, flow = _lib.f32c(feat), _lib.f32c(flow)
+    b, c, fh, fw = feat.shape
+    assert tuple(flow.shape) == (b, n_groups * n_samples, 2, fh, fw), f"flow shape {tuple(flow.shape)}"
+    out = torch.empty((b, c, n_samples, fh * fw), dtype=torch.float32, device=dev)
+    grid = torch.empty((b, n_groups * n_samples, fh * fw, 2), dtype=torch.float32, device=dev) if want_grid else None
+    _lib.call("vfi_dsample_f32", dev, feat.data_ptr(), flow.data_ptr(), _lib.linspace_m11(fw, dev).data_ptr(),
+                                          _lib.linspace_m11(fh, dev).data_ptr(), out.data_ptr(), _lib.ptr(grid), b, c, fh, fw,
+                                          n_groups, n_samples, _lib.stream_ptr(dev))
+    return (out, grid) if want_grid else out
+
+
+def _w2d(w: torch.Tensor) -> torch.Tensor:
+    return _lib.f32c(w.reshape(w.shape[0], -1))
+
+
+def attention_over_samples(q, kv, wq, bq, wk, bk, wv, bv, n_heads: int, want_scores: bool = False):
+    """Per-pixel multi-head attention of q (b,c,h,w) over kv (b,c,S,h*w); weights (c,c[,1,1]) / biases (c)."""
+    dev = _lib.require_cuda(q, kv)
+    q, kv = _lib.f32c(q), _lib.f32c(kv)
+    b, c, fh, fw = q.shape
+    S = kv.shape[2]
+    assert tuple(kv.shape) == (b, c, S, fh * fw), f"kv shape {tuple(kv.shape)}"
+    out = torch.empty((b, c, fh, fw), dtype=torch.float32, device=dev)
+    s0 = s1 = None
+    if want_scores:
+        s0 = torch.empty((b * n_heads, S // 2, fh * fw), dtype=torch.float32, device=dev)
+        s1 = torch.empty_like(s0)
+    _lib.call("vfi_attn_f32", dev, q.data_ptr(), kv.data_ptr(), _w2d(wq).data_ptr(), _lib.f32c(bq).data_ptr(),
+                                       _w2d(wk).data_ptr(), _lib.f32c(bk).data_ptr(), _w2d(wv).data_ptr(),
+                                       _lib.f32c(bv).data_ptr(), out.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), b, c, fh, fw, S,
+                                       n_heads, _lib.stream_ptr(dev))
+    return (out, s0, s1) if want_scores else out
+
+
+def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torch.Tensor], ft1: Optional[torch.Tensor],
+                               wq, bq, wk, bk, wv, bv, n_groups: int, n_samples: int, n_heads: int, offset_scale: float,
+                               coords_final: bool = False, want_scores: bool = False):
+    """Sampler + attention over both frames in one kernel (vfi_dattn_f32).
+
+    offs* (b, nG*nS*2, h, w): raw conv_res_offset outputs (``coords_final=False``: the kernel applies
+    offset_scale*tanh(.) + ft*) or final displacements laid out (b, nG*nS, 2, h, w) (``coords_final=True``).
+    """
+    dev = _lib.require_cuda(q, feat0, feat1, offs0, offs1)
+    q, feat0, feat1 = _lib.f32c(q), _lib.f32c(feat0), _lib.f32c(feat1)
+    offs0, offs1 = _lib.f32c(offs0), _lib.f32c(offs1)
+    b, c, fh, fw = q.shape
+    assert offs0.numel() == b * n_groups * n_samples * 2 * fh * fw and offs1.numel() == offs0.numel(), "offset shape"
+    if not coords_final:
+        ft0, ft1 = _lib.f32(ft0), _lib.f32(ft1)
+        assert ft0.stride() == ft1.stride(), "ft0 / ft1 must share strides"
+        ft_strides = _lib.strides4(ft0)
+    else:
+        ft_strides = None
+    out = torch.empty((b, c, fh, fw), dtype=torch.float32, device=dev)
+    s0 = s1 = None
+    if want_scores:
+        s0 = torch.empty((b * n_heads, n_samples, fh * fw), dtype=torch.float32, device=dev)
+        s1 = torch.empty_like(s0)
+    _lib.call("vfi_dattn_f32", dev, q.data_ptr(), feat0.data_ptr(), feat1.data_ptr(), offs0.data_ptr(), offs1.data_ptr(),
+                                        _lib.ptr(ft0) if not coords_final else None, _lib.ptr(ft1) if not coords_final else None,
+                                        ft_strides, _w2d(wq).data_ptr(), _lib.f32c(bq).data_ptr(), _w2d(wk).data_ptr(),
+                                        _lib.f32c(bk).data_ptr(), _w2d(wv).data_ptr(), _lib.f32c(bv).data_ptr(),
+                                        _lib.linspace_m11(fw, dev).data_ptr(), _lib.linspace_m11(fh, dev).data_ptr(),
+                                        out.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), b, c, fh, fw, n_groups, n_samples, n_heads,
+                                        float(offset_scale), 1 if coords_final else 0, _lib.stream_ptr(dev))
+    return (out, s0, s1) if want_scores else out
+
+
+class Attn(nn.Module):
+    def __init__(self, in_c, out_c, n_samples, n_heads):
+        super().__init__()
+        assert in_c == out_c, "the fused projections assume in_c == out_c (true for every reference block)"
+        self.in_c, self.out_c = in_c, out_c
+        self.q_proj = nn.Conv2d(in_c, out_c, 1, 1, 0)
+        self.k_proj = nn.Conv2d(in_c, out_c, 1, 1, 0)
+        self.v_proj = nn.Conv2d(in_c, out_c, 1, 1, 0)
+        self.n_samples = n_samples
+        self.n_head = n_heads
+        self.n_head_c = out_c // n_heads
+        self.scale = self.n_head_c ** -0.5
+
+    def _weights(self):
+        return (self.q_proj.weight, self.q_proj.bias, self.k_proj.weight, self.k_proj.bias, self.v_proj.weight,
+                self.v_proj.bias)
+
+    def forward(self, q, kv):
+        """q: b, c, fh, fw;  kv: b, c, nS, fh*fw  ->  b, out_c, fh, fw"""
+        return attention_over_samples(q, kv, *self._weights(), n_heads=self.n_head)
+
+
+class CrossDeformableAttentionBlockwFlow(nn.Module):
+    def __init__(self, in_c, out_c, n_samples=9, n_groups=12, n_heads=12, mlp_ratio=2.0, offset_scale=2.0,
+                 pred_res_flow=True):
+        super().__init__()
+        self.in_c, self.out_c = in_c, out_c
+        self.n_groups, self.n_group_c = n_groups, in_c // n_groups
+        self.n_heads, self.n_samples = n_heads, n_samples
+        self.offset_scale, self.pred_res_flow = offset_scale, pred_res_flow
+        self.movement_extractor = nn.Sequential(conv_prelu(in_c * 2 + 2, in_c * 2), conv_prelu(in_c * 2, in_c),
+                                                HalfChannelConv5ResBlock(in_c, in_c // 2))
+        self.conv_res_offset = nn.Conv2d(in_c, n_groups * n_samples * 2, 3, 1, 1)
+        nn.init.zeros_(self.conv_res_offset.weight)       # modules/deformable_attn.py:64
+        nn.init.zeros_(self.conv_res_offset.bias)
+        if pred_res_flow:
+            self.conv_res_flow = nn.ConvTranspose2d(in_c, 2, 4, 2, 1, bias=True)
+        self.attn = Attn(in_c, out_c, n_samples * 2, n_heads)
+        self.mlp = FeadForward(in_dim=out_c, hidden_dim=out_c * mlp_ratio, out_dim=out_c)
+
+    # -- piecewise API of the reference ---------------------------------------------------------
+    def _get_movement_feats(self, feat_t, feat_x, ftx):
+        return self.movement_extractor(torch.cat((feat_t, bwarp(feat_x, ftx), ftx), dim=1))
+
+    def _get_ref_coords(self, feat_t, ftx, movement_feat):
+        b, c, fh, fw = feat_t.shape
+        res = self.offset_scale * torch.tanh(self.conv_res_offset(movement_feat))
+        return res.view(b, self.n_groups * self.n_samples, 2, fh, fw) + ftx.unsqueeze(1)
+
+    def _get_ref_feats(self, feat, flow):
+        return grouped_sample(feat, flow, self.n_groups, self.n_samples)        # b, c, nS, fh*fw
+
+    # -- fused forward ------------------------------------------------------------------------------
+    def forward(self, feat_t, feat0, feat1, ft0, ft1):
+        mv0 = self._get_movement_feats(feat_t, feat0, ft0)
+        mv1 = self._get_movement_feats(feat_t, feat1, ft1)
+        raw0, raw1 = self.conv_res_offset(mv0), self.conv_res_offset(mv1)
+        if self.n_groups == self.n_heads:
+            attended = fused_deformable_attention(feat_t, feat0, feat1, raw0, raw1, ft0, ft1, *self.attn._weights(),
+                                                  n_groups=self.n_groups, n_samples=self.n_samples, n_heads=self.n_heads,
+                                                  offset_scale=self.offset_scale)
+        else:   # groups != heads: materialising kernels (still CUDA, never a CPU path)
+            b, _, fh, fw = feat_t.shape
+            shp = (b, self.n_groups * self.n_samples, 2, fh, fw)
+            c0 = (self.offset_scale * torch.tanh(raw0)).view(shp) + ft0.unsqueeze(1)
+            c1 = (self.offset_scale * torch.tanh(raw1)).view(shp) + ft1.unsqueeze(1)
+            kv = torch.cat((self._get_ref_feats(feat0, c0), self._get_ref_feats(feat1, c1)), dim=2)
+            attended = self.attn(feat_t, kv)
+        out = attended + self.mlp(attended)
+        if not self.pred_res_flow:
+            return out
+        up_ft0 = self.conv_res_flow(mv0) + 2.0 * resize(ft0, scale_factor=2.0)
+        up_ft1 = self.conv_res_flow(mv1) + 2.0 * resize(ft1, scale_factor=2.0)
+        return out, up_ft0, up_ft1

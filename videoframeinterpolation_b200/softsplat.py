@@ -1,0 +1,99 @@
+"""Drop-in for the reference's ``modules/softsplat.py`` (forward): ``softsplat`` and ``softsplat_func``.
+
+    softsplat(tenIn, tenFlow, tenMetric, strMode)          modules/softsplat.py:237-279
+    softsplat_func.apply(tenIn, tenFlow)                   modules/softsplat.py:282-360 (forward)
+
+The reference JIT-compiles one NVRTC kernel per tensor shape and wraps it in cat / exp / multiply /
+zero-fill / slice / divide passes; here one C-ABI call does pre-scale + splat (csrc/splat.cu) and one
+does the divide -- or a single fused call (csrc/splat_fused.cu) when the flow statistics allow it.
+Backward (modules/softsplat.py:364-533) is not built yet: tensors that require grad raise.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+__all__ = ["softsplat", "softsplat_func", "splat_accumulate", "splat_normalize"]
+
+_WEIGHT_MODES = {"none": 0, "ones": 1, "linear": 2, "soft": 3, "soft_clip_t": 4}
+_EPS_MODES = {"add": 0, "zero": 1, "clip": 2}
+
+
+def splat_accumulate(tenIn, tenFlow, tenMetric, t, num, den, weight: str, accumulate: bool) -> None:
+    """num (+)= splat(tenIn * w), den (+)= splat(w) with w chosen by ``weight`` (vfi_splat_f32)."""
+    dev = _lib.require_cuda(tenIn, tenFlow, tenMetric, num, den)
+    tenIn, tenFlow, tenMetric, t = _lib.f32c(tenIn), _lib.f32c(tenFlow), _lib.f32c(tenMetric), _lib.f32c(t)
+    B, C, H, W = tenIn.shape
+    assert tuple(tenFlow.shape) == (B, 2, H, W), "flow must be (B,2,H,W)"
+    assert tenMetric is None or tuple(tenMetric.shape) == (B, 1, H, W), "metric must be (B,1,H,W)"
+    assert num.is_contiguous() and (den is None or den.is_contiguous())
+    _lib.call("vfi_splat_f32", dev, tenIn.data_ptr(), tenFlow.data_ptr(), _lib.ptr(tenMetric), _lib.ptr(t),
+                                        num.data_ptr(), _lib.ptr(den), B, C, H, W, _WEIGHT_MODES[weight],
+                                        1 if accumulate else 0, None, 0, _lib.stream_ptr(dev))
+
+
+def splat_normalize(num, den, eps_mode: str, eps_value: float, want_mask: bool = False,
+                    blank_threshold: float = 0.0):
+    """out = num / f(den) in place of ``num`` (vfi_splat_normalize_f32); optionally the blank-pixel mask."""
+    dev = _lib.require_cuda(num, den)
+    B, C, H, W = num.shape
+    mask = torch.empty((B, 1, H, W), dtype=torch.uint8, device=dev) if want_mask else None
+    _lib.call("vfi_splat_normalize_f32", dev, num.data_ptr(), den.data_ptr(), num.data_ptr(), _lib.ptr(mask), B, C, H, W,
+                                                  _EPS_MODES[eps_mode], eps_value, blank_threshold,
+                                                  _lib.stream_ptr(dev))
+    if want_mask:
+        return num, mask.view(torch.bool)
+    return num
+
+
+def _check_mode(tenMetric, strMode: str) -> Tuple[str, Optional[str]]:
+    # same assertions as the reference (modules/softsplat.py:238-243)
+    parts = strMode.split('-')
+    assert(parts[0] in ['sum', 'avg', 'linear', 'soft'])
+    if strMode == 'sum': assert(tenMetric is None)
+    if strMode == 'avg': assert(tenMetric is None)
+    if parts[0] == 'linear': assert(tenMetric is not None)
+    if parts[0] == 'soft': assert(tenMetric is not None)
+    return parts[0], (parts[1] if len(parts) > 1 else None)
+
+
+def softsplat(tenIn: torch.Tensor, tenFlow: torch.Tensor, tenMetric: torch.Tensor, strMode: str):
+    """Forward splatting: 'sum' | 'avg' | 'linear[-eps]' | 'soft[-eps]', eps in addeps / zeroeps / clipeps."""
+    head, eps = _check_mode(tenMetric, strMode)
+    dev = _lib.require_cuda(tenIn, tenFlow, tenMetric)
+    if tenIn.requires_grad or tenFlow.requires_grad or (tenMetric is not None and tenMetric.requires_grad):
+        if torch.is_grad_enabled():
+            raise _lib.VfiError("vfi_b200 softsplat: backward is not built yet; call under torch.no_grad()")
+    B, C, H, W = tenIn.shape
+    num = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+    if head == 'sum':
+        splat_accumulate(tenIn, tenFlow, None, None, num, None, "none", accumulate=False)
+        return num
+    den = torch.empty((B, 1, H, W), dtype=torch.float32, device=dev)
+    weight = {"avg": "ones", "linear": "linear", "soft": "soft"}[head]
+    splat_accumulate(tenIn, tenFlow, tenMetric, None, num, den, weight, accumulate=False)
+    if eps is None or eps == 'addeps':
+        return splat_normalize(num, den, "add", 0.0000001)
+    if eps == 'zeroeps':
+        return splat_normalize(num, den, "zero", 0.0)
+    if eps == 'clipeps':
+        return splat_normalize(num, den, "clip", 0.0000001)
+    # the reference leaves tenNormalize un-adjusted for an unknown suffix (modules/softsplat.py:262-274)
+    return splat_normalize(num, den, "add", 0.0)
+
+
+class softsplat_func:
+    """``softsplat_func.apply(tenIn, tenFlow)``: raw summation splat of every channel (forward only)."""
+
+    @staticmethod
+    def apply(tenIn: torch.Tensor, tenFlow: torch.Tensor) -> torch.Tensor:
+        dev = _lib.require_cuda(tenIn, tenFlow)          # CPU tensors: the reference asserts False (352-353)
+        B, C, H, W = tenIn.shape
+        num = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+        splat_accumulate(tenIn, tenFlow, None, None, num, None, "none", accumulate=False)
+        return num
+
+    forward = apply

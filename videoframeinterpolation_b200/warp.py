@@ -1,0 +1,80 @@
+"""Drop-in for the reference's ``modules/warp.py``: same names, argument order and return types.
+
+    bwarp(img, flow)                                                       modules/warp.py:7-15
+    fwarp(tenIn, tenFlow, tenMetric, strMode='soft')                       modules/warp.py:18-59
+    fwarp_using_two_frames(in1, flow1, t1, in2, flow2, t2, m1, m2)         modules/warp.py:68-83
+    fwarp_mframes(in1, flow1, t1, in2, flow2, t2, m1, m2)                  modules/warp.py:86-114
+
+All arithmetic runs in libvfi_b200.so (csrc/bwarp.cu, csrc/splat.cu, csrc/splat_fused.cu).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from .softsplat import softsplat, splat_accumulate, splat_normalize
+
+__all__ = ["bwarp", "fwarp", "fwarp_using_two_frames", "fwarp_mframes"]
+
+
+def bwarp(img: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
+    """Backward bilinear warp, border clamp.  img (B,C,H,W), flow (B,2,H,W) [ch0 = dx, ch1 = dy, pixels].
+
+    NCHW-contiguous and channels-last inputs both run vectorised kernels; the output has the input's
+    memory format.  Flow may be a non-contiguous channel slice (e.g. ``pred_scale_3[:, nf:nf+2]``,
+    models/DAT.py:82): strides are passed through, nothing is copied.
+    """
+    dev = _lib.require_cuda(img, flow)
+    B, _, H, W = flow.shape
+    assert img.shape[0] == B and tuple(img.shape[2:]) == (H, W), "img / flow shape mismatch"
+    img, flow = _lib.f32(img), _lib.f32(flow)
+    C = img.shape[1]
+    if img.stride(1) == 1 and C > 1:
+        out = torch.empty_like(img, memory_format=torch.channels_last)
+    else:
+        out = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+    _lib.call("vfi_bwarp_f32", dev, img.data_ptr(), flow.data_ptr(), _lib.linspace_m11(W, dev).data_ptr(),
+                                        _lib.linspace_m11(H, dev).data_ptr(), out.data_ptr(), B, C, H, W,
+                                        _lib.strides4(img), _lib.strides4(flow), _lib.strides4(out),
+                                        _lib.stream_ptr(dev))
+    return out
+
+
+def fwarp(tenIn: torch.Tensor, tenFlow: torch.Tensor, tenMetric: torch.Tensor, strMode: str = 'soft'):
+    """Forward splatting front-end -- identical contract to ``softsplat`` (the reference keeps two copies)."""
+    return softsplat(tenIn, tenFlow, tenMetric, strMode)
+
+
+def _two_directions(num, den, tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2, first: bool):
+    B = tenIn1.shape[0]
+    splat_accumulate(tenIn1, tenFlow1, tenMetric1, t1.reshape(B), num, den, "soft_clip_t", accumulate=not first)
+    splat_accumulate(tenIn2, tenFlow2, tenMetric2, t2.reshape(B), num, den, "soft_clip_t", accumulate=True)
+
+
+def fwarp_using_two_frames(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1=None, tenMetric2=None):
+    """Two-direction soft splat blended by t; returns (num / den, den < 1e-5).
+
+    Both directions accumulate into ONE numerator / denominator pair (2 kernel launches instead of the
+    reference's 2 splats + ~10 elementwise passes); the two +1e-7 terms of modules/warp.py:73 become
+    one +2e-7 in the divide.
+    """
+    assert tenMetric1 is not None and tenMetric2 is not None, "fwarp_using_two_frames needs both metrics"
+    dev = _lib.require_cuda(tenIn1, tenFlow1, tenIn2, tenFlow2, tenMetric1, tenMetric2)
+    B, C, H, W = tenIn1.shape
+    num = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+    den = torch.empty((B, 1, H, W), dtype=torch.float32, device=dev)
+    _two_directions(num, den, tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2, first=True)
+    return splat_normalize(num, den, "add", 2 * 0.0000001, want_mask=True, blank_threshold=0.00001)
+
+
+def fwarp_mframes(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2):
+    """Many-to-many splatting: flows (n_branch,B,2,H,W), t (n_branch,B,1,1,1); inputs shared by branches."""
+    dev = _lib.require_cuda(tenIn1, tenFlow1, tenIn2, tenFlow2, tenMetric1, tenMetric2)
+    n_branch = tenFlow1.shape[0]
+    B, C, H, W = tenIn1.shape
+    num = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+    den = torch.empty((B, 1, H, W), dtype=torch.float32, device=dev)
+    for idx in range(n_branch):
+        _two_directions(num, den, tenIn1, tenFlow1[idx], t1[idx], tenIn2, tenFlow2[idx], t2[idx], tenMetric1, tenMetric2,
+                        first=idx == 0)
+    return splat_normalize(num, den, "add", 2 * n_branch * 0.0000001, want_mask=True, blank_threshold=0.00001)
