@@ -58,7 +58,10 @@ def test_bwarp_identity_and_idempotence_1080p(vfi):
     """Size-independent properties at BASELINE size: zero flow is the identity; integer shifts commute with slicing."""
     img = torch.rand(1, 16, 1080, 1920, device="cuda")
     zero = torch.zeros(1, 2, 1080, 1920, device="cuda")
-    assert rel_err(vfi.bwarp(img, zero), img) <= 2e-6
+    # NOT exactly the identity: the reference's fp32 normalise/unnormalise round trip moves coordinates by up to
+    # ~2e-4 px at this width (SURVEY.md H1); the kernel must reproduce that, so compare with the oracle below too
+    assert rel_err(vfi.bwarp(img, zero), img) <= 1e-3
+    assert_close(vfi.bwarp(img[:, :2], zero), oracle.bwarp(img[:, :2].cpu(), zero.cpu()), TOL, "bwarp zero flow 1080p vs oracle")
     shift = zero.clone()
     shift[:, 0] = 3.0
     shift[:, 1] = -2.0
