@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--width", type=int, default=W_RAW)
     ap.add_argument("--no-micro", action="store_true", help="skip the warp/splat micro-benchmark")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs under ncu only)")
     ap.add_argument("--tf32", type=int, default=1, help="allow TF32 in the cuDNN convs around the hot path (PyTorch default)")
     return ap.parse_args()
 
@@ -294,9 +295,12 @@ def run_vfi(args):
         clocks = clock.stop()
         ops = tm.summary()
         dattn_events = tm.records.get("vfi_dattn_f32", [])
-        for _ in range(2):
-            step_e2e()
-        e2e_ms = timed(step_e2e, args.steps)
+        if args.no_e2e:
+            e2e_ms = float("nan")
+        else:
+            for _ in range(2):
+                step_e2e()
+            e2e_ms = timed(step_e2e, args.steps)
 
     ms_per_step = total_ms / args.steps
     value = world * P / (ms_per_step / 1e3)
