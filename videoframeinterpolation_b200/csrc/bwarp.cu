@@ -7,6 +7,9 @@
 //     coalesced and the taps of neighbouring lanes share L1 lines when the flow is locally smooth;
 //   * channels-last (stride_c == 1): a thread owns 4 consecutive channels of one pixel, all taps and the
 //     store are 128-bit.
+#include <stdlib.h>
+
+#include "tma.cuh"
 #include "vfi_common.cuh"
 
 namespace vfi {
@@ -128,6 +131,216 @@ __global__ void __launch_bounds__(256) bwarp_cl_kernel(const float* __restrict__
     }
 }
 
+
+// ---- tile kernel (contiguous NCHW): source window staged in shared memory by TMA -------------------------
+// The direct-gather kernels above are bound by L1 wavefronts (4 unaligned 128 B tap requests per warp-output).
+// Here a CTA owns a 64x16 output tile; the source window of the tile -- the tile displaced by the median flow of
+// nine probe pixels, +-16 px in x and +-8 px in y -- is brought into shared memory one channel per pipeline
+// stage with a 3-D TMA box load (out-of-frame parts are zero-filled and never read: taps are border-clamped),
+// and the four taps become conflict-free LDS.  Pixels whose taps leave the window (flow outliers) fall back to
+// global loads, so the result never depends on the window choice.  Geometry is computed once per pixel and
+// reused for every channel.  Warps 0-7 consume, warp 8 is the TMA producer (full/empty mbarrier ring).
+#ifndef VFI_BWARP_HVX
+#define VFI_BWARP_HVX 16
+#endif
+#ifndef VFI_BWARP_HVY
+#define VFI_BWARP_HVY 8
+#endif
+constexpr int kTW = 64, kTH = 16, kHVX = VFI_BWARP_HVX, kHVY = VFI_BWARP_HVY;
+constexpr int kRW = kTW + 2 * kHVX, kRH = kTH + 2 * kHVY;   // 96 x 32 window
+constexpr int kStageFloats = kRW * kRH;
+constexpr int kStages = 6;
+constexpr int kTileThreads = 288;
+
+struct TilePix {
+    int o_s;        // window offset of the north-west tap
+    int o_g;        // frame offset of the north-west tap
+    int dxy;        // bit 0: x1 = x0 + 1, bit 1: y1 = y0 + 1, bit 2: taps inside the window, bit 3: pixel inside the frame
+    float w_nw, w_ne, w_sw, w_se;
+};
+
+__device__ __forceinline__ float median9(float* v) {
+    // tiny insertion sort (thread 0 only)
+    for (int i = 1; i < 9; ++i) {
+        const float k = v[i];
+        int j = i - 1;
+        while (j >= 0 && v[j] > k) {
+            v[j + 1] = v[j];
+            --j;
+        }
+        v[j + 1] = k;
+    }
+    return v[4];
+}
+
+__global__ void __launch_bounds__(kTileThreads) bwarp_tile_kernel(const __grid_constant__ CUtensorMap tmap,
+                                                                  const float* __restrict__ img, const float* __restrict__ flow,
+                                                                  const float* __restrict__ lin_x, const float* __restrict__ lin_y,
+                                                                  float* __restrict__ out, int C, int H, int W, Str4 sf,
+                                                                  int tiles_x, int tiles_y, int n_tiles_all, int c_chunk) {
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    uint8_t* smem_al = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);   // TMA destinations need 128 B alignment
+    float* stage = reinterpret_cast<float*>(smem_al);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_al + (size_t)kStages * kStageFloats * sizeof(float));
+    uint64_t* empty = full + kStages;
+    __shared__ float s_probe[18];
+    __shared__ int s_shift[2];
+    __shared__ int s_nout;
+    __shared__ unsigned short s_outlist[kTW * kTH];   // tile-local ids of pixels whose taps leave the window
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tiles_per_img = tiles_x * tiles_y;
+    // block order: all tiles of one channel chunk first, so that co-resident CTAs share windows in L2
+    const int chunk = blockIdx.x / n_tiles_all;
+    const int tile_id = blockIdx.x - chunk * n_tiles_all;
+    const int b = tile_id / tiles_per_img;
+    const int trem = tile_id - b * tiles_per_img;
+    const int ty = trem / tiles_x, tx = trem - ty * tiles_x;
+    const int x_t0 = tx * kTW, y_t0 = ty * kTH;
+    const int c_begin = chunk * c_chunk, c_end = min(C, c_begin + c_chunk), n_c = c_end - c_begin;
+
+    if (tid == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 8);
+        }
+        fence_mbar_init();
+    }
+    if (tid < 9) {   // 3x3 probe grid inside the tile
+        const int px = min(x_t0 + (kTW / 6) * (1 + 2 * (tid % 3)), W - 1);
+        const int py = min(y_t0 + (kTH / 6) * (1 + 2 * (tid / 3)), H - 1);
+        const float* fp = flow + b * sf.n + py * sf.h + px * sf.w;
+        const float fx = __ldg(fp), fy = __ldg(fp + sf.c);
+        s_probe[tid] = isfinite(fx) ? fx : 0.0f;
+        s_probe[9 + tid] = isfinite(fy) ? fy : 0.0f;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const float mx = median9(s_probe), my = median9(s_probe + 9);
+        s_shift[0] = (int)rintf(fminf(fmaxf(mx, -1.0e6f), 1.0e6f));
+        s_shift[1] = (int)rintf(fminf(fmaxf(my, -1.0e6f), 1.0e6f));
+        s_nout = 0;
+    }
+    __syncthreads();
+    // window origin, clamped so that it always overlaps the frame the taps are clamped to
+    // (TMA: the innermost box coordinate must be a multiple of 16 bytes -- other values fault; `& ~3` floors)
+    const int rx0 = min(max(x_t0 + s_shift[0] - kHVX, -kRW + 4), W - 1) & ~3;
+    const int ry0 = min(max(y_t0 + s_shift[1] - kHVY, -kRH + 1), H - 1);
+    const int64_t HW = (int64_t)H * W;
+
+    if (warp == 8) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmap);
+            for (int c = 0; c < n_c; ++c) {
+                const int s = c % kStages;
+                if (c >= kStages) mbar_wait(&empty[s], ((c / kStages) - 1) & 1);
+                mbar_arrive_expect_tx(&full[s], kStageFloats * sizeof(float));
+                tma_load_3d(stage + (size_t)s * kStageFloats, &tmap, &full[s], rx0, ry0, b * C + c_begin + c);
+            }
+        }
+        return;
+    }
+
+    // ---- consumers: geometry of my 4 pixels (x = lane, lane+32; y = warp, warp+8) ----
+    TilePix px[4];
+    const float half_w = (float)((W - 1.0) / 2.0), half_h = (float)((H - 1.0) / 2.0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int xr = x_t0 + lane + 32 * (k & 1), yr = y_t0 + warp + 8 * (k >> 1);
+        const bool valid = xr < W && yr < H;
+        const int x = min(xr, W - 1), y = min(yr, H - 1);
+        const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
+        const BwarpGeom g = bwarp_geom(ld_stream(fp), ld_stream(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, half_w, half_h);
+        const int lx0 = g.x0 - rx0, ly0 = g.y0 - ry0, lx1 = g.x1 - rx0, ly1 = g.y1 - ry0;
+        const bool inside = lx0 >= 0 && lx1 < kRW && ly0 >= 0 && ly1 < kRH;
+        if (valid && !inside) s_outlist[atomicAdd(&s_nout, 1)] = (unsigned short)((yr - y_t0) * kTW + (xr - x_t0));
+        px[k].o_s = ly0 * kRW + lx0;
+        px[k].o_g = g.y0 * W + g.x0;
+        px[k].dxy = (g.x1 - g.x0) | ((g.y1 - g.y0) << 1) | (inside ? 4 : 0) | (valid ? 8 : 0);
+        px[k].w_nw = g.w_nw;
+        px[k].w_ne = g.w_ne;
+        px[k].w_sw = g.w_sw;
+        px[k].w_se = g.w_se;
+    }
+
+    for (int c = 0; c < n_c; ++c) {
+        const int s = c % kStages;
+        mbar_wait(&full[s], (c / kStages) & 1);
+        const float* st = stage + (size_t)s * kStageFloats;
+        float* oplane = out + ((int64_t)b * C + c_begin + c) * HW;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if ((px[k].dxy & 12) == 12) {      // inside the frame, taps inside the window
+                const int dx = px[k].dxy & 1, dy = (px[k].dxy >> 1) & 1;
+                const float* p = st + px[k].o_s;
+                const float r = p[0] * px[k].w_nw + p[dx] * px[k].w_ne + p[dy * kRW] * px[k].w_sw + p[dy * kRW + dx] * px[k].w_se;
+                const int xr = x_t0 + lane + 32 * (k & 1), yr = y_t0 + warp + 8 * (k >> 1);
+                st_stream(oplane + (int64_t)yr * W + xr, r);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+    }
+
+    // ---- pixels whose taps left the window: direct gathers, all channels, after the streamed part ----
+    asm volatile("bar.sync 1, 256;" ::: "memory");   // consumers only (the producer warp is not part of it)
+    const int n_out = s_nout;
+    if (n_out == 0) return;
+    constexpr int kCh = 8;                             // channels per work item
+    const int n_chunks = (n_c + kCh - 1) / kCh;
+    for (int item = tid; item < n_out * n_chunks; item += 256) {
+        const int pid = s_outlist[item / n_chunks], c0 = c_begin + (item % n_chunks) * kCh;
+        const int x = x_t0 + pid % kTW, y = y_t0 + pid / kTW;
+        const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
+        const BwarpGeom g = bwarp_geom(__ldg(fp), __ldg(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, half_w, half_h);
+        const int o_nw = g.y0 * W + g.x0, o_ne = g.y0 * W + g.x1, o_sw = g.y1 * W + g.x0, o_se = g.y1 * W + g.x1;
+        const float* ip = img + ((int64_t)b * C + c0) * HW;
+        float* op = out + ((int64_t)b * C + c0) * HW + (int64_t)y * W + x;
+        const int cn = min(kCh, c_end - c0);
+        float v[kCh][4];
+#pragma unroll
+        for (int u = 0; u < kCh; ++u) {
+            if (u < cn) {
+                const float* p = ip + (int64_t)u * HW;
+                v[u][0] = ld_gather(p + o_nw);
+                v[u][1] = ld_gather(p + o_ne);
+                v[u][2] = ld_gather(p + o_sw);
+                v[u][3] = ld_gather(p + o_se);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kCh; ++u)
+            if (u < cn) st_stream(op + (int64_t)u * HW, v[u][0] * g.w_nw + v[u][1] * g.w_ne + v[u][2] * g.w_sw + v[u][3] * g.w_se);
+    }
+}
+
+struct TmapCacheEntry {
+    const void* base;
+    int BC, H, W;
+    CUtensorMap map;
+};
+
+static int get_img_tmap(const float* img, int BC, int H, int W, const CUtensorMap** out) {
+    static thread_local TmapCacheEntry cache[16];
+    static thread_local int next = 0;
+    for (int i = 0; i < 16; ++i)
+        if (cache[i].base == img && cache[i].BC == BC && cache[i].H == H && cache[i].W == W) {
+            *out = &cache[i].map;
+            return VFI_OK;
+        }
+    TmapCacheEntry& e = cache[next];
+    next = (next + 1) % 16;
+    e.base = nullptr;
+    int rc = make_tmap_f32_3d(&e.map, img, (uint64_t)W, (uint64_t)H, (uint64_t)BC, (uint64_t)W * 4, (uint64_t)H * W * 4, kRW, kRH, 1);
+    if (rc) return rc;
+    e.base = img;
+    e.BC = BC;
+    e.H = H;
+    e.W = W;
+    *out = &e.map;
+    return VFI_OK;
+}
+
 }  // namespace vfi
 
 extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* lin_x, const float* lin_y, float* out,
@@ -152,6 +365,27 @@ extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* l
         const int blocks = (int)min64(ceil_div(total, 256), (int64_t)kNumSMs * 32);
         bwarp_cl_kernel<<<blocks, 256, 0, st>>>(img, flow, lin_x, lin_y, out, B, C, H, W, si, sf, so);
         VFI_CHECK_LAUNCH("bwarp_cl_kernel");
+        return VFI_OK;
+    }
+    const bool nchw = si.w == 1 && si.h == W && si.c == (int64_t)H * W && si.n == (int64_t)C * H * W && so.w == 1 && so.h == W &&
+                      so.c == (int64_t)H * W && so.n == (int64_t)C * H * W;
+    const char* force = getenv("VFI_BWARP_ALGO");   // "gather" | "tile" (testing / profiling)
+    // measured on B200 (profiles/): the tile kernel ties the gather kernel on smooth flows and is 1.5x faster on
+    // rough ones once its per-CTA prologue is amortised over >= 8 channels
+    const bool want_tile = force ? force[0] == 't' : ((int64_t)H * W >= 64 * 1024 && C >= 8);
+    if (nchw && want_tile && W % 4 == 0 && aligned16(img) && (int64_t)B * C < (1ll << 31) && (int64_t)H * W < (1ll << 31)) {
+        const CUtensorMap* tm = nullptr;
+        int rc = get_img_tmap(img, B * C, H, W, &tm);
+        if (rc) return rc;
+        const int tiles_x = (int)ceil_div(W, kTW), tiles_y = (int)ceil_div(H, kTH);
+        const size_t smem = (size_t)kStages * kStageFloats * sizeof(float) + 2 * kStages * sizeof(uint64_t) + 128;
+        VFI_CUDA(cudaFuncSetAttribute(bwarp_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int c_chunk = 32;
+        if (const char* e = getenv("VFI_BWARP_CCHUNK")) c_chunk = atoi(e) > 0 ? atoi(e) : c_chunk;
+        const int n_tiles_all = tiles_x * tiles_y * B, n_cchunks = (int)ceil_div(C, c_chunk);
+        bwarp_tile_kernel<<<(unsigned)(n_tiles_all * n_cchunks), kTileThreads, smem, st>>>(*tm, img, flow, lin_x, lin_y, out, C, H, W, sf,
+                                                                                          tiles_x, tiles_y, n_tiles_all, c_chunk);
+        VFI_CHECK_LAUNCH("bwarp_tile_kernel");
         return VFI_OK;
     }
     // channel chunking: enough CTAs to fill the machine, flow re-read at most once per 16 channels

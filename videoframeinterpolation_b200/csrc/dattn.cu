@@ -7,12 +7,18 @@
 //   logit[h,s] = kt_h . x_s + cb_h ;  a = softmax_s(logit) ;  out_h = Wv_h (sum_s a[h,s] x_s) + bv_h
 // where x_s (C values) is slot s of the pixel: group g's channels sampled at group g's s-th point.
 //
-// Mapping: a TEAM of NG lanes owns one pixel; lane g of the team owns group g for sampling (its offsets,
-// its geometry, its GC channels of x_s) and head g for the softmax.  Per slot the lane forms the NG partial
-// dot products kt_h[block g] . x_s[block g]; a transposed butterfly over the team (NG-1 shuffles) leaves
-// head h's logit in lane h.  The softmax shift is lazy (re-based only when a logit exceeds the current
-// base by 30), so the common path per slot is 2*NG*GC FMAs + NG shuffles.  Requires nG == nH.
-// HBM traffic per pixel: q, feat0, feat1, out (4C floats) + 2*2*nG*nS offsets + 4 flow values.
+// Mapping (v2).  The kernel is bound by the L1/LSU gather rate (4 taps x C x 2nS loads per pixel), so the
+// mapping is chosen for the gathers: a WARP owns one group g for a tile of 32 adjacent pixels, i.e. the 32
+// lanes of every tap load read neighbouring addresses of ONE feature plane (1-3 cache lines per request
+// instead of the 8-10 of a lanes-across-groups mapping).  A CTA is NG warps = all groups of the same 32
+// pixels.  Warp g also owns head g of the softmax.  Per chunk of SC slots:
+//   A. every warp samples its group's GC channels for SC slots and forms the NG partial dot products
+//      kt_h[block g] . x_s[block g]                       -> red[si][h][g][lane]      (shared memory)
+//   C. warp h sums the NG partials of its head, updates the (lazily re-based) softmax state and
+//      publishes p[h][si], alpha[h]                       -> pbuf / abuf             (shared memory)
+//   D. every warp accumulates yv[h][cc] += p[h][si] * x[si][cc] for all heads.
+// Epilogue: po[h][j] = Wv[h*GC+j][block g] . yv[h], reduced over g through shared memory by warp h.
+// Requires nG == nH.  HBM traffic per pixel: q, feat0, feat1, out (4C floats) + 2*2*nG*nS offsets + 4 flow values.
 #include "sampler.cuh"
 
 namespace vfi {
@@ -25,59 +31,113 @@ struct DattnArgs {
     int B, H, W, nS;
     float offset_scale;
     int coords_final;
+    int tw_log2;              // tile = (1 << tw_log2) x (32 >> tw_log2) pixels per warp
+    int tiles_x, tiles_y;
 };
 
-constexpr int kDattnThreads = 128;
+constexpr int cmax(int a, int b) { return a > b ? a : b; }
+constexpr int cmin(int a, int b) { return a < b ? a : b; }
 
 template <int GC, int NG>
-__global__ void __launch_bounds__(kDattnThreads) dattn_kernel(DattnArgs a) {
-    constexpr int C = GC * NG;
-    constexpr int CP = C | 1;                      // odd row stride: team lanes hit distinct banks
-    constexpr int PPW = 32 / NG;                   // pixels per warp
-    constexpr int PPB = (kDattnThreads / 32) * PPW;
-    extern __shared__ float smem[];
-    float* Wq_s = smem;
-    float* Wk_s = Wq_s + C * CP;
-    float* Wv_s = Wk_s + C * CP;
-    for (int i = threadIdx.x; i < C * C; i += kDattnThreads) {
-        const int r = i / C, c = i - r * C;
-        Wq_s[r * CP + c] = __ldg(a.Wq + i);
-        Wk_s[r * CP + c] = __ldg(a.Wk + i);
-        Wv_s[r * CP + c] = __ldg(a.Wv + i);
-    }
-    __syncthreads();
+struct DattnCfg {
+    static constexpr int C = GC * NG;
+    static constexpr int C4 = (C + 3) & ~3;       // Wq row stride (16 B aligned rows: broadcast LDS.128)
+    static constexpr int GCP = (GC + 3) & ~3;     // padded channel block
+    static constexpr int SC = GC > 12 ? 2 : 4;    // slots per chunk (register budget: xs[SC][GC])
+    static constexpr int THREADS = NG * 32;
+    static constexpr int WQ = C * C4;
+    static constexpr int WT = NG * C * GCP;       // Wk / Wv re-blocked [g][row][GCP]
+    static constexpr int RED = SC * NG * NG * 32;
+    static constexpr int EPI_CAP = 10240;         // floats (40 KB) for one epilogue round
+    static constexpr int EPI_H_RAW = cmax(1, cmin(NG, EPI_CAP / (GC * NG * 32)));
+    static constexpr int EPI_H = EPI_H_RAW >= 8 ? 8 : (EPI_H_RAW >= 4 ? 4 : (EPI_H_RAW >= 2 ? 2 : 1));
+    static constexpr int EPI = EPI_H * GC * NG * 32;
+    static constexpr int UNI = cmax(cmax(RED, 2 * C * 32), EPI);
+    static constexpr int PB = NG * SC * 32;
+    static constexpr int AB = NG * 32;
+    static constexpr int SMEM_FLOATS = WQ + 2 * WT + UNI + PB + AB;
+    static constexpr int MIN_BLOCKS = NG <= 4 ? 2 : 1;
+};
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int g = lane % NG, team = lane / NG, team_base = team * NG;
-    const int64_t HW = (int64_t)a.H * a.W, total = (int64_t)a.B * HW;
+template <int GC, int NG>
+__global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::MIN_BLOCKS) dattn_kernel(DattnArgs a) {
+    using Cfg = DattnCfg<GC, NG>;
+    constexpr int C = Cfg::C, C4 = Cfg::C4, GCP = Cfg::GCP, SC = Cfg::SC, T = Cfg::THREADS;
+    extern __shared__ __align__(16) float smem[];
+    float* Wq_s = smem;                       // [C][C4]
+    float* WkT_s = Wq_s + Cfg::WQ;            // [g][r][GCP] = Wk[r][g*GC + cc]
+    float* WvT_s = WkT_s + Cfg::WT;           // [g][r][GCP] = Wv[r][g*GC + cc]
+    float* uni = WvT_s + Cfg::WT;             // q_s/qp_s | red | epilogue exchange
+    float* pbuf = uni + Cfg::UNI;             // [h][si][lane]
+    float* abuf = pbuf + Cfg::PB;             // [h][lane]
+
+    for (int i = threadIdx.x; i < C * C4; i += T) {
+        const int r = i / C4, c = i - r * C4;
+        Wq_s[i] = c < C ? __ldg(a.Wq + r * C + c) : 0.0f;
+    }
+    for (int i = threadIdx.x; i < NG * C * GCP; i += T) {
+        const int cc = i % GCP, r = (i / GCP) % C, g = i / (GCP * C);
+        const bool ok = cc < GC;
+        WkT_s[i] = ok ? __ldg(a.Wk + r * C + g * GC + cc) : 0.0f;
+        WvT_s[i] = ok ? __ldg(a.Wv + r * C + g * GC + cc) : 0.0f;
+    }
+
+    const int lane = threadIdx.x & 31;
+    const int g = threadIdx.x >> 5;            // my group == my head
+    const int64_t HW = (int64_t)a.H * a.W;
     const float scale = rsqrtf((float)GC);
     const int nS = a.nS;
+    const int lx = lane & ((1 << a.tw_log2) - 1), ly = lane >> a.tw_log2;
+    const int tiles_per_img = a.tiles_x * a.tiles_y;
+    const int64_t n_tiles = (int64_t)a.B * tiles_per_img;
+    float* q_s = uni;                // [C][32]
+    float* qp_s = uni + C * 32;      // [C][32]
 
-    for (int64_t tile = (int64_t)blockIdx.x * PPB; tile < total; tile += (int64_t)gridDim.x * PPB) {
-        const int64_t gp_raw = tile + warp * PPW + team;
-        const bool live = gp_raw < total;
-        const int64_t gp = live ? gp_raw : total - 1;
-        const int b = (int)(gp / HW);
-        const int64_t pix = gp - (int64_t)b * HW;
-        const int y = (int)(pix / a.W), x = (int)(pix - (int64_t)y * a.W);
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int b = (int)(tile / tiles_per_img);
+        const int trem = (int)(tile - (int64_t)b * tiles_per_img);
+        const int ty = trem / a.tiles_x, tx = trem - ty * a.tiles_x;
+        const int x_raw = (tx << a.tw_log2) + lx, y_raw = ty * (32 >> a.tw_log2) + ly;
+        const bool live = x_raw < a.W && y_raw < a.H;
+        const int x = min(x_raw, a.W - 1), y = min(y_raw, a.H - 1);
+        const int64_t pix = (int64_t)y * a.W + x;
 
-        // ---- prologue: qp (my head), kt (all heads x my channel block), cb (my head) ----
-        float qp[GC];
-#pragma unroll
-        for (int j = 0; j < GC; ++j) qp[j] = __ldg(a.bq + g * GC + j);
+        __syncthreads();   // weights staged (first tile) / previous tile's epilogue reads done
+        // ---- prologue ----
         {
-            const float* qpix = a.q + (int64_t)b * C * HW + pix;
-#pragma unroll 4
-            for (int c = 0; c < C; ++c) {
-                const float qv = __ldg(qpix + (int64_t)c * HW);
+            const float* qpix = a.q + ((int64_t)b * C + g * GC) * HW + pix;
 #pragma unroll
-                for (int j = 0; j < GC; ++j) qp[j] = fmaf(Wq_s[(g * GC + j) * CP + c], qv, qp[j]);
-            }
+            for (int j = 0; j < GC; ++j) q_s[(g * GC + j) * 32 + lane] = __ldg(qpix + (int64_t)j * HW);
         }
-        float cb = 0.0f;
+        __syncthreads();
+        float cb;
+        {
+            float qp[GC];
 #pragma unroll
-        for (int j = 0; j < GC; ++j) cb = fmaf(qp[j], __ldg(a.bk + g * GC + j), cb);
-        cb *= scale;
+            for (int j = 0; j < GC; ++j) qp[j] = __ldg(a.bq + g * GC + j);
+#pragma unroll 2
+            for (int c4 = 0; c4 < C4; c4 += 4) {
+                float qv[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) qv[k] = (c4 + k < C) ? q_s[(c4 + k) * 32 + lane] : 0.0f;
+#pragma unroll
+                for (int j = 0; j < GC; ++j) {
+                    const float4 w = *reinterpret_cast<const float4*>(Wq_s + (g * GC + j) * C4 + c4);
+                    qp[j] = fmaf(w.x, qv[0], qp[j]);
+                    if (c4 + 1 < C) qp[j] = fmaf(w.y, qv[1], qp[j]);
+                    if (c4 + 2 < C) qp[j] = fmaf(w.z, qv[2], qp[j]);
+                    if (c4 + 3 < C) qp[j] = fmaf(w.w, qv[3], qp[j]);
+                }
+            }
+            cb = 0.0f;
+#pragma unroll
+            for (int j = 0; j < GC; ++j) {
+                cb = fmaf(qp[j], __ldg(a.bk + g * GC + j), cb);
+                qp_s[(g * GC + j) * 32 + lane] = qp[j] * scale;
+            }
+            cb *= scale;
+        }
+        __syncthreads();
         float kt[NG][GC];
 #pragma unroll
         for (int h = 0; h < NG; ++h) {
@@ -85,12 +145,19 @@ __global__ void __launch_bounds__(kDattnThreads) dattn_kernel(DattnArgs a) {
             for (int cc = 0; cc < GC; ++cc) kt[h][cc] = 0.0f;
 #pragma unroll
             for (int j = 0; j < GC; ++j) {
-                const float qh = __shfl_sync(0xffffffffu, qp[j], team_base + h) * scale;
-                const float* wr = Wk_s + (h * GC + j) * CP + g * GC;
+                const float qh = qp_s[(h * GC + j) * 32 + lane];
+                const float* wr = WkT_s + (g * C + h * GC + j) * GCP;
 #pragma unroll
-                for (int cc = 0; cc < GC; ++cc) kt[h][cc] = fmaf(qh, wr[cc], kt[h][cc]);
+                for (int c4 = 0; c4 < GCP; c4 += 4) {
+                    const float4 w = *reinterpret_cast<const float4*>(wr + c4);
+                    kt[h][c4] = fmaf(qh, w.x, kt[h][c4]);
+                    if (c4 + 1 < GC) kt[h][c4 + 1] = fmaf(qh, w.y, kt[h][c4 + 1]);
+                    if (c4 + 2 < GC) kt[h][c4 + 2] = fmaf(qh, w.z, kt[h][c4 + 2]);
+                    if (c4 + 3 < GC) kt[h][c4 + 3] = fmaf(qh, w.w, kt[h][c4 + 3]);
+                }
             }
         }
+        __syncthreads();   // q_s / qp_s (aliased with red) fully consumed
 
         float yv[NG][GC];
 #pragma unroll
@@ -98,7 +165,8 @@ __global__ void __launch_bounds__(kDattnThreads) dattn_kernel(DattnArgs a) {
 #pragma unroll
             for (int cc = 0; cc < GC; ++cc) yv[h][cc] = 0.0f;
         float m_ref = -INFINITY, sum = 0.0f;
-        const float lx = __ldg(a.lin_x + x), ly = __ldg(a.lin_y + y);
+        const float lxv = __ldg(a.lin_x + x), lyv = __ldg(a.lin_y + y);
+        float* red = uni;   // [si][h][g][lane]
 
         for (int f = 0; f < 2; ++f) {
             float ftx = 0.0f, fty = 0.0f;
@@ -109,96 +177,121 @@ __global__ void __launch_bounds__(kDattnThreads) dattn_kernel(DattnArgs a) {
             }
             const float* offp = a.offs[f] + ((int64_t)b * NG * nS + (int64_t)g * nS) * 2 * HW + pix;
             const float* featp = a.feat[f] + ((int64_t)b * C + g * GC) * HW;
-            for (int s = 0; s < nS; ++s) {
-                float dx = ld_stream(offp + (int64_t)(2 * s) * HW);
-                float dy = ld_stream(offp + (int64_t)(2 * s + 1) * HW);
-                if (!a.coords_final) {
-                    dx = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dx)), ftx);
-                    dy = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dy)), fty);
+            for (int s0 = 0; s0 < nS; s0 += SC) {
+                float xs[SC][GC];
+                // ---- A: sample + partial logits ----
+                float odx[SC], ody[SC];
+#pragma unroll
+                for (int si = 0; si < SC; ++si) {
+                    const int s = min(s0 + si, nS - 1);
+                    odx[si] = ld_stream(offp + (int64_t)(2 * s) * HW);
+                    ody[si] = ld_stream(offp + (int64_t)(2 * s + 1) * HW);
                 }
-                const TapGeom tg = sampler_geom(dx, dy, lx, ly, a.H, a.W);
-                float xs[GC];
 #pragma unroll
-                for (int cc = 0; cc < GC; ++cc) xs[cc] = sample_plane(featp + (int64_t)cc * HW, tg, a.W);
-                float part[NG];
-#pragma unroll
-                for (int h = 0; h < NG; ++h) {
-                    float d = 0.0f;
-#pragma unroll
-                    for (int cc = 0; cc < GC; ++cc) d = fmaf(kt[h][cc], xs[cc], d);
-                    part[h] = d;
-                }
-                // transposed butterfly: afterwards part[0] of lane g is the full dot product of head g
-#pragma unroll
-                for (int off = NG / 2; off >= 1; off >>= 1) {
-                    const bool upper = (g & off) != 0;
-#pragma unroll
-                    for (int i = 0; i < off; ++i) {
-                        const float send = upper ? part[i] : part[i + off];
-                        const float keep = upper ? part[i + off] : part[i];
-                        part[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+                for (int si = 0; si < SC; ++si) {
+                    float dx = odx[si], dy = ody[si];
+                    if (!a.coords_final) {
+                        dx = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dx)), ftx);
+                        dy = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dy)), fty);
                     }
-                }
-                const float l = part[0] + cb;
-                if (a.score[f] != nullptr && live)
-                    a.score[f][(((int64_t)b * NG + g) * nS + s) * HW + pix] = l;
-                const float d = l - m_ref;
-                const bool need = d > 30.0f;
-                if (__any_sync(0xffffffffu, need)) {       // re-base the softmax shift (rare)
-                    const float alpha = need ? expf(-d) : 1.0f;
-                    if (need) {
-                        m_ref = l;
-                        sum *= alpha;
-                    }
+                    const TapGeom tg = sampler_geom(dx, dy, lxv, lyv, a.H, a.W);
+#pragma unroll
+                    for (int cc = 0; cc < GC; ++cc) xs[si][cc] = sample_plane(featp + (int64_t)cc * HW, tg, a.W);
 #pragma unroll
                     for (int h = 0; h < NG; ++h) {
-                        const float ah = __shfl_sync(0xffffffffu, alpha, team_base + h);
+                        float d = 0.0f;
 #pragma unroll
-                        for (int cc = 0; cc < GC; ++cc) yv[h][cc] *= ah;
+                        for (int cc = 0; cc < GC; ++cc) d = fmaf(kt[h][cc], xs[si][cc], d);
+                        red[((si * NG + h) * NG + g) * 32 + lane] = d;
                     }
                 }
-                const float p = expf(l - m_ref);
-                sum += p;
+                __syncthreads();
+                // ---- C: head g: logits of this chunk, softmax state ----
+                {
+                    float l[SC];
+                    float lmax = -INFINITY;
+#pragma unroll
+                    for (int si = 0; si < SC; ++si) {
+                        float acc = red[((si * NG + g) * NG + 0) * 32 + lane];
+#pragma unroll
+                        for (int gg = 1; gg < NG; ++gg) acc += red[((si * NG + g) * NG + gg) * 32 + lane];
+                        l[si] = acc + cb;
+                        const bool valid = s0 + si < nS;
+                        if (valid) {
+                            lmax = fmaxf(lmax, l[si]);
+                            if (a.score[f] != nullptr && live)
+                                a.score[f][(((int64_t)b * NG + g) * nS + (s0 + si)) * HW + pix] = l[si];
+                        }
+                    }
+                    float alpha = 1.0f;
+                    if (lmax - m_ref > 30.0f) {          // lazy re-base of the softmax shift (first chunk: m_ref = -inf)
+                        alpha = expf(m_ref - lmax);       // exp(-inf) = 0 on the first chunk
+                        m_ref = lmax;
+                        sum *= alpha;
+                    }
+                    abuf[g * 32 + lane] = alpha;
+#pragma unroll
+                    for (int si = 0; si < SC; ++si) {
+                        const float p = (s0 + si < nS) ? expf(l[si] - m_ref) : 0.0f;
+                        sum += p;
+                        pbuf[(g * SC + si) * 32 + lane] = p;
+                    }
+                }
+                __syncthreads();
+                // ---- D: weighted accumulation for all heads ----
 #pragma unroll
                 for (int h = 0; h < NG; ++h) {
-                    const float ph = __shfl_sync(0xffffffffu, p, team_base + h);
+                    const float al = abuf[h * 32 + lane];
+                    if (al != 1.0f) {
 #pragma unroll
-                    for (int cc = 0; cc < GC; ++cc) yv[h][cc] = fmaf(ph, xs[cc], yv[h][cc]);
+                        for (int cc = 0; cc < GC; ++cc) yv[h][cc] *= al;
+                    }
+#pragma unroll
+                    for (int si = 0; si < SC; ++si) {
+                        const float ph = pbuf[(h * SC + si) * 32 + lane];
+#pragma unroll
+                        for (int cc = 0; cc < GC; ++cc) yv[h][cc] = fmaf(ph, xs[si][cc], yv[h][cc]);
+                    }
                 }
             }
         }
 
-        // ---- epilogue: out_h = Wv_h y_h / sum_h + bv_h, reduced over the team's channel blocks ----
-        // reuse kt as the partial-output array: po[h][j] = sum_cc Wv[h*GC+j][g*GC+cc] * yv[h][cc]
+        // ---- epilogue: out_h = Wv_h y_h / sum_h + bv_h; y_h is spread over the NG warps ----
+        const float inv = 1.0f / sum;
+        float* epi = uni;   // [hh][j][g][lane]
 #pragma unroll
-        for (int h = 0; h < NG; ++h) {
+        for (int r = 0; r < NG / Cfg::EPI_H; ++r) {
+            __syncthreads();   // red / previous round fully read
 #pragma unroll
-            for (int j = 0; j < GC; ++j) {
-                const float* wr = Wv_s + (h * GC + j) * CP + g * GC;
-                float d = 0.0f;
-#pragma unroll
-                for (int cc = 0; cc < GC; ++cc) d = fmaf(wr[cc], yv[h][cc], d);
-                kt[h][j] = d;
-            }
-        }
-#pragma unroll
-        for (int off = NG / 2; off >= 1; off >>= 1) {
-            const bool upper = (g & off) != 0;
-#pragma unroll
-            for (int i = 0; i < off; ++i) {
+            for (int hh = 0; hh < Cfg::EPI_H; ++hh) {
+                const int h = r * Cfg::EPI_H + hh;
 #pragma unroll
                 for (int j = 0; j < GC; ++j) {
-                    const float send = upper ? kt[i][j] : kt[i + off][j];
-                    const float keep = upper ? kt[i + off][j] : kt[i][j];
-                    kt[i][j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+                    const float* wr = WvT_s + (g * C + h * GC + j) * GCP;
+                    float d = 0.0f;
+#pragma unroll
+                    for (int c4 = 0; c4 < GCP; c4 += 4) {
+                        const float4 w = *reinterpret_cast<const float4*>(wr + c4);
+                        d = fmaf(w.x, yv[h][c4], d);
+                        if (c4 + 1 < GC) d = fmaf(w.y, yv[h][c4 + 1], d);
+                        if (c4 + 2 < GC) d = fmaf(w.z, yv[h][c4 + 2], d);
+                        if (c4 + 3 < GC) d = fmaf(w.w, yv[h][c4 + 3], d);
+                    }
+                    epi[((hh * GC + j) * NG + g) * 32 + lane] = d;
                 }
             }
-        }
-        if (live) {
-            const float inv = 1.0f / sum;
-            float* op = a.out + ((int64_t)b * C + g * GC) * HW + pix;
+            __syncthreads();
+            if (g / Cfg::EPI_H == r) {
+                const int hh = g - r * Cfg::EPI_H;
+                float* op = a.out + ((int64_t)b * C + g * GC) * HW + pix;
 #pragma unroll
-            for (int j = 0; j < GC; ++j) op[(int64_t)j * HW] = fmaf(kt[0][j], inv, __ldg(a.bv + g * GC + j));
+                for (int j = 0; j < GC; ++j) {
+                    float acc = epi[((hh * GC + j) * NG + 0) * 32 + lane];
+#pragma unroll
+                    for (int gg = 1; gg < NG; ++gg) acc += epi[((hh * GC + j) * NG + gg) * 32 + lane];
+                    if (live) st_stream(op + (int64_t)j * HW, fmaf(acc, inv, __ldg(a.bv + g * GC + j)));
+                }
+            }
         }
     }
 }
@@ -206,14 +299,19 @@ __global__ void __launch_bounds__(kDattnThreads) dattn_kernel(DattnArgs a) {
 int launch_softmax_samples(float* sc, int64_t R, int n, int64_t HW, cudaStream_t st);
 
 template <int GC, int NG>
-static int launch_dattn(const DattnArgs& a, cudaStream_t st) {
-    constexpr int C = GC * NG;
-    constexpr int PPB = (kDattnThreads / 32) * (32 / NG);
-    const size_t smem = (size_t)3 * C * (C | 1) * sizeof(float);
+static int launch_dattn(DattnArgs a, cudaStream_t st) {
+    using Cfg = DattnCfg<GC, NG>;
+    const size_t smem = (size_t)Cfg::SMEM_FLOATS * sizeof(float);
     VFI_CUDA(cudaFuncSetAttribute(dattn_kernel<GC, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t tiles = ceil_div((int64_t)a.B * a.H * a.W, PPB);
-    const int blocks = (int)min64(tiles, (int64_t)kNumSMs * 3);
-    dattn_kernel<GC, NG><<<blocks, kDattnThreads, smem, st>>>(a);
+    // warp tile: 32x1 pixels of a row (fewest cache lines per tap request); narrow images use 16x2 / 8x4
+    a.tw_log2 = a.W >= 32 ? 5 : (a.W >= 16 ? 4 : 3);
+    const char* env = getenv("VFI_DATTN_TW_LOG2");
+    if (env && env[0] >= '3' && env[0] <= '5') a.tw_log2 = env[0] - '0';
+    a.tiles_x = (int)ceil_div(a.W, 1 << a.tw_log2);
+    a.tiles_y = (int)ceil_div(a.H, 32 >> a.tw_log2);
+    const int64_t tiles = (int64_t)a.B * a.tiles_x * a.tiles_y;
+    const int blocks = (int)min64(tiles, (int64_t)kNumSMs * Cfg::MIN_BLOCKS);
+    dattn_kernel<GC, NG><<<blocks, Cfg::THREADS, smem, st>>>(a);
     VFI_CHECK_LAUNCH("dattn_kernel");
     return VFI_OK;
 }
@@ -246,6 +344,7 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
     a.B = B; a.H = H; a.W = W; a.nS = nS;
     a.offset_scale = offset_scale;
     a.coords_final = coords_final;
+    a.tw_log2 = 5; a.tiles_x = a.tiles_y = 0;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int gc = C / nG;
     int rc;

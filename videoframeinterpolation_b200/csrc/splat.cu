@@ -104,8 +104,6 @@ __global__ void __launch_bounds__(256) splat_normalize_kernel(const float* __res
 
 }  // namespace vfi
 
-extern "C" size_t vfi_splat_workspace_bytes(int, int, int, int) { return 0; }
-
 extern "C" int vfi_splat_f32(const float* in, const float* flow, const float* metric, const float* t, float* num,
                              float* den, int B, int C, int H, int W, int weight_mode, int accumulate, void* workspace,
                              size_t workspace_bytes, void* stream) {
