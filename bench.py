@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--no-micro", action="store_true", help="skip the warp/splat micro-benchmark")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs under ncu only)")
+    ap.add_argument("--channels-last", type=int, default=0, help="run the cuDNN conv stacks around the hot path in NHWC")
     ap.add_argument("--tf32", type=int, default=1, help="allow TF32 in the cuDNN convs around the hot path (PyTorch default)")
     return ap.parse_args()
 
@@ -244,6 +245,8 @@ def run_vfi(args):
 
     torch.manual_seed(0)
     net = init_dat_weights(v.DATwConstantnCv1(v.default_args())).to(dev).eval()
+    if args.channels_last:
+        net = net.to(memory_format=torch.channels_last)
     P, H, W = args.pairs, args.height, args.width
     g = torch.Generator().manual_seed(seed_for(4, rank))
     h_x0 = torch.rand(P, 3, H, W, generator=g).pin_memory()
@@ -252,6 +255,8 @@ def run_vfi(args):
     t = torch.full((P, 1, 1, 1), 0.5, device=dev)
     padder = v.InputPadder((H, W), divisor=16)
     d_x0, d_x1 = padder.pad(h_x0.to(dev), h_x1.to(dev))
+    if args.channels_last:
+        d_x0, d_x1 = d_x0.contiguous(memory_format=torch.channels_last), d_x1.contiguous(memory_format=torch.channels_last)
 
     def step_device():
         return net.inference(d_x0, d_x1, t)

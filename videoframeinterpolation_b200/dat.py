@@ -70,9 +70,12 @@ class DATwConstantnCv1(nn.Module):
         mean_ = torch.cat((x0, x1), dim=2).mean(1, keepdim=True).mean(2, keepdim=True).mean(3, keepdim=True)
         return x0 - mean_, x1 - mean_, mean_
 
-    def _generate_frame(self, x0, x1, t, return_flows: bool = False):
+    def _generate_frame(self, x0, x1, t, return_flows: bool = False, mean_=None):
         nf = self.nf
-        x0, x1, mean_ = self.norm_w_rgb_mean(x0, x1)
+        if mean_ is None:
+            x0, x1, mean_ = self.norm_w_rgb_mean(x0, x1)
+        else:       # tile of a larger frame: the mean is the GLOBAL one (models/BaseModel.py:14-17)
+            x0, x1 = x0 - mean_, x1 - mean_
         f0 = self.feature_encoder(x0)
         f1 = self.feature_encoder(x1)
         q4, ft0_4, ft1_4 = self.coarse_query_builder(f0[3], f1[3], t)
@@ -93,6 +96,24 @@ class DATwConstantnCv1(nn.Module):
 
     def forward(self, x0, x1, t):
         return self._generate_frame(x0, x1, t)
+
+    @torch.no_grad()
+    def inference_tiled(self, x0, x1, t, grid=(2, 4), halo=64, rank: int = 0, world: int = 1, out=None):
+        """Spatially tiled inference (BASELINE configs[4]): every tile+halo crop runs the whole forward with the
+        global rgb mean; interiors are written into ``out``.  ``rank``/``world`` select this process's tiles
+        (no collective: each rank fills its own interiors; gather them however the caller likes)."""
+        from .shard import tile_plan, tiles_of_rank
+        B, _, H, W = x0.shape
+        mean_ = torch.cat((x0, x1), dim=2).mean(1, keepdim=True).mean(2, keepdim=True).mean(3, keepdim=True)
+        if out is None:
+            out = torch.zeros((B, 3, H, W), dtype=x0.dtype, device=x0.device)
+        for tl in tiles_of_rank(tile_plan(H, W, grid, halo), rank, world):
+            ys, xs = tl.crop
+            pred = self._generate_frame(x0[:, :, ys, xs].contiguous(), x1[:, :, ys, xs].contiguous(), t, mean_=mean_)
+            iy, ix = tl.interior_in_crop
+            oy, ox = tl.interior
+            out[:, :, oy, ox] = pred[:, :, iy, ix]
+        return out
 
 
 class InputPadder:
