@@ -45,6 +45,34 @@ def test_dcn_op_golden(vfi, golden, algo):
         assert_close(out, g[key], TOL, f"dcn[{key}]")
 
 
+def test_dcn_tcgen05_path(vfi, golden):
+    """The tensor-core path (tcgen05.mma kind::tf32, error-compensated 3xTF32, accumulators in TMEM) against the same
+    fixtures and against the oracle at dim 64 (cin/group 8: one k-step per tap) and dim 72 (9: two k-steps per tap)."""
+    from videoframeinterpolation_b200._lib import VfiError
+    g = golden("dcn")
+    covered = 0
+    for key, kw in gc.dcn_op_cases().items():
+        k = cu_kw(kw)
+        try:
+            out = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=k["stride"], padding=k["padding"],
+                                    dilation=k["dilation"], mask=k["mask"], algo="tcgen05")
+        except VfiError as e:
+            assert "does not cover" in str(e), str(e)
+            continue
+        assert_close(out, g[key], TOL, f"dcn tcgen05[{key}]")
+        covered += 1
+    assert covered >= 2, f"tcgen05 path covered only {covered} fixture cases"
+    for name, C, OG in (("tc64", 64, 8), ("tc72", 72, 8), ("tc64og4", 64, 4)):
+        kw = gc._dcn_op(name, 2, C, C, 37, 53, WG=8, OG=OG)        # 1961 px: last 128-px tile is partial
+        with oracle.library_ops():
+            ref = oracle.deform_conv2d(**kw)
+        k = cu_kw(kw)
+        out = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"], algo="tcgen05")
+        assert_close(out, ref, TOL, f"dcn tcgen05 {name}")
+        simt = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"], algo="simt")
+        assert_close(out, simt, TOL, f"dcn tcgen05 vs simt {name}")
+
+
 def test_dcn_module_golden(vfi, golden):
     from test_oracle_golden import _module_sd_dcn
     g = golden("dcn")

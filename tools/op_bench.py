@@ -66,8 +66,16 @@ def run_dattn(a, dev, flush):
     q = torch.randn(B, C, H, W, generator=g).to(dev)
     f0 = torch.randn(B, C, H, W, generator=g).to(dev)
     f1 = torch.randn(B, C, H, W, generator=g).to(dev)
-    raw0 = (torch.randn(B, nG * nS * 2, H, W, generator=g) * 0.5).to(dev)
-    raw1 = (torch.randn(B, nG * nS * 2, H, W, generator=g) * 0.5).to(dev)
+    def raw_offsets():
+        # conv_res_offset outputs are spatially smooth (a 3x3 conv of smooth features): correlated field + small noise;
+        # --flow iid gives per-pixel independent offsets (adversarial for the gather)
+        n = nG * nS * 2
+        if a.flow == "iid":
+            return (torch.randn(B, n, H, W, generator=g) * 0.5).to(dev)
+        coarse = torch.randn(B, n, H // 16 + 2, W // 16 + 2, generator=g).to(dev)
+        f = torch.nn.functional.interpolate(coarse, size=(H, W), mode="bilinear", align_corners=True) * 0.5
+        return f + torch.randn(B, n, H, W, generator=g).to(dev) * 0.02
+    raw0, raw1 = raw_offsets(), raw_offsets()
     ft0 = wl.make_flow(B, H, W, 8.0 / (1 << lv), g, device=dev)
     ft1 = wl.make_flow(B, H, W, 8.0 / (1 << lv), g, device=dev)
     ws = [torch.randn(C, C, generator=g).to(dev) * C ** -0.5 if i % 2 == 0 else torch.randn(C, generator=g).to(dev) * 0.1
@@ -76,7 +84,7 @@ def run_dattn(a, dev, flush):
                                             offset_scale=scale)
     ms, best = timeit(fn, a.iters, flush)
     flops = 2.0 * B * H * W * (2 * C * C + C * C + 2 * (2 * nS) * nG * (C // nG) * nG + 4 * C * 2 * nS)
-    report("dattn", dict(level=lv, B=B, C=C, H=H, W=W, nG=nG, nS=nS), ms, best, wl.bytes_dattn(B, C, H, W, nG, nS),
+    report("dattn", dict(level=lv, B=B, C=C, H=H, W=W, nG=nG, nS=nS, offsets=a.flow), ms, best, wl.bytes_dattn(B, C, H, W, nG, nS),
            {"tflops_fp32": round(flops / ms / 1e9, 2)})
 
 
@@ -113,10 +121,11 @@ def run_dcn(a, dev, flush):
     mask = torch.sigmoid(torch.randn(B, OG * 9, H, W, generator=g)).to(dev)
     wgt = (torch.randn(C, C // WG, 3, 3, generator=g) * 0.1).to(dev)
     bias = torch.randn(C, generator=g).to(dev)
-    fn = lambda: v.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask)
+    algo = os.environ.get("VFI_DCN_ALGO", "auto")
+    fn = lambda: v.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask, algo=algo)
     ms, best = timeit(fn, a.iters, flush)
     flops = 2.0 * C * (C // WG) * 9 * B * H * W
-    report("dcn", dict(B=B, C=C, H=H, W=W, OG=OG, WG=WG), ms, best, wl.bytes_dcn(B, C, C, H, W, OG),
+    report("dcn", dict(B=B, C=C, H=H, W=W, OG=OG, WG=WG, algo=algo), ms, best, wl.bytes_dcn(B, C, C, H, W, OG),
            {"gemm_tflops": round(flops / ms / 1e9, 2)})
 
 

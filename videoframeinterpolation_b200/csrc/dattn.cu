@@ -177,16 +177,18 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
             }
             const float* offp = a.offs[f] + ((int64_t)b * NG * nS + (int64_t)g * nS) * 2 * HW + pix;
             const float* featp = a.feat[f] + ((int64_t)b * C + g * GC) * HW;
+            // offsets are the only HBM-streamed operand of the loop (2*nG*nS floats per pixel and frame): keep the
+            // next chunk's loads in flight across the two barriers of the current chunk
+            float odx[SC], ody[SC];
+#pragma unroll
+            for (int si = 0; si < SC; ++si) {
+                const int s = min(si, nS - 1);
+                odx[si] = ld_stream(offp + (int64_t)(2 * s) * HW);
+                ody[si] = ld_stream(offp + (int64_t)(2 * s + 1) * HW);
+            }
             for (int s0 = 0; s0 < nS; s0 += SC) {
                 float xs[SC][GC];
                 // ---- A: sample + partial logits ----
-                float odx[SC], ody[SC];
-#pragma unroll
-                for (int si = 0; si < SC; ++si) {
-                    const int s = min(s0 + si, nS - 1);
-                    odx[si] = ld_stream(offp + (int64_t)(2 * s) * HW);
-                    ody[si] = ld_stream(offp + (int64_t)(2 * s + 1) * HW);
-                }
 #pragma unroll
                 for (int si = 0; si < SC; ++si) {
                     float dx = odx[si], dy = ody[si];
@@ -203,6 +205,14 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
 #pragma unroll
                         for (int cc = 0; cc < GC; ++cc) d = fmaf(kt[h][cc], xs[si][cc], d);
                         red[((si * NG + h) * NG + g) * 32 + lane] = d;
+                    }
+                }
+                if (s0 + SC < nS) {
+#pragma unroll
+                    for (int si = 0; si < SC; ++si) {
+                        const int s = min(s0 + SC + si, nS - 1);
+                        odx[si] = ld_stream(offp + (int64_t)(2 * s) * HW);
+                        ody[si] = ld_stream(offp + (int64_t)(2 * s + 1) * HW);
                     }
                 }
                 __syncthreads();

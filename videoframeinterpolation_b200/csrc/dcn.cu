@@ -6,42 +6,9 @@
 // [ci*K + tap][out] so one LDS.128 feeds four FMAs; a thread owns one pixel and accumulates the
 // group's Cout/WG outputs in registers.  Offsets/mask are read once per (offset group, tap).
 // HBM traffic = 4*(Cin + 3*OG*K + Cout) B/px (x is re-read through L1/L2 only).
-#include "vfi_common.cuh"
+#include "dcn_common.cuh"
 
 namespace vfi {
-
-struct DcnParams {
-    int Cin, Cout, H, W, Ho, Wo, kh, kw, stride, pad, dil, WG, OG;
-};
-
-struct DcnTap {
-    int64_t o;  // offset of (h_low, w_low) in a plane
-    float w1, w2, w3, w4;
-    bool k1, k2, k3, k4;
-};
-
-// torchvision bilinear_interpolate: 0 if h <= -1 || h >= H || w <= -1 || w >= W, else 4 corners, each
-// dropped when outside.
-__device__ __forceinline__ DcnTap dcn_tap(float h, float w, int H, int W, float mask) {
-    DcnTap t;
-    const bool inside = h > -1.0f && h < (float)H && w > -1.0f && w < (float)W;
-    const float hc = inside ? h : 0.0f, wc = inside ? w : 0.0f;
-    const float hl = floorf(hc), wl = floorf(wc);
-    const int h_low = (int)hl, w_low = (int)wl;
-    const float lh = hc - hl, lw = wc - wl;
-    const float hh = 1.0f - lh, hw = 1.0f - lw;
-    t.k1 = inside && h_low >= 0 && w_low >= 0;
-    t.k2 = inside && h_low >= 0 && w_low + 1 <= W - 1;
-    t.k3 = inside && h_low + 1 <= H - 1 && w_low >= 0;
-    t.k4 = inside && h_low + 1 <= H - 1 && w_low + 1 <= W - 1;
-    t.w1 = hh * hw;
-    t.w2 = hh * lw;
-    t.w3 = lh * hw;
-    t.w4 = lh * lw;
-    t.o = (int64_t)h_low * W + w_low;
-    (void)mask;
-    return t;
-}
 
 template <int COGP>
 __global__ void __launch_bounds__(128) dcn_simt_kernel(const float* __restrict__ x, const float* __restrict__ offset,
@@ -85,14 +52,9 @@ __global__ void __launch_bounds__(128) dcn_simt_kernel(const float* __restrict__
                     const float dy = ld_stream(offb + ((int64_t)og * 2 * K + 2 * tap) * HWo);
                     const float dx = ld_stream(offb + ((int64_t)og * 2 * K + 2 * tap + 1) * HWo);
                     mval = maskb ? ld_stream(maskb + ((int64_t)og * K + tap) * HWo) : 1.0f;
-                    t = dcn_tap(base_h + (float)(i * p.dil) + dy, base_w + (float)(j * p.dil) + dx, p.H, p.W, mval);
+                    t = dcn_tap(base_h + (float)(i * p.dil) + dy, base_w + (float)(j * p.dil) + dx, p.H, p.W);
                 }
-                const float* pl = xb + (int64_t)cl * HW + t.o;
-                float v = 0.0f;
-                if (t.k1) v = t.w1 * __ldg(pl);
-                if (t.k2) v += t.w2 * __ldg(pl + 1);
-                if (t.k3) v += t.w3 * __ldg(pl + p.W);
-                if (t.k4) v += t.w4 * __ldg(pl + p.W + 1);
+                float v = dcn_sample(xb + (int64_t)cl * HW + t.o, t, p.W);
                 v *= mval;
                 const float4* wr = reinterpret_cast<const float4*>(w_s + (size_t)(cl * K + tap) * COGP);
 #pragma unroll
