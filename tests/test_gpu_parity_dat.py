@@ -62,8 +62,11 @@ def test_dcn_tcgen05_path(vfi, golden):
         assert_close(out, g[key], TOL, f"dcn tcgen05[{key}]")
         covered += 1
     assert covered >= 2, f"tcgen05 path covered only {covered} fixture cases"
-    for name, C, OG in (("tc64", 64, 8), ("tc72", 72, 8), ("tc64og4", 64, 4)):
-        kw = gc._dcn_op(name, 2, C, C, 37, 53, WG=8, OG=OG)        # 1961 px: last 128-px tile is partial
+    # W = 53: direct gathers only; W = 64 / 96: input window staged by TMA (rows must be 16-byte aligned), large sigma
+    # pushes many taps out of the window and out of the frame
+    for name, C, OG, H, W, sig in (("tc64", 64, 8, 37, 53, 1.5), ("tc72", 72, 8, 37, 53, 1.5), ("tc64og4", 64, 4, 37, 53, 1.5),
+                                   ("tc64w", 64, 8, 38, 64, 1.5), ("tc72w", 72, 8, 21, 96, 6.0), ("tc64wog4", 64, 4, 38, 64, 4.0)):
+        kw = gc._dcn_op(name, 2, C, C, H, W, WG=8, OG=OG, sigma=sig)        # partial tiles on both axes
         with oracle.library_ops():
             ref = oracle.deform_conv2d(**kw)
         k = cu_kw(kw)

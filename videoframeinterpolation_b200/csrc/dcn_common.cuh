@@ -10,6 +10,7 @@ struct DcnParams {
 
 struct DcnTap {
     int64_t o;  // offset of (h_low, w_low) in a plane
+    int hl, wl; // h_low, w_low
     float w1, w2, w3, w4;
     bool k1, k2, k3, k4;
 };
@@ -33,6 +34,8 @@ __device__ __forceinline__ DcnTap dcn_tap(float h, float w, int H, int W) {
     t.w3 = lh * hw;
     t.w4 = lh * lw;
     t.o = (int64_t)h_low * W + w_low;
+    t.hl = h_low;
+    t.wl = w_low;
     return t;
 }
 

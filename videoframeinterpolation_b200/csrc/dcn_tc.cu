@@ -13,6 +13,9 @@
 // fence.proxy.async; empty: tcgen05.commit), the epilogue reads TMEM with tcgen05.ld (lane = pixel, so the
 // NCHW stores are coalesced) and adds the bias.  K ordering is tap-major (k' = tap*CP + channel): one tap =
 // CP/8 MMA k-steps; the weights are re-laid once per call by a tiny prep kernel (workspace).
+#include <stdlib.h>
+#include <string.h>
+
 #include "dcn_common.cuh"
 #include "tma.cuh"
 
@@ -20,7 +23,9 @@ namespace vfi {
 
 constexpr int kTcPix = 128;       // pixels per CTA = UMMA M
 constexpr int kTcN = 16;          // UMMA N (padded out channels per group)
-constexpr int kTcThreads = 160;   // 4 gather/epilogue warps + 1 MMA warp
+constexpr int kTcThreads = 192;   // 4 gather/epilogue warps + 1 MMA warp + 1 TMA warp
+constexpr int kTcTW = 32, kTcTH = 4;                    // output tile (a warp = one row of 32 pixels)
+constexpr int kWinW = 48, kWinH = 20, kWinHalo = 7;     // staged input window (stride 1): tile + kernel + halo
 
 __device__ __forceinline__ uint32_t to_tf32_rna(float v) {
     uint32_t r;
@@ -81,10 +86,11 @@ __global__ void dcn_tc_prep_kernel(const float* __restrict__ weight, float* __re
 }
 
 template <int KS>
-__global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __restrict__ x, const float* __restrict__ offset,
+__global__ void __launch_bounds__(kTcThreads, 2) dcn_tc_kernel(const float* __restrict__ x, const float* __restrict__ offset,
                                                             const float* __restrict__ mask, const float* __restrict__ wprep,
                                                             const float* __restrict__ bias, float* __restrict__ out, DcnParams p,
-                                                            int tiles_per_img, int b_bytes, int tmem_cols) {
+                                                            int tiles_x, int tiles_per_img, int b_bytes, int tmem_cols,
+                                                            const __grid_constant__ CUtensorMap xmap, int use_win) {
     constexpr int CP = KS * 8;
     constexpr int NS = KS == 1 ? 4 : 3;
     constexpr int A_PART = 4096;                 // bytes of one (part, k-step) block: 16 row groups x 256 B
@@ -95,7 +101,10 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
     uint64_t* full = reinterpret_cast<uint64_t*>(b_buf + 2 * b_bytes);
     uint64_t* empty = full + NS;
     uint64_t* done = empty + NS;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+    uint64_t* win_full = done + 1;      // [2]
+    uint64_t* win_empty = win_full + 2; // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(win_empty + 2);
+    int* s_shift = reinterpret_cast<int*>(tmem_slot + 1);   // [2] window displacement (y, x)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int taps = p.kh * p.kw;
@@ -103,6 +112,11 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
     const int b = blockIdx.x / tiles_per_img;
     const int tile = blockIdx.x - b * tiles_per_img;
     const int64_t HWo = (int64_t)p.Ho * p.Wo, HW = (int64_t)p.H * p.W;
+    const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+    const int xo0 = tx * kTcTW, yo0 = ty * kTcTH;
+    const int win_bytes = kWinW * kWinH * cin_g * 4;
+    uint8_t* win_buf = reinterpret_cast<uint8_t*>(s_shift + 2);
+    win_buf += (128u - (smem_u32(win_buf) & 127u)) & 127u;      // TMA destination alignment
 
     if (tid == 0) {
         for (int s = 0; s < NS; ++s) {
@@ -110,7 +124,24 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
             mbar_init(&empty[s], 1);
         }
         mbar_init(done, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&win_full[s], 1);
+            mbar_init(&win_empty[s], kTcPix);
+        }
         fence_mbar_init();
+        // window displacement: mean offset of the centre tap (offset group 0) at four probe pixels of the tile.
+        // Any value is correct (taps outside the window are fetched from global memory); a good one keeps them rare.
+        float sy = 0.0f, sx = 0.0f;
+        const int ctap = taps / 2;
+        for (int k = 0; k < 4; ++k) {
+            const int px = min(xo0 + 4 + 8 * k, p.Wo - 1), py = min(yo0 + (k & 1) * 2 + 1, p.Ho - 1);
+            const float* o = offset + (int64_t)b * p.OG * 2 * taps * HWo + (int64_t)py * p.Wo + px;
+            const float dy = __ldg(o + (int64_t)(2 * ctap) * HWo), dx = __ldg(o + (int64_t)(2 * ctap + 1) * HWo);
+            sy += isfinite(dy) ? fminf(fmaxf(dy, -1.0e6f), 1.0e6f) : 0.0f;
+            sx += isfinite(dx) ? fminf(fmaxf(dx, -1.0e6f), 1.0e6f) : 0.0f;
+        }
+        s_shift[0] = (int)rintf(sy * 0.25f);
+        s_shift[1] = (int)rintf(sx * 0.25f);
     }
     if (warp == 4) {   // one warp allocates (and later frees) the accumulator columns
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(tmem_cols) : "memory");
@@ -120,14 +151,16 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // window origin in input coordinates (x a multiple of 4: TMA's 16-byte rule for the innermost coordinate)
+    const int wy0 = yo0 * p.stride - p.pad + s_shift[0] - kWinHalo;
+    const int wx0 = (xo0 * p.stride - p.pad + s_shift[1] - kWinHalo) & ~3;
 
     if (warp < 4) {
         // ================= gather warps: thread = output pixel =================
         const int m = tid;
-        const int64_t pix_raw = (int64_t)tile * kTcPix + m;
-        const bool live = pix_raw < HWo;
-        const int64_t pix = live ? pix_raw : HWo - 1;
-        const int ho = (int)(pix / p.Wo), wo = (int)(pix - (int64_t)ho * p.Wo);
+        const bool live = xo0 + lane < p.Wo && yo0 + warp < p.Ho;
+        const int wo = min(xo0 + lane, p.Wo - 1), ho = min(yo0 + warp, p.Ho - 1);
+        const int64_t pix = (int64_t)ho * p.Wo + wo;
         const float base_h = (float)(ho * p.stride - p.pad), base_w = (float)(wo * p.stride - p.pad);
         const float* offb = offset + (int64_t)b * p.OG * 2 * taps * HWo + pix;
         const float* maskb = mask ? mask + (int64_t)b * p.OG * taps * HWo + pix : nullptr;
@@ -136,16 +169,23 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
         // offsets / mask are the HBM-streamed operands: when a weight group sits inside one offset group (the usual
         // OG | WG case) the next tap's three values are requested one iteration ahead
         const bool uniform_og = (cpo % cin_g) == 0;
-        const int n_it = p.WG * taps;
-        float ndy = 0.0f, ndx = 0.0f, nm = 1.0f;
-        auto load_tap = [&](int itn, float& dy, float& dx, float& mv) {
-            const int gg = itn / taps, tt = itn - gg * taps;
+        // prefetch distance = one whole weight group (kMaxPf taps): registers hold the current group's values while the
+        // next group's loads are in flight, so HBM latency never sits on the per-tap critical path
+        constexpr int kMaxPf = 9;
+        const bool pf = uniform_og && taps <= kMaxPf;
+        float cdy[kMaxPf], cdx[kMaxPf], cm[kMaxPf], ndy[kMaxPf], ndx[kMaxPf], nm[kMaxPf];
+        auto load_group = [&](int gg, float* dy, float* dx, float* mv) {
             const int og = (gg * cin_g) / cpo;
-            dy = ld_stream(offb + ((int64_t)og * 2 * taps + 2 * tt) * HWo);
-            dx = ld_stream(offb + ((int64_t)og * 2 * taps + 2 * tt + 1) * HWo);
-            mv = maskb ? ld_stream(maskb + ((int64_t)og * taps + tt) * HWo) : 1.0f;
+#pragma unroll
+            for (int tt = 0; tt < kMaxPf; ++tt) {
+                if (tt < taps) {
+                    dy[tt] = ld_stream(offb + ((int64_t)og * 2 * taps + 2 * tt) * HWo);
+                    dx[tt] = ld_stream(offb + ((int64_t)og * 2 * taps + 2 * tt + 1) * HWo);
+                    mv[tt] = maskb ? ld_stream(maskb + ((int64_t)og * taps + tt) * HWo) : 1.0f;
+                }
+            }
         };
-        if (uniform_og) load_tap(0, ndy, ndx, nm);
+        if (pf) load_group(0, ndy, ndx, nm);
         for (int g = 0; g < p.WG; ++g) {
             {   // this group's re-laid weights (hi | lo) -> shared
                 const float4* src = reinterpret_cast<const float4*>(wprep) + (size_t)g * (b_bytes / 16);
@@ -153,16 +193,59 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
                 for (int i = m; i < b_bytes / 16; i += kTcPix) dst[i] = __ldg(src + i);
             }
             const float* xb = x + ((int64_t)b * p.Cin + (int64_t)g * cin_g) * HW;
+            if (pf) {
+#pragma unroll
+                for (int tt = 0; tt < kMaxPf; ++tt) {
+                    cdy[tt] = ndy[tt];
+                    cdx[tt] = ndx[tt];
+                    cm[tt] = nm[tt];
+                }
+                if (g + 1 < p.WG) load_group(g + 1, ndy, ndx, nm);
+            }
+            const float* wb = reinterpret_cast<const float*>(win_buf + (size_t)(g & 1) * win_bytes);
+            if (use_win) mbar_wait(&win_full[g & 1], (g >> 1) & 1);
+#pragma unroll 1
             for (int tap = 0; tap < taps; ++tap, ++it) {
                 const int stage = it % NS;
                 const int ki = tap / p.kw, kj = tap - ki * p.kw;
                 float v[CP];
                 if (uniform_og) {
-                    const float dy = ndy, dx = ndx, mval = nm;
-                    if (it + 1 < n_it) load_tap(it + 1, ndy, ndx, nm);
-                    const DcnTap t = dcn_tap(base_h + (float)(ki * p.dil) + dy, base_w + (float)(kj * p.dil) + dx, p.H, p.W);
+                    float dy, dx, mval;
+                    if (pf) {   // select from registers without dynamic indexing
+                        dy = cdy[0]; dx = cdx[0]; mval = cm[0];
 #pragma unroll
-                    for (int cl = 0; cl < CP; ++cl) v[cl] = cl < cin_g ? dcn_sample(xb + (int64_t)cl * HW + t.o, t, p.W) * mval : 0.0f;
+                        for (int tt = 1; tt < kMaxPf; ++tt)
+                            if (tap == tt) { dy = cdy[tt]; dx = cdx[tt]; mval = cm[tt]; }
+                    } else {
+                        const int og = (g * cin_g) / cpo;
+                        dy = ld_stream(offb + ((int64_t)og * 2 * taps + 2 * tap) * HWo);
+                        dx = ld_stream(offb + ((int64_t)og * 2 * taps + 2 * tap + 1) * HWo);
+                        mval = maskb ? ld_stream(maskb + ((int64_t)og * taps + tap) * HWo) : 1.0f;
+                    }
+                    const DcnTap t = dcn_tap(base_h + (float)(ki * p.dil) + dy, base_w + (float)(kj * p.dil) + dx, p.H, p.W);
+                    // taps inside the staged window come from shared memory (zero-filled outside the frame, and the
+                    // per-corner predicates still apply); the rare pixel whose taps leave the window reads global memory
+                    const int ly = t.hl - wy0, lx = t.wl - wx0;
+                    const bool in_win = use_win && ly >= 0 && ly + 1 < kWinH && lx >= 0 && lx + 1 < kWinW;
+                    if (in_win) {
+                        const float* wp = wb + ly * kWinW + lx;
+#pragma unroll
+                        for (int cl = 0; cl < CP; ++cl) {
+                            float r = 0.0f;
+                            if (cl < cin_g) {
+                                const float* q = wp + cl * (kWinW * kWinH);
+                                if (t.k1) r = t.w1 * q[0];
+                                if (t.k2) r += t.w2 * q[1];
+                                if (t.k3) r += t.w3 * q[kWinW];
+                                if (t.k4) r += t.w4 * q[kWinW + 1];
+                                r *= mval;
+                            }
+                            v[cl] = r;
+                        }
+                    } else {
+#pragma unroll
+                        for (int cl = 0; cl < CP; ++cl) v[cl] = cl < cin_g ? dcn_sample(xb + (int64_t)cl * HW + t.o, t, p.W) * mval : 0.0f;
+                    }
                 } else {
                     int prev_og = -1;
                     DcnTap t;
@@ -203,6 +286,7 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
                 fence_proxy_async_smem();     // generic-proxy stores (slab + weights) -> visible to the tensor core
                 mbar_arrive(&full[stage]);
             }
+            if (use_win) mbar_arrive(&win_empty[g & 1]);   // this thread is done reading the group's window
         }
         // ================= epilogue: TMEM -> registers -> + bias -> NCHW =================
         mbar_wait(done, 0);
@@ -227,7 +311,7 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
                 }
             }
         }
-    } else if (lane == 0) {
+    } else if (warp == 4 && lane == 0) {
         // ================= MMA issuer (one thread) =================
         const uint32_t a_base = smem_u32(a_ring), b_base = smem_u32(b_buf);
         int it = 0;
@@ -252,6 +336,15 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
             }
         }
         umma_commit(done);
+    } else if (warp == 5 && lane == 0 && use_win) {
+        // ================= TMA producer: one window (cin_g planes) per weight group, double buffered =================
+        tma_prefetch_desc(&xmap);
+        for (int g = 0; g < p.WG; ++g) {
+            const int s = g & 1;
+            if (g >= 2) mbar_wait(&win_empty[s], ((g >> 1) - 1) & 1);
+            mbar_arrive_expect_tx(&win_full[s], win_bytes);
+            tma_load_3d(win_buf + (size_t)s * win_bytes, &xmap, &win_full[s], wx0, wy0, b * p.Cin + g * cin_g);
+        }
     }
     __syncwarp();
     tc_fence_before();
@@ -263,14 +356,18 @@ __global__ void __launch_bounds__(kTcThreads, 4) dcn_tc_kernel(const float* __re
 
 static int tc_ks(const DcnParams& p) { return (p.Cin / p.WG) <= 8 ? 1 : 2; }
 
+static size_t tc_smem_bytes(const DcnParams& p) {
+    const int ks = tc_ks(p), taps = p.kh * p.kw;
+    return (size_t)(ks == 1 ? 4 : 3) * 2 * ks * 4096 + 2 * (size_t)(2 * taps * ks * 512) + 256 +
+           2 * (size_t)kWinW * kWinH * (p.Cin / p.WG) * 4 + 128;
+}
+
 // 0 = unsupported, 1 = supported, 2 = supported and preferred by algo 0 (auto)
 int dcn_tc_supported(const DcnParams& p) {
     const int cin_g = p.Cin / p.WG, cog = p.Cout / p.WG, taps = p.kh * p.kw;
     if (cin_g > 16 || cog > kTcN || p.WG * kTcN > 512 || taps > 49) return 0;
     if ((int64_t)p.Ho * p.Wo >= (1ll << 31)) return 0;
-    const int ks = tc_ks(p);
-    const size_t smem = (size_t)(ks == 1 ? 4 : 3) * 2 * ks * 4096 + 2 * (size_t)(2 * taps * ks * 512) + 256;
-    if (smem > 200 * 1024) return 0;
+    if (tc_smem_bytes(p) > 220 * 1024) return 0;
     return 1;
 }
 
@@ -293,18 +390,32 @@ int launch_dcn_tc(const float* x, const float* offset, const float* mask, const 
     else dcn_tc_prep_kernel<2><<<pblocks, 256, 0, st>>>(weight, wprep, cin_g, cog, taps, p.WG);
     VFI_CHECK_LAUNCH("dcn_tc_prep_kernel");
     const int b_bytes = 2 * taps * ks * 512;
-    const size_t smem = (size_t)(ks == 1 ? 4 : 3) * 2 * ks * 4096 + 2 * (size_t)b_bytes + 256;
+    const size_t smem = tc_smem_bytes(p);
     int tmem_cols = 32;
     while (tmem_cols < p.WG * kTcN) tmem_cols *= 2;
-    const int tiles_per_img = (int)ceil_div((int64_t)p.Ho * p.Wo, kTcPix);
+    const int tiles_x = (int)ceil_div(p.Wo, kTcTW), tiles_y = (int)ceil_div(p.Ho, kTcTH);
+    const int tiles_per_img = tiles_x * tiles_y;
     const int64_t grid = (int64_t)B * tiles_per_img;
     VFI_REQUIRE(grid < (1ll << 31), "vfi_dcn_f32: grid too large");
+    // input window staged by TMA: stride 1, kernel extent <= 3, rows 16-byte aligned
+    CUtensorMap xmap;
+    memset(&xmap, 0, sizeof(xmap));
+    int use_win = p.stride == 1 && (p.kh - 1) * p.dil <= 2 && (p.kw - 1) * p.dil <= 2 && p.W % 4 == 0 &&
+                  (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (int64_t)B * p.Cin < (1ll << 31);
+    if (const char* e = getenv("VFI_DCN_WINDOW")) use_win = use_win && e[0] != '0';
+    if (use_win) {
+        int rc = make_tmap_f32_3d(&xmap, x, (uint64_t)p.W, (uint64_t)p.H, (uint64_t)B * p.Cin, (uint64_t)p.W * 4,
+                                  (uint64_t)p.H * p.W * 4, kWinW, kWinH, (uint32_t)cin_g);
+        if (rc) return rc;
+    }
     if (ks == 1) {
         VFI_CUDA(cudaFuncSetAttribute(dcn_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        dcn_tc_kernel<1><<<(unsigned)grid, kTcThreads, smem, st>>>(x, offset, mask, wprep, bias, out, p, tiles_per_img, b_bytes, tmem_cols);
+        dcn_tc_kernel<1><<<(unsigned)grid, kTcThreads, smem, st>>>(x, offset, mask, wprep, bias, out, p, tiles_x, tiles_per_img, b_bytes,
+                                                                  tmem_cols, xmap, use_win);
     } else {
         VFI_CUDA(cudaFuncSetAttribute(dcn_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        dcn_tc_kernel<2><<<(unsigned)grid, kTcThreads, smem, st>>>(x, offset, mask, wprep, bias, out, p, tiles_per_img, b_bytes, tmem_cols);
+        dcn_tc_kernel<2><<<(unsigned)grid, kTcThreads, smem, st>>>(x, offset, mask, wprep, bias, out, p, tiles_x, tiles_per_img, b_bytes,
+                                                                  tmem_cols, xmap, use_win);
     }
     VFI_CHECK_LAUNCH("dcn_tc_kernel");
     return VFI_OK;
