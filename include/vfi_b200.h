@@ -139,6 +139,15 @@ int vfi_dcn_f32(const float* x, const float* offset, const float* mask, const fl
 size_t vfi_dcn_workspace_bytes(int B, int Cin, int Cout, int H, int W, int kh, int kw, int n_weight_grps,
                                int n_offset_grps, int algo);
 
+/* ---- conv epilogue (the PReLU / residual tails of modules/basic_blocks.py:13-73,
+ * modules/cnn_encoders.py:6-42, modules/generator.py:7-24 around the cuDNN convolutions).
+ *   t = y + bias[c];  residual_mode 1: t = residual + t;  slope != NULL: t = t > 0 ? t : slope[c] * t;
+ *   residual_mode 2: t = residual + t.   y / residual / out are (B,C,H,W) contiguous NCHW (channels_last = 0) or
+ * channels-last (channels_last = 1) and share one layout; out may alias y.  bias / slope (C) may be NULL.
+ * Same fp32 operation order as the separate PyTorch ops (bit-identical to them). */
+int vfi_bias_act_f32(const float* y, const float* bias, const float* slope, const float* residual, float* out,
+                     int B, int C, int H, int W, int channels_last, int residual_mode, void* stream);
+
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vfi_launch_count(void);

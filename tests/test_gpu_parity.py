@@ -124,3 +124,28 @@ def test_splat_mass_conservation_1080p(vfi):
     assert abs(float(out.double().sum() / x.double().sum()) - 1.0) < 1e-5
     out2 = vfi.softsplat(2.0 * x, fl, None, "sum")
     assert rel_err(out2, 2.0 * out) < 1e-5
+
+
+# ---- conv epilogue (bias + PReLU + residual), SURVEY.md 8f row f2 ---------------------------------
+@pytest.mark.parametrize("cl", [False, True])
+@pytest.mark.parametrize("shape", [(2, 72, 17, 24), (1, 3, 9, 7), (1, 76, 5, 6)])
+def test_conv_epilogue_bit_identical_to_torch_ops(vfi, cl, shape):
+    from videoframeinterpolation_b200.blocks import conv_bias_act
+    B, C, H, W = shape
+    torch.manual_seed(1)
+    conv = torch.nn.Conv2d(C, C, 3, 1, 1).cuda()
+    prelu = torch.nn.PReLU(C).cuda()
+    with torch.no_grad():
+        prelu.weight.copy_(torch.rand(C) - 0.3)
+    x = torch.randn(B, C, H, W, device="cuda")
+    if cl:
+        x = x.contiguous(memory_format=torch.channels_last)
+        conv = conv.to(memory_format=torch.channels_last)
+    with torch.no_grad():
+        y = torch.nn.functional.conv2d(x, conv.weight, None, 1, 1)          # the same cuDNN call both sides
+        b = conv.bias.view(1, C, 1, 1)
+        assert torch.equal(conv_bias_act(conv, x, prelu), prelu(y + b))
+        assert torch.equal(conv_bias_act(conv, x, None, residual=x), x + (y + b))
+        assert torch.equal(conv_bias_act(conv, x, prelu, residual=x), prelu(x + (y + b)))
+        assert torch.equal(conv_bias_act(conv, x, prelu, residual=x, residual_after_act=True), x + prelu(y + b))
+        assert torch.equal(conv_bias_act(conv, x), y + b)

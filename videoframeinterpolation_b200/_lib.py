@@ -35,6 +35,7 @@ SIGNATURES = {
     "vfi_dattn_f32": (c_int, [c_void_p] * 19 + [c_int] * 7 + [c_float, c_int, c_void_p]),
     "vfi_dcn_f32": (c_int, [c_void_p] * 6 + [c_int] * 13 + [c_void_p, c_size_t, c_void_p]),
     "vfi_dcn_workspace_bytes": (c_size_t, [c_int] * 10),
+    "vfi_bias_act_f32": (c_int, [c_void_p] * 5 + [c_int] * 6 + [c_void_p]),
     "vfi_launch_count": (c_int64, []),
     "vfi_launch_count_reset": (None, []),
 }

@@ -10,8 +10,74 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 
+from . import _lib
+
+
+def _fusable(x: torch.Tensor, conv: nn.Conv2d) -> bool:
+    return (x.is_cuda and x.dtype == torch.float32 and not torch.is_grad_enabled() and conv.bias is not None
+            and conv.padding_mode == "zeros")
+
+
+def conv_bias_act(conv: nn.Conv2d, x: torch.Tensor, prelu: nn.PReLU = None, residual: torch.Tensor = None,
+                  residual_after_act: bool = False) -> torch.Tensor:
+    """cuDNN convolution (no bias) + ONE fused epilogue kernel: bias, optional residual, optional per-channel PReLU
+    (vfi_bias_act_f32).  Same arithmetic order as ``prelu(residual + conv(x))`` / ``residual + conv(x)`` in PyTorch, which
+    runs bias add, PReLU and residual add as three strided elementwise kernels.  Training (grad enabled) and CPU
+    tensors take the plain PyTorch route."""
+    if not _fusable(x, conv):
+        y = conv(x)
+        if residual is not None and not residual_after_act:
+            y = residual + y
+        if prelu is not None:
+            y = prelu(y)
+        if residual is not None and residual_after_act:
+            y = residual + y
+        return y
+    y = F.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
+    B, C, H, W = y.shape
+    cl = y.is_contiguous(memory_format=torch.channels_last) and not y.is_contiguous()
+    if not cl and not y.is_contiguous():
+        y = y.contiguous()
+    res = None
+    if residual is not None:
+        res = residual.contiguous(memory_format=torch.channels_last) if cl else residual.contiguous()
+    slope = None
+    if prelu is not None:
+        slope = prelu.weight if prelu.weight.numel() == C else prelu.weight.expand(C).contiguous()
+    mode = 0 if res is None else (2 if residual_after_act else 1)
+    dev = y.device
+    _lib.call("vfi_bias_act_f32", dev, y.data_ptr(), conv.bias.data_ptr(), _lib.ptr(slope), _lib.ptr(res), y.data_ptr(), B, C, H, W,
+              1 if cl else 0, mode, _lib.stream_ptr(dev))
+    return y
+
+
+class ConvPReLU(nn.Sequential):
+    """Conv2d + PReLU with the reference's Sequential key layout ('0' = conv, '1' = prelu); fused epilogue at inference."""
+
+    def forward(self, x):
+        return conv_bias_act(self[0], x, self[1])
+
+
 def conv_prelu(cin: int, cout: int, stride: int = 1) -> nn.Sequential:
-    return nn.Sequential(nn.Conv2d(cin, cout, 3, stride, 1), nn.PReLU(cout))
+    return ConvPReLU(nn.Conv2d(cin, cout, 3, stride, 1), nn.PReLU(cout))
+
+
+def run_conv_chain(seq: nn.Sequential, x: torch.Tensor) -> torch.Tensor:
+    """Run a Sequential, fusing every Conv2d -> PReLU pair (and trailing bare Conv2d's bias) into conv + one epilogue."""
+    mods = list(seq)
+    i = 0
+    while i < len(mods):
+        m = mods[i]
+        if isinstance(m, nn.Conv2d) and type(m) is nn.Conv2d:
+            if i + 1 < len(mods) and isinstance(mods[i + 1], nn.PReLU):
+                x = conv_bias_act(m, x, mods[i + 1])
+                i += 2
+                continue
+            x = conv_bias_act(m, x)
+        else:
+            x = m(x)
+        i += 1
+    return x
 
 
 class ResBlocknoBN(nn.Module):
@@ -28,7 +94,7 @@ class ResBlocknoBN(nn.Module):
             nn.init.zeros_(conv.bias)
 
     def forward(self, x):
-        return x + self.conv2(self.prelu(self.conv1(x)))
+        return conv_bias_act(self.conv2, conv_bias_act(self.conv1, x, self.prelu), residual=x)
 
 
 class HalfChannelConv5ResBlock(nn.Module):
@@ -49,7 +115,7 @@ class HalfChannelConv5ResBlock(nn.Module):
     def forward(self, x):
         t = self._side(self.conv1(x), self.conv2)
         t = self._side(self.conv3(t), self.conv4)
-        return self.prelu(x + self.conv5(t))
+        return conv_bias_act(self.conv5, t, self.prelu, residual=x)
 
 
 class FeadForward(nn.Module):
@@ -79,10 +145,10 @@ class SameChannelResEncoder(nn.Module):
         self.fea_L2_conv, self.fea_L3_conv, self.fea_L4_conv = down(), down(), down()
 
     def forward(self, x):
-        f1 = self.projection(x)
-        f2 = self.fea_L2_conv(f1)
-        f3 = self.fea_L3_conv(f2)
-        return f1, f2, f3, self.fea_L4_conv(f3)
+        f1 = run_conv_chain(self.projection, x)
+        f2 = run_conv_chain(self.fea_L2_conv, f1)
+        f3 = run_conv_chain(self.fea_L3_conv, f2)
+        return f1, f2, f3, run_conv_chain(self.fea_L4_conv, f3)
 
 
 class BasicResPixelShuffleGenerator(nn.Module):
@@ -100,8 +166,8 @@ class BasicResPixelShuffleGenerator(nn.Module):
         self.conv_last = nn.Conv2d(nf, 3, 3, 1, 1)
 
     def forward(self, feat, m):
-        t = self.prelu1(self.pixel_shuffle(self.upconv1(self.reconstruction(feat))))
-        return torch.clamp(self.conv_last(self.prelu2(self.HRconv(t))) + m, 0, 1)
+        t = self.prelu1(self.pixel_shuffle(conv_bias_act(self.upconv1, self.reconstruction(feat))))
+        return torch.clamp(conv_bias_act(self.conv_last, conv_bias_act(self.HRconv, t, self.prelu2)) + m, 0, 1)
 
 
 def resize(x, scale_factor):

@@ -12,7 +12,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .blocks import BasicResPixelShuffleGenerator, SameChannelResEncoder
+from .blocks import BasicResPixelShuffleGenerator, SameChannelResEncoder, run_conv_chain
 from .dcnv2 import DeformableConv2d
 from .deformable_attn import CrossDeformableAttentionBlockwFlow
 
@@ -40,11 +40,11 @@ class DCNInterFeatBuilderwithT(nn.Module):
     def forward(self, feat0, feat1, t):
         _, _, fh, fw = feat0.shape
         tt = t.repeat(1, 1, fh, fw)
-        m01 = self.convblock(torch.cat((feat0, feat1, tt), 1))
-        m10 = self.convblock(torch.cat((feat1, feat0, 1 - tt), 1))
+        m01 = run_conv_chain(self.convblock, torch.cat((feat0, feat1, tt), 1))
+        m10 = run_conv_chain(self.convblock, torch.cat((feat1, feat0, 1 - tt), 1))
         from0, ft0 = self.dcnt0(feat0, m01)
         from1, ft1 = self.dcnt1(feat1, m10)
-        return self.blendblock(torch.cat((from0, from1), 1)), ft0, ft1
+        return run_conv_chain(self.blendblock, torch.cat((from0, from1), 1)), ft0, ft1
 
 
 class DATwConstantnCv1(nn.Module):

@@ -17,7 +17,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from .blocks import FeadForward, HalfChannelConv5ResBlock, conv_prelu, resize
+from .blocks import FeadForward, HalfChannelConv5ResBlock, conv_bias_act, conv_prelu, resize
 from .warp import bwarp
 
 __all__ = ["Attn", "CrossDeformableAttentionBlockwFlow", "grouped_sample", "attention_over_samples", "fused_deformable_attention"]
@@ -150,7 +150,7 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
     def forward(self, feat_t, feat0, feat1, ft0, ft1):
         mv0 = self._get_movement_feats(feat_t, feat0, ft0)
         mv1 = self._get_movement_feats(feat_t, feat1, ft1)
-        raw0, raw1 = self.conv_res_offset(mv0), self.conv_res_offset(mv1)
+        raw0, raw1 = conv_bias_act(self.conv_res_offset, mv0), conv_bias_act(self.conv_res_offset, mv1)
         if self.n_groups == self.n_heads:
             attended = fused_deformable_attention(feat_t, feat0, feat1, raw0, raw1, ft0, ft1, *self.attn._weights(),
                                                   n_groups=self.n_groups, n_samples=self.n_samples, n_heads=self.n_heads,
