@@ -158,6 +158,13 @@ def test_fused_dattn_vs_oracle(vfi, cfg):
     out = fused_deformable_attention(*cu(q, f0, f1, raw0, raw1, ft0, ft1), *w, n_groups=nG, n_samples=nS, n_heads=nG,
                                      offset_scale=cfg["scale"])
     assert_close(out, ref, TOL, f"fused dattn {cfg}")
+    # same offsets delivered the way a bias-free channels-last conv writes them: (B,H,W,nG*nS*2) memory + separate bias
+    bias = det.normal(f"{tag}.ob", (nG * nS * 2,), std=0.3)
+    r0 = (raw0 - bias.view(1, -1, 1, 1)).cuda().contiguous(memory_format=torch.channels_last)
+    r1 = (raw1 - bias.view(1, -1, 1, 1)).cuda().contiguous(memory_format=torch.channels_last)
+    out_cl = fused_deformable_attention(*cu(q, f0, f1), r0, r1, *cu(ft0, ft1), *w, n_groups=nG, n_samples=nS, n_heads=nG,
+                                        offset_scale=cfg["scale"], offs_bias=bias.cuda())
+    assert_close(out_cl, ref, 2e-5, f"fused dattn, channels-last offsets + bias {cfg}")   # (raw - b) + b re-rounds the offsets
 
 
 def test_madat_golden(vfi, golden):

@@ -27,6 +27,8 @@ struct DattnArgs {
     const float *q, *feat[2], *offs[2], *ft[2];
     int64_t ft_sn, ft_sc, ft_sh, ft_sw;
     const float *Wq, *bq, *Wk, *bk, *Wv, *bv, *lin_x, *lin_y;
+    const float* obias;      // optional bias of the offset head (nG*nS*2), added before tanh
+    int offs_cl;             // offsets are channels-last: (B, H, W, nG*nS*2)
     float *out, *score[2];
     int B, H, W, nS;
     float offset_scale;
@@ -59,7 +61,7 @@ struct DattnCfg {
     static constexpr int MIN_BLOCKS = NG <= 4 ? 2 : 1;
 };
 
-template <int GC, int NG>
+template <int GC, int NG, bool OCL>
 __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::MIN_BLOCKS) dattn_kernel(DattnArgs a) {
     using Cfg = DattnCfg<GC, NG>;
     constexpr int C = Cfg::C, C4 = Cfg::C4, GCP = Cfg::GCP, SC = Cfg::SC, T = Cfg::THREADS;
@@ -180,18 +182,47 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
             // offsets are the only HBM-streamed operand of the loop (2*nG*nS floats per pixel and frame): keep the
             // next chunk's loads in flight across the two barriers of the current chunk
             float odx[SC], ody[SC];
+            // channels-last offsets: the 2*SC floats of a chunk are contiguous per pixel -> 128-bit loads when aligned
+            const int nOff = NG * nS * 2;
+            const float* offcl = a.offs[f] + ((int64_t)b * HW + pix) * nOff + (int64_t)g * nS * 2;
+            const bool cl_vec = OCL && (nS % SC == 0) && ((reinterpret_cast<uintptr_t>(offcl) & 15) == 0) && (SC % 2 == 0);
+            auto load_offs = [&](int s_first) {
+                if (OCL) {
+                    if (cl_vec) {
 #pragma unroll
-            for (int si = 0; si < SC; ++si) {
-                const int s = min(si, nS - 1);
-                odx[si] = ld_stream(offp + (int64_t)(2 * s) * HW);
-                ody[si] = ld_stream(offp + (int64_t)(2 * s + 1) * HW);
-            }
+                        for (int k = 0; k < SC / 2; ++k) {
+                            const float4 v = ld_stream4(offcl + 2 * s_first + 4 * k);
+                            odx[2 * k] = v.x; ody[2 * k] = v.y; odx[2 * k + 1] = v.z; ody[2 * k + 1] = v.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int si = 0; si < SC; ++si) {
+                            const int s = min(s_first + si, nS - 1);
+                            odx[si] = ld_stream(offcl + 2 * s);
+                            ody[si] = ld_stream(offcl + 2 * s + 1);
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int si = 0; si < SC; ++si) {
+                        const int s = min(s_first + si, nS - 1);
+                        odx[si] = ld_stream(offp + (int64_t)(2 * s) * HW);
+                        ody[si] = ld_stream(offp + (int64_t)(2 * s + 1) * HW);
+                    }
+                }
+            };
+            load_offs(0);
             for (int s0 = 0; s0 < nS; s0 += SC) {
                 float xs[SC][GC];
                 // ---- A: sample + partial logits ----
 #pragma unroll
                 for (int si = 0; si < SC; ++si) {
                     float dx = odx[si], dy = ody[si];
+                    if (a.obias != nullptr) {
+                        const int s = min(s0 + si, nS - 1);
+                        dx = __fadd_rn(dx, __ldg(a.obias + (g * nS + s) * 2));
+                        dy = __fadd_rn(dy, __ldg(a.obias + (g * nS + s) * 2 + 1));
+                    }
                     if (!a.coords_final) {
                         dx = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dx)), ftx);
                         dy = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dy)), fty);
@@ -207,14 +238,7 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
                         red[((si * NG + h) * NG + g) * 32 + lane] = d;
                     }
                 }
-                if (s0 + SC < nS) {
-#pragma unroll
-                    for (int si = 0; si < SC; ++si) {
-                        const int s = min(s0 + SC + si, nS - 1);
-                        odx[si] = ld_stream(offp + (int64_t)(2 * s) * HW);
-                        ody[si] = ld_stream(offp + (int64_t)(2 * s + 1) * HW);
-                    }
-                }
+                if (s0 + SC < nS) load_offs(s0 + SC);
                 __syncthreads();
                 // ---- C: head g: logits of this chunk, softmax state ----
                 {
@@ -312,7 +336,8 @@ template <int GC, int NG>
 static int launch_dattn(DattnArgs a, cudaStream_t st) {
     using Cfg = DattnCfg<GC, NG>;
     const size_t smem = (size_t)Cfg::SMEM_FLOATS * sizeof(float);
-    VFI_CUDA(cudaFuncSetAttribute(dattn_kernel<GC, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (a.offs_cl) VFI_CUDA(cudaFuncSetAttribute(dattn_kernel<GC, NG, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else VFI_CUDA(cudaFuncSetAttribute(dattn_kernel<GC, NG, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // warp tile: 32x1 pixels of a row (fewest cache lines per tap request); narrow images use 16x2 / 8x4
     a.tw_log2 = a.W >= 32 ? 5 : (a.W >= 16 ? 4 : 3);
     const char* env = getenv("VFI_DATTN_TW_LOG2");
@@ -321,7 +346,8 @@ static int launch_dattn(DattnArgs a, cudaStream_t st) {
     a.tiles_y = (int)ceil_div(a.H, 32 >> a.tw_log2);
     const int64_t tiles = (int64_t)a.B * a.tiles_x * a.tiles_y;
     const int blocks = (int)min64(tiles, (int64_t)kNumSMs * Cfg::MIN_BLOCKS);
-    dattn_kernel<GC, NG><<<blocks, Cfg::THREADS, smem, st>>>(a);
+    if (a.offs_cl) dattn_kernel<GC, NG, true><<<blocks, Cfg::THREADS, smem, st>>>(a);
+    else dattn_kernel<GC, NG, false><<<blocks, Cfg::THREADS, smem, st>>>(a);
     VFI_CHECK_LAUNCH("dattn_kernel");
     return VFI_OK;
 }
@@ -332,7 +358,8 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
                              const float* ft0, const float* ft1, const int64_t ft_strides[4], const float* Wq, const float* bq,
                              const float* Wk, const float* bk, const float* Wv, const float* bv, const float* lin_x,
                              const float* lin_y, float* out, float* score0, float* score1, int B, int C, int H, int W, int nG,
-                             int nS, int nH, float offset_scale, int coords_final, void* stream) {
+                             int nS, int nH, float offset_scale, int coords_final, const float* offs_bias, int offs_channels_last,
+                             void* stream) {
     using namespace vfi;
     VFI_REQUIRE(q && feat0 && feat1 && offs0 && offs1 && Wq && bq && Wk && bk && Wv && bv && lin_x && lin_y && out,
                 "vfi_dattn_f32: null pointer");
@@ -350,6 +377,7 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
     a.ft_sh = ft_strides ? ft_strides[2] : 0; a.ft_sw = ft_strides ? ft_strides[3] : 0;
     a.Wq = Wq; a.bq = bq; a.Wk = Wk; a.bk = bk; a.Wv = Wv; a.bv = bv;
     a.lin_x = lin_x; a.lin_y = lin_y;
+    a.obias = offs_bias; a.offs_cl = offs_channels_last;
     a.out = out; a.score[0] = score0; a.score[1] = score1;
     a.B = B; a.H = H; a.W = W; a.nS = nS;
     a.offset_scale = offset_scale;

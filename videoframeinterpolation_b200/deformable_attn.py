@@ -15,6 +15,7 @@ from typing import Optional
 
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from . import _lib
 from .blocks import FeadForward, HalfChannelConv5ResBlock, conv_bias_act, conv_prelu, resize
@@ -62,7 +63,7 @@ def attention_over_samples(q, kv, wq, bq, wk, bk, wv, bv, n_heads: int, want_sco
 
 def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torch.Tensor], ft1: Optional[torch.Tensor],
                                wq, bq, wk, bk, wv, bv, n_groups: int, n_samples: int, n_heads: int, offset_scale: float,
-                               coords_final: bool = False, want_scores: bool = False):
+                               coords_final: bool = False, want_scores: bool = False, offs_bias=None):
     """Sampler + attention over both frames in one kernel (vfi_dattn_f32).
 
     offs* (b, nG*nS*2, h, w): raw conv_res_offset outputs (``coords_final=False``: the kernel applies
@@ -70,7 +71,14 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
     """
     dev = _lib.require_cuda(q, feat0, feat1, offs0, offs1)
     q, feat0, feat1 = _lib.f32c(q), _lib.f32c(feat0), _lib.f32c(feat1)
-    offs0, offs1 = _lib.f32c(offs0), _lib.f32c(offs1)
+    # offsets are read in the layout the conv wrote them: channels-last (B,H,W,nG*nS*2) needs no transpose
+    offs_cl = (offs0.dim() == 4 and offs0.dtype == torch.float32 and not offs0.is_contiguous()
+               and offs0.is_contiguous(memory_format=torch.channels_last)
+               and offs1.dtype == torch.float32 and not offs1.is_contiguous()
+               and offs1.is_contiguous(memory_format=torch.channels_last))
+    if not offs_cl:
+        offs0, offs1 = _lib.f32c(offs0), _lib.f32c(offs1)
+    offs_bias = _lib.f32c(offs_bias)
     b, c, fh, fw = q.shape
     assert offs0.numel() == b * n_groups * n_samples * 2 * fh * fw and offs1.numel() == offs0.numel(), "offset shape"
     if not coords_final:
@@ -90,7 +98,8 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
                                         _lib.f32c(bk).data_ptr(), _w2d(wv).data_ptr(), _lib.f32c(bv).data_ptr(),
                                         _lib.linspace_m11(fw, dev).data_ptr(), _lib.linspace_m11(fh, dev).data_ptr(),
                                         out.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), b, c, fh, fw, n_groups, n_samples, n_heads,
-                                        float(offset_scale), 1 if coords_final else 0, _lib.stream_ptr(dev))
+                                        float(offset_scale), 1 if coords_final else 0, _lib.ptr(offs_bias), 1 if offs_cl else 0,
+                                        _lib.stream_ptr(dev))
     return (out, s0, s1) if want_scores else out
 
 
@@ -150,12 +159,16 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
     def forward(self, feat_t, feat0, feat1, ft0, ft1):
         mv0 = self._get_movement_feats(feat_t, feat0, ft0)
         mv1 = self._get_movement_feats(feat_t, feat1, ft1)
-        raw0, raw1 = conv_bias_act(self.conv_res_offset, mv0), conv_bias_act(self.conv_res_offset, mv1)
         if self.n_groups == self.n_heads:
+            # bias-free conv: the fused kernel adds conv_res_offset.bias itself (same fp32 order: conv + bias, then tanh)
+            co = self.conv_res_offset
+            raw0 = F.conv2d(mv0, co.weight, None, co.stride, co.padding)
+            raw1 = F.conv2d(mv1, co.weight, None, co.stride, co.padding)
             attended = fused_deformable_attention(feat_t, feat0, feat1, raw0, raw1, ft0, ft1, *self.attn._weights(),
                                                   n_groups=self.n_groups, n_samples=self.n_samples, n_heads=self.n_heads,
-                                                  offset_scale=self.offset_scale)
+                                                  offset_scale=self.offset_scale, offs_bias=co.bias)
         else:   # groups != heads: materialising kernels (still CUDA, never a CPU path)
+            raw0, raw1 = conv_bias_act(self.conv_res_offset, mv0), conv_bias_act(self.conv_res_offset, mv1)
             b, _, fh, fw = feat_t.shape
             shp = (b, self.n_groups * self.n_samples, 2, fh, fw)
             c0 = (self.offset_scale * torch.tanh(raw0)).view(shp) + ft0.unsqueeze(1)
