@@ -30,6 +30,8 @@ import torch  # noqa: E402
 METRIC = "DAT frames/sec @1080p"
 UNIT = "frames/s"
 H_RAW, W_RAW = 1080, 1920
+# dram__bytes_read.sum + dram__bytes_write.sum of the 1/2-res dattn launch, one ncu --set full capture (profiles/)
+TRAFFIC_DATTN_LV1 = None
 CPU_SAMPLE_HW = (256, 448)        # BASELINE.json configs[0]: the reference's own CPU-runnable case
 
 
@@ -45,7 +47,8 @@ def parse_args():
     ap.add_argument("--no-micro", action="store_true", help="skip the warp/splat micro-benchmark")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs under ncu only)")
-    ap.add_argument("--channels-last", type=int, default=0, help="run the cuDNN conv stacks around the hot path in NHWC")
+    ap.add_argument("--channels-last", type=int, default=1, help="run the cuDNN conv stacks around the hot path in NHWC (0 = NCHW)")
+    ap.add_argument("--graph", type=int, default=1, help="replay the forward from a CUDA graph (0 = eager launches from Python)")
     ap.add_argument("--tf32", type=int, default=1, help="allow TF32 in the cuDNN convs around the hot path (PyTorch default)")
     return ap.parse_args()
 
@@ -265,6 +268,15 @@ def run_vfi(args):
         a, b = padder.pad(h_x0.to(dev, non_blocking=True), h_x1.to(dev, non_blocking=True))
         h_out.copy_(padder.unpad(net.inference(a, b, t)), non_blocking=True)
 
+    graphed = None
+
+    def step_graph():
+        return graphed.replay()
+
+    def step_graph_e2e():
+        a, b = padder.pad(h_x0.to(dev, non_blocking=True), h_x1.to(dev, non_blocking=True))
+        h_out.copy_(padder.unpad(graphed(a, b)), non_blocking=True)
+
     def barrier():
         if world > 1:
             dist.barrier()
@@ -300,12 +312,26 @@ def run_vfi(args):
         clocks = clock.stop()
         ops = tm.summary()
         dattn_events = tm.records.get("vfi_dattn_f32", [])
+        # host enqueue time of the eager loop (no synchronisation inside): > GPU time means launch-bound
+        torch.cuda.synchronize()
+        h0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_device()
+        host_ms = (time.perf_counter() - h0) * 1e3 / args.steps
+        torch.cuda.synchronize()
+        eager_ms = total_ms / args.steps
+        if args.graph:
+            graphed = v.GraphedInference(net, d_x0, d_x1, t)
+            for _ in range(3):
+                step_graph()
+            total_ms = timed(step_graph, args.steps)
         if args.no_e2e:
             e2e_ms = float("nan")
         else:
+            fn = step_graph_e2e if args.graph else step_e2e
             for _ in range(2):
-                step_e2e()
-            e2e_ms = timed(step_e2e, args.steps)
+                fn()
+            e2e_ms = timed(fn, args.steps)
 
     ms_per_step = total_ms / args.steps
     value = world * P / (ms_per_step / 1e3)
@@ -319,20 +345,25 @@ def run_vfi(args):
     alg = bytes_dattn(P, 72, ph // 2, pw // 2, 8, 32)
     achieved = alg / lv1_ms / 1e6 if lv1_ms > 0 else 0.0
     roofline = {"kernel": "dattn_kernel<9,8> (fused sampler+attention, 1/2 res)", "bound": "hbm", "achieved": achieved,
-                "peak": hbm_peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "peak": hbm_peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / hbm_peak,
                 "algorithmic_bytes_per_launch": alg, "ms_per_launch": lv1_ms,
-                "note": "per-pixel work is ~170 kFLOP of fp32 FMA (no fp32 tensor path): bounded by max(HBM, FP32 FMA)"}
+                "note": "gather kernel: 18.4k data-dependent taps + ~170 kFLOP fp32 per pixel; binding resource is the L1/LSU request rate "
+                        "(gather floor ~4.3 ms) and fp32 FMA (~2.5 ms), not HBM (DESIGN.md 4.3); traffic from profiles/ ncu capture",
+                "traffic": TRAFFIC_DATTN_LV1 if (P == 1 and (ph, pw) == (1088, 1920)) else None}
     op_ms = {k: {"calls_per_step": c / args.steps, "ms_per_step": ms / args.steps} for k, (c, ms) in ops.items()}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": workload_name(args), "pairs_per_gpu": P, "global_pairs_per_step": P * world,
-                       "parallelism": f"frame-pair sharding x{world}, no collective", "conv_math": "tf32" if args.tf32 else "fp32",
+                       "parallelism": f"frame-pair sharding x{world}, no collective", "conv_layout": "channels_last" if args.channels_last else "nchw", "conv_math": "tf32" if args.tf32 else "fp32",
+                       "launch": "CUDA graph replay" if args.graph else "eager", "eager_ms_per_step": eager_ms,
+                       "eager_host_enqueue_ms_per_step": host_ms,
                        "l2": "inputs + activations per step (>1 GB) exceed the 126 MB L2"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * h_x0.numel() * 4, "d2h_bytes_per_step": h_out.numel() * 4,
                     "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "vfi_ops_ms": op_ms}
+            "gpu_launches": int(launches),      # vfi_b200 kernels per K steps (counted on the eager pass; the graph replays the same kernels)
+            "clocks": clocks, "roofline": roofline, "vfi_ops_ms": op_ms}
 
     if rank == 0:
         if not args.no_micro:

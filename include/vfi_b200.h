@@ -80,6 +80,8 @@ int vfi_bwarp_f32(const float* img, const float* flow, const float* lin_x, const
 int vfi_splat_f32(const float* in, const float* flow, const float* metric, const float* t,
                   float* num, float* den, int B, int C, int H, int W,
                   int weight_mode, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
+/* Bytes of scratch vfi_splat_fused_f32 needs for this shape (68 B per source pixel: 4 claim slots + 4 slot weights
+ * + list head + 4 overflow nodes; independent of C).  vfi_splat_f32 itself needs none (workspace may be NULL). */
 size_t vfi_splat_workspace_bytes(int B, int C, int H, int W);
 
 /* out = num / f(den) per eps_mode; blank_mask (B,1,H,W) uint8, optional: f(den) < blank_threshold
@@ -88,10 +90,11 @@ int vfi_splat_normalize_f32(const float* num, const float* den, float* out, uint
                             int B, int C, int H, int W, int eps_mode, float eps_value, float blank_threshold,
                             void* stream);
 
-/* Fused single-call form of softsplat(tenIn, tenFlow, tenMetric, strMode) for avg/linear/soft:
- * tiled gather-form splat that owns each output tile, so the divide happens in the same kernel and no
- * zero-fill / normalise passes touch HBM.  Same results as vfi_splat_f32 + vfi_splat_normalize_f32 up to
- * fp32 summation order. */
+/* Fused single-call form of softsplat(tenIn, tenFlow, tenMetric, strMode) for sum/avg/linear/soft in GATHER form:
+ * a link pass records, per target pixel, which source pixels hit it (integer CAS / exchange only), then one thread
+ * per target pixel sums its sources for every plane and divides in the same pass -- no floating-point atomics,
+ * no zero-fill / normalise passes over HBM, bitwise reproducible.  Same results as vfi_splat_f32 +
+ * vfi_splat_normalize_f32 up to fp32 summation order.  workspace: vfi_splat_workspace_bytes. */
 int vfi_splat_fused_f32(const float* in, const float* flow, const float* metric, float* out,
                         int B, int C, int H, int W, int weight_mode, int eps_mode, float eps_value,
                         void* workspace, size_t workspace_bytes, void* stream);
@@ -149,6 +152,26 @@ size_t vfi_dcn_workspace_bytes(int B, int Cin, int Cout, int H, int W, int kh, i
  * Same fp32 operation order as the separate PyTorch ops (bit-identical to them). */
 int vfi_bias_act_f32(const float* y, const float* bias, const float* slope, const float* residual, float* out,
                      int B, int C, int H, int W, int channels_last, int residual_mode, void* stream);
+
+/* ---- 3x3 / stride 1 / pad 1 convolution on the tensor cores (nn.Conv2d(k=3, s=1, p=1) in
+ * modules/basic_blocks.py:13-73, modules/cnn_encoders.py:6-42, modules/generator.py:7-24, and conv_res_offset of
+ * modules/deformable_attn.py:56-64) with the epilogue of vfi_bias_act_f32 fused in.  TF32 inputs (weights rounded
+ * to nearest, activations truncated by the tensor core), fp32 accumulation: the arithmetic class of PyTorch's default
+ * cudnn.allow_tf32 = True.  Callers that need fp32 convolutions keep cuDNN.
+ *   x        NHWC fp32: pixel (b,y,x) at x + ((b*H + y)*W + x) * x_pix_stride, Cin channels from there
+ *            (a channel slice of a wider tensor is x_pix_stride > Cin); Cin % 4 == 0, x_pix_stride % 4 == 0.
+ *   wprep    vfi_conv3x3_prep_f32(weight (Cout,Cin,3,3) contiguous) -> vfi_conv3x3_prep_bytes(Cout, Cin) bytes.
+ *   out      out_channels_last = 1: NHWC with out_c_total channels per pixel; 0: NCHW (B, out_c_total, H, W);
+ *            channels [0, Cout) are written.  residual (mode 1: before the activation, 2: after) has the layout of
+ *            out with res_c_total channels.  bias / slope (Cout) may be NULL.
+ * vfi_conv3x3_supported: 1 when this (Cin, x_pix_stride, Cout) runs here (weights of a Cout tile must fit in shared
+ * memory: Cin <= 72 for a 72-wide tile). */
+int vfi_conv3x3_supported(int Cin, int x_pix_stride, int Cout);
+size_t vfi_conv3x3_prep_bytes(int Cout, int Cin);
+int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout, int Cin, void* stream);
+int vfi_conv3x3_f32(const float* x, const float* wprep, const float* bias, const float* slope, const float* residual,
+                    float* out, int B, int H, int W, int Cin, int x_pix_stride, int Cout, int out_channels_last,
+                    int out_c_total, int res_c_total, int residual_mode, void* stream);
 
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */

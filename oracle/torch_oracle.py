@@ -27,7 +27,7 @@ __all__ = [
     "library_ops", "grid_sample_bilinear", "bwarp", "splat_sum", "fwarp", "softsplat",
     "fwarp_using_two_frames", "fwarp_mframes", "deform_conv2d", "dcn_block", "dcn_given_offset",
     "ref_coords", "dsample", "attn", "dat_block", "madat_ref_feats", "madat_attn",
-    "layer_norm_c", "dat_forward", "dat_config", "dat_param_shapes", "input_pad", "input_unpad", "count_params",
+    "layer_norm_c", "conv3x3_tf32", "tf32_truncate", "tf32_round", "dat_forward", "dat_config", "dat_param_shapes", "input_pad", "input_unpad", "count_params",
 ]
 
 _USE_LIBRARY = False
@@ -627,3 +627,29 @@ def dat_param_shapes(cfg: Optional[dict] = None) -> Dict[str, tuple]:
     conv(g + "upconv1", 4 * nf, nf); prelu(g + "prelu1", nf)
     conv(g + "HRconv", nf, nf); prelu(g + "prelu2", nf); conv(g + "conv_last", 3, nf)
     return s
+
+
+# ---- f2: 3x3 convolutions of the conv stacks in TF32 -------------------------------------------
+def tf32_truncate(x: torch.Tensor) -> torch.Tensor:
+    """fp32 -> TF32 by dropping the low 13 mantissa bits (what the tensor core does to an fp32 operand)."""
+    return (x.contiguous().view(torch.int32) & ~0x1FFF).view(torch.float32)
+
+
+def tf32_round(x: torch.Tensor) -> torch.Tensor:
+    """fp32 -> TF32 round-to-nearest, ties away from zero (cvt.rna.tf32.f32)."""
+    return ((x.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+
+
+def conv3x3_tf32(x, weight, bias=None, slope=None, residual=None, residual_after_act=False):
+    """nn.Conv2d(k=3, s=1, p=1) [+ residual] [+ per-channel PReLU] as the reference's GPU runs it under PyTorch's
+    default ``cudnn.allow_tf32 = True`` (modules/basic_blocks.py:13-73, modules/cnn_encoders.py:6-42,
+    modules/generator.py:7-24): operands reduced to TF32 (activations truncated, weights rounded), products and sums
+    exact (float64 here; fp32 accumulation order is the implementation's).  Returns float64."""
+    y = F.conv2d(tf32_truncate(x).double(), tf32_round(weight).double(), None if bias is None else bias.double(), padding=1)
+    if residual is not None and not residual_after_act:
+        y = residual.double() + y
+    if slope is not None:
+        y = torch.where(y > 0, y, slope.double().view(1, -1, 1, 1) * y)
+    if residual is not None and residual_after_act:
+        y = residual.double() + y
+    return y

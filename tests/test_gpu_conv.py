@@ -1,0 +1,118 @@
+"""GPU parity of the tcgen05 3x3 convolution through the C ABI.
+
+The kernel computes in TF32 (activations truncated by the tensor core, weights rounded to nearest) with fp32
+accumulation -- PyTorch's default conv arithmetic on a GPU.  It is checked (a) against the oracle's exact TF32
+restatement at 1e-5, and (b) against the fp32 convolution at a TF32-sized tolerance, on the shapes and epilogues the
+DAT model uses, including ragged tiles, channel-slice inputs, Cout tiling and both output layouts."""
+import pytest
+import torch
+import torch.nn as nn
+
+import oracle
+from _util import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def tf32():
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = True
+    yield
+    torch.backends.cudnn.allow_tf32 = old
+
+
+def _case(B, Cin, Cout, H, W, prelu=False, res=0, ocl=True, slice_of=None, bias=True, seed=0):
+    from videoframeinterpolation_b200 import conv as vc
+    g = torch.Generator().manual_seed(seed)
+    conv = nn.Conv2d(Cin, Cout, 3, 1, 1, bias=bias)
+    with torch.no_grad():
+        conv.weight.copy_(torch.randn(conv.weight.shape, generator=g) * 0.1)
+        if bias:
+            conv.bias.copy_(torch.randn(Cout, generator=g))
+    conv = conv.cuda()
+    ctot = slice_of or Cin
+    xfull = torch.randn(B, ctot, H, W, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    x = xfull[:, ctot - Cin:]
+    slope = torch.rand(Cout, generator=g).cuda() if prelu else None
+    r = torch.randn(B, Cout, H, W, generator=g).cuda().contiguous(memory_format=torch.channels_last) if res else None
+    with torch.no_grad():
+        assert vc.eligible(conv, x)
+        y = vc.conv3x3(conv, x, slope, r, residual_after_act=(res == 2), out_channels_last=ocl)
+    assert y.shape == (B, Cout, H, W)
+    assert y.is_contiguous(memory_format=torch.channels_last) if (ocl and Cout > 1) else y.is_contiguous()
+    ref = oracle.conv3x3_tf32(x.cpu(), conv.weight.detach().cpu(), None if not bias else conv.bias.detach().cpu(),
+                              None if slope is None else slope.cpu(), None if r is None else r.cpu(), res == 2)
+    assert rel_err(y.double().cpu(), ref) <= 1e-5
+    fp32 = torch.nn.functional.conv2d(x.double().cpu(), conv.weight.detach().double().cpu(),
+                                      None if not bias else conv.bias.detach().double().cpu(), padding=1)
+    if not prelu and not res:
+        assert rel_err(y.double().cpu(), fp32) <= 3e-3
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(B=1, Cin=72, Cout=72, H=16, W=8),                               # exactly one tile
+    dict(B=2, Cin=72, Cout=72, H=45, W=37, prelu=True, res=1),           # ragged tiles, ResBlock tail
+    dict(B=1, Cin=72, Cout=72, H=33, W=20, prelu=True, res=2),
+    dict(B=1, Cin=72, Cout=72, H=35, W=29, ocl=False),                   # planar output (feeds the gather kernels)
+    dict(B=1, Cin=72, Cout=512, H=33, W=40, bias=False),                 # conv_res_offset: 8 Cout tiles
+    dict(B=1, Cin=72, Cout=288, H=32, W=32),                             # upconv1
+    dict(B=1, Cin=72, Cout=3, H=40, W=24, ocl=False),                    # conv_last
+    dict(B=1, Cin=72, Cout=2, H=24, W=24),                               # flow head
+    dict(B=1, Cin=36, Cout=36, H=32, W=24, prelu=True, slice_of=72),     # HalfChannelConv5ResBlock side conv (half chunk)
+    dict(B=3, Cin=64, Cout=64, H=17, W=9, prelu=True),
+])
+def test_conv3x3_vs_oracle(tf32, cfg):
+    _case(**cfg)
+
+
+def test_conv3x3_full_size_properties(tf32):
+    """1/2-res 1080p shape: linearity in the input and agreement with cuDNN's TF32 convolution."""
+    from videoframeinterpolation_b200 import conv as vc
+    torch.manual_seed(1)
+    conv = nn.Conv2d(72, 72, 3, 1, 1).cuda()
+    x = torch.randn(1, 72, 544, 960, device="cuda").contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        y = vc.conv3x3(conv, x)
+        y2 = vc.conv3x3(conv, 2.0 * x)              # scaling by 2 is exact in TF32
+        b = conv.bias.view(1, -1, 1, 1)
+        assert torch.equal(y2 - b, 2.0 * (y - b)) or rel_err(y2 - b, 2.0 * (y - b)) <= 1e-6
+        ref = conv(x)
+        assert rel_err(y, ref) <= 2e-3
+
+
+def test_conv3x3_not_used_when_tf32_is_off():
+    from videoframeinterpolation_b200 import conv as vc
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        conv = nn.Conv2d(72, 72, 3, 1, 1).cuda()
+        x = torch.randn(1, 72, 16, 16, device="cuda").contiguous(memory_format=torch.channels_last)
+        with torch.no_grad():
+            assert not vc.eligible(conv, x)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+
+
+def test_dat_forward_tc_convs_match_fp32_convs(tf32):
+    """Whole DAT forward (channels-last) with the tensor-core convs vs the same model with fp32 cuDNN convs."""
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.workloads import init_dat_weights
+    torch.manual_seed(0)
+    net = init_dat_weights(v.DATwConstantnCv1(v.default_args())).cuda().eval().to(memory_format=torch.channels_last)
+    g = torch.Generator().manual_seed(3)
+    x0 = torch.rand(1, 3, 128, 192, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    x1 = torch.rand(1, 3, 128, 192, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    t = torch.full((1, 1, 1, 1), 0.5, device="cuda")
+    from videoframeinterpolation_b200 import _lib
+    with torch.no_grad():
+        _lib.reset_launch_count()
+        y_tc = net.inference(x0, x1, t)
+        n_tc = _lib.launch_count()
+        torch.backends.cudnn.allow_tf32 = False
+        _lib.reset_launch_count()
+        y_fp32 = net.inference(x0, x1, t)
+        n_fp32 = _lib.launch_count()
+    assert n_tc != n_fp32, "the tensor-core conv path did not run"
+    assert float((y_tc - y_fp32).abs().max()) <= 2e-2
+    assert float((y_tc - y_fp32).abs().mean()) <= 2e-3

@@ -129,8 +129,9 @@ def test_splat_mass_conservation_1080p(vfi):
 # ---- conv epilogue (bias + PReLU + residual), SURVEY.md 8f row f2 ---------------------------------
 @pytest.mark.parametrize("cl", [False, True])
 @pytest.mark.parametrize("shape", [(2, 72, 17, 24), (1, 3, 9, 7), (1, 76, 5, 6)])
-def test_conv_epilogue_bit_identical_to_torch_ops(vfi, cl, shape):
+def test_conv_epilogue_bit_identical_to_torch_ops(vfi, cl, shape, monkeypatch):
     from videoframeinterpolation_b200.blocks import conv_bias_act
+    monkeypatch.setenv("VFI_CONV_ALGO", "cudnn")      # this test is about the epilogue kernel behind a cuDNN conv
     B, C, H, W = shape
     torch.manual_seed(1)
     conv = torch.nn.Conv2d(C, C, 3, 1, 1).cuda()

@@ -9,6 +9,7 @@ from .dcnv2 import deform_conv2d, DeformableConv2d, DeformableConv2dGivenOffset
 from .deformable_attn import Attn, CrossDeformableAttentionBlockwFlow
 from .madat import DeformAttnwMotion, DATwithMotionEstimation
 from .dat import DATwConstantnCv1, DCNInterFeatBuilderwithT, InputPadder, default_args
+from .graph import GraphedInference
 
 FunctionSoftsplat = softsplat   # name used by BASELINE.json's north_star for the same four-argument call
 

@@ -11,6 +11,7 @@ import torch.nn.functional as F
 
 
 from . import _lib
+from . import conv as _conv
 
 
 def _fusable(x: torch.Tensor, conv: nn.Conv2d) -> bool:
@@ -24,6 +25,8 @@ def conv_bias_act(conv: nn.Conv2d, x: torch.Tensor, prelu: nn.PReLU = None, resi
     (vfi_bias_act_f32).  Same arithmetic order as ``prelu(residual + conv(x))`` / ``residual + conv(x)`` in PyTorch, which
     runs bias add, PReLU and residual add as three strided elementwise kernels.  Training (grad enabled) and CPU
     tensors take the plain PyTorch route."""
+    if _conv.eligible(conv, x):      # tcgen05 implicit GEMM with the epilogue fused (TF32, as cuDNN's default)
+        return _conv.conv3x3(conv, x, None if prelu is None else prelu.weight, residual, residual_after_act)
     if not _fusable(x, conv):
         y = conv(x)
         if residual is not None and not residual_after_act:

@@ -1,0 +1,95 @@
+"""3x3 / stride-1 convolutions of the DAT conv stacks on the tcgen05 tensor cores (``csrc/conv3x3.cu``; SURVEY.md 8f
+row f2).  Used by ``blocks.conv_bias_act`` for channels-last fp32 CUDA tensors at inference when PyTorch's own switch
+``torch.backends.cudnn.allow_tf32`` permits TF32 convolutions (its default, and therefore the arithmetic the reference
+runs on a GPU); everything else stays on cuDNN.  ``VFI_CONV_ALGO=cudnn`` disables it, ``=tc`` makes ineligible calls
+raise instead of falling back to cuDNN.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+def _algo() -> str:
+    return os.environ.get("VFI_CONV_ALGO", "auto")
+
+
+def _nhwc_pixel_stride(x: torch.Tensor) -> Optional[int]:
+    """Pixel stride (floats) when x (B,C,H,W) is NHWC-dense or a channel slice of an NHWC tensor, else None."""
+    if x.dim() != 4:
+        return None
+    B, C, H, W = x.shape
+    sb, sc, sh, sw = x.stride()
+    if C > 1 and sc != 1:
+        return None
+    if sw < C or (H > 1 and sh != W * sw) or (B > 1 and sb != H * W * sw):
+        return None
+    return sw
+
+
+def eligible(conv: nn.Conv2d, x: torch.Tensor) -> bool:
+    if _algo() == "cudnn" or not torch.backends.cudnn.allow_tf32:
+        return False
+    if not (type(conv) is nn.Conv2d and conv.kernel_size == (3, 3) and conv.stride == (1, 1) and conv.padding == (1, 1)
+            and conv.dilation == (1, 1) and conv.groups == 1 and conv.padding_mode == "zeros"):
+        return False
+    if not (x.is_cuda and x.dtype == torch.float32 and not torch.is_grad_enabled() and x.data_ptr() % 16 == 0):
+        return False
+    ps = _nhwc_pixel_stride(x)
+    if ps is None:
+        return False
+    return bool(_lib.lib().vfi_conv3x3_supported(conv.in_channels, ps, conv.out_channels))
+
+
+def prepared_weight(conv: nn.Conv2d) -> torch.Tensor:
+    """TF32-rounded, UMMA-ordered copy of conv.weight, cached on the module and rebuilt when the weight changes."""
+    w = conv.weight
+    key = (w.data_ptr(), w._version, str(w.device))
+    cached = getattr(conv, "_vfi_wprep", None)
+    if cached is not None and cached[0] == key:
+        return cached[1]
+    cout, cin = w.shape[:2]
+    nbytes = _lib.lib().vfi_conv3x3_prep_bytes(cout, cin)
+    wp = torch.empty(nbytes // 4, dtype=torch.float32, device=w.device)
+    wc = w.detach().contiguous()          # (Cout, Cin, 3, 3) row-major whatever the module's memory format
+    _lib.call("vfi_conv3x3_prep_f32", w.device, wc.data_ptr(), wp.data_ptr(), cout, cin, _lib.stream_ptr(w.device))
+    object.__setattr__(conv, "_vfi_wprep", (key, wp))
+    return wp
+
+
+def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tensor] = None,
+            residual: Optional[torch.Tensor] = None, residual_after_act: bool = False, use_bias: bool = True,
+            out_channels_last: bool = True) -> torch.Tensor:
+    """``act(residual + conv(x) + bias)`` in one kernel; x must satisfy :func:`eligible`."""
+    dev = _lib.require_cuda(x, residual)
+    B, Cin, H, W = x.shape
+    Cout = conv.out_channels
+    ps = _nhwc_pixel_stride(x)
+    if ps is None:
+        raise _lib.VfiError("conv3x3: x must be channels-last (or a channel slice of a channels-last tensor)")
+    wp = prepared_weight(conv)
+    if out_channels_last:
+        out = torch.empty((B, H, W, Cout), dtype=torch.float32, device=dev).permute(0, 3, 1, 2)
+    else:
+        out = torch.empty((B, Cout, H, W), dtype=torch.float32, device=dev)
+    res, res_c, mode = None, Cout, 0
+    if residual is not None:
+        if out_channels_last:
+            rps = _nhwc_pixel_stride(residual)
+            res = residual if rps is not None else residual.contiguous(memory_format=torch.channels_last)
+            res_c = rps if rps is not None else Cout
+        else:
+            res = residual.contiguous()
+        mode = 2 if residual_after_act else 1
+    slope = None
+    if prelu_weight is not None:
+        slope = prelu_weight if prelu_weight.numel() == Cout else prelu_weight.expand(Cout).contiguous()
+    bias = conv.bias if use_bias else None
+    _lib.call("vfi_conv3x3_f32", dev, x.data_ptr(), wp.data_ptr(), _lib.ptr(bias), _lib.ptr(slope), _lib.ptr(res), out.data_ptr(),
+              B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, Cout, res_c, mode, _lib.stream_ptr(dev))
+    return out

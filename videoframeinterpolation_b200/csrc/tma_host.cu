@@ -1,6 +1,7 @@
 // Host side of tma.cuh: tensor-map encoding through the driver entry point (resolved at run time so the
 // library still loads on a machine without libcuda.so.1, e.g. the CPU-only build container).
 #include "tma.cuh"
+#include "umma.cuh"
 #include "vfi_common.cuh"
 
 namespace vfi {
@@ -40,6 +41,31 @@ int make_tmap_f32_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed with CUresult %d (dims %llu x %llu x %llu, box %u x %u x %u)", (int)r,
                   (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)d2, b0, b1, b2);
+        return VFI_ERR_CUDA;
+    }
+    return VFI_OK;
+}
+
+int make_tmap_f32_nd(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                     const uint32_t* box) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled is not available from the driver");
+        return VFI_ERR_CUDA;
+    }
+    cuuint64_t d[5], s[4];
+    cuuint32_t b[5], e[5];
+    for (int i = 0; i < rank; ++i) {
+        d[i] = dims[i];
+        b[i] = box[i];
+        e[i] = 1;
+        if (i > 0) s[i - 1] = strides_bytes[i - 1];
+    }
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, e,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (rank %d) failed with CUresult %d", rank, (int)r);
         return VFI_ERR_CUDA;
     }
     return VFI_OK;

@@ -18,6 +18,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from . import _lib
+from . import conv as _conv
 from .blocks import FeadForward, HalfChannelConv5ResBlock, conv_bias_act, conv_prelu, resize
 from .warp import bwarp
 
@@ -162,8 +163,11 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
         if self.n_groups == self.n_heads:
             # bias-free conv: the fused kernel adds conv_res_offset.bias itself (same fp32 order: conv + bias, then tanh)
             co = self.conv_res_offset
-            raw0 = F.conv2d(mv0, co.weight, None, co.stride, co.padding)
-            raw1 = F.conv2d(mv1, co.weight, None, co.stride, co.padding)
+            if _conv.eligible(co, mv0) and _conv.eligible(co, mv1):
+                raw0, raw1 = _conv.conv3x3(co, mv0, use_bias=False), _conv.conv3x3(co, mv1, use_bias=False)
+            else:
+                raw0 = F.conv2d(mv0, co.weight, None, co.stride, co.padding)
+                raw1 = F.conv2d(mv1, co.weight, None, co.stride, co.padding)
             attended = fused_deformable_attention(feat_t, feat0, feat1, raw0, raw1, ft0, ft1, *self.attn._weights(),
                                                   n_groups=self.n_groups, n_samples=self.n_samples, n_heads=self.n_heads,
                                                   offset_scale=self.offset_scale, offs_bias=co.bias)
