@@ -4,18 +4,27 @@
 // (the arithmetic PyTorch's default `cudnn.allow_tf32 = True` gives the reference), with the bias + residual + PReLU
 // epilogue of epilogue.cu fused in.
 //
-// Persistent kernel, one CTA per SM, 6 warps:
-//   warp 0  producer : per tile and per 8-channel chunk ONE 5-D TMA box {4 ch, 10 x, 18 y, 2 ch-quads, 1 image} of the
-//                      NHWC input (zero-filled outside the image = the conv padding) into a ring of stages.  The box
-//                      lands as [ch-quad][y][x][16 B], i.e. 8 horizontally adjacent pixels x 16 B = one UMMA core
-//                      matrix, so the 9 taps of the 3x3 stencil are 9 *descriptor offsets* into the same stage --
-//                      no im2col, every input byte is fetched once per tile (+ halo).
-//   warp 1  MMA      : tcgen05.mma.cta_group::1.kind::tf32, M = 128 pixels (8 x 16 tile), N = Cout tile, K = 8 per
-//                      instruction; 9 taps x Cin/8 chunks accumulate into one of two TMEM accumulators.  The whole
-//                      weight tensor of the Cout tile (<= 187 KB, pre-rounded to TF32 and pre-arranged by
-//                      conv3x3_prep_kernel) stays resident in shared memory for the life of the CTA.
-//   warps 2-5 epilogue: tcgen05.ld (lane = pixel) -> bias, residual, PReLU -> global; overlaps the next tile's MMAs
-//                      through the second accumulator.
+// Formulation.  With shared-memory operands tcgen05.mma streams the M-side operand at ~64 B/clk, i.e. an
+// M = 128, K = 8 (tf32) instruction costs >= 64 clk whatever N is (measured: 75 + 0.25 N clk), so N = Cout = 72 leaves
+// the tensor core two thirds idle.  The three vertical taps are therefore concatenated along N:
+//     P[dy][r, x, co] = sum_dx sum_ci X[r, x + dx, ci] * W[co, ci, dy, dx]         (one MMA chain, N = 3 * Cout)
+//     out[y, x, co]   = P[-1][y - 1, x, co] + P[0][y, x, co] + P[+1][y + 1, x, co]
+// The tile is 8 columns x 16 input rows stored COLUMN-major (M index = 16 * column + row), so the row shift of the
+// second line is a +-1 lane shift inside a half-warp of the epilogue (two __shfl per value) and the first and last
+// row of the tile are halo: 14 output rows per tile.  MMAs per tile: 3 (dx) x Cin/8 with N = 216 instead of
+// 9 x Cin/8 with N = 72.
+//
+// Persistent kernel, one CTA per SM, 10 warps:
+//   warp 0  producer : per tile and per 24-channel stage ONE 5-D TMA box {4 ch, 16 y, 10 x, 6 ch-quads, 1 image} of
+//                      the NHWC input (zero-filled outside the image = the conv padding).  It lands as
+//                      [ch-quad][x][y][16 B]: 8 vertically adjacent pixels x 16 B = one UMMA core matrix
+//                      (K-major, no swizzle), and the horizontal taps are descriptor offsets of 256 B -- no im2col.
+//   warp 1  MMA      : tcgen05.mma.cta_group::1.kind::tf32, M = 128, N = 3 * (Cout tile), accumulating in one of two
+//                      TMEM accumulators.  The weights of the Cout tile (<= 187 KB, RN-rounded to TF32 and arranged by
+//                      conv3x3_prep_kernel) stay resident in shared memory for the life of the CTA.
+//   warps 2-9 epilogue: tcgen05.ld (lane = pixel; two warps per TMEM lane quadrant, alternate 8-channel chunks) ->
+//                      plane sum -> bias, residual, PReLU -> global (one 32-byte sector per thread and chunk);
+//                      overlaps the next tile's MMAs through the second accumulator.
 #include <stdlib.h>
 
 #include "umma.cuh"
@@ -23,51 +32,67 @@
 
 namespace vfi {
 
-constexpr int kCvTW = 8, kCvTH = 16;                    // output tile: an 8-pixel row segment = one 8-row core-matrix group
-constexpr int kCvM = kCvTW * kCvTH;                     // 128 = UMMA M
-constexpr int kCvWinW = kCvTW + 2, kCvWinH = kCvTH + 2;
-constexpr int kCvStageBytes = 2 * kCvWinW * kCvWinH * 16;   // one 8-channel chunk of the window: 5760 B
-constexpr int kCvThreads = 192;
-constexpr int kCvMaxStages = 12;
+constexpr int kCvTW = 8, kCvRows = 16;                  // tile: 8 columns x 16 input rows (M = 128, column-major)
+constexpr int kCvTH = kCvRows - 2;                      // output rows per tile
+constexpr int kCvM = kCvTW * kCvRows;
+constexpr int kCvWinW = kCvTW + 2;
+constexpr int kCvKSteps = 3;                            // 8-channel k-steps per stage
+constexpr int kCvQuadBytes = kCvWinW * kCvRows * 16;    // one 4-channel quad of the window: 2560 B
+constexpr int kCvStageBytes = 2 * kCvKSteps * kCvQuadBytes;   // 15360 B
+constexpr int kCvThreads = 320;                         // producer warp, MMA warp, 8 epilogue warps
+constexpr int kCvMaxStages = 4;
 constexpr int kCvSmemMax = 232448;                      // 227 KB opt-in limit
-constexpr int kCvAccStride = 128;                       // TMEM columns between the two accumulators
+constexpr int kCvAccStride = 256;                       // TMEM columns between the two accumulators
 
 struct ConvArgs {
-    const float* wprep;   // this Cout tile: [tap 9][chunk][k-half 2][n NPAD][4] floats
+    const float* wprep;   // this Cout tile: [dx 3][chunk nchunkP][k-half 2][n = dy * NPAD + co][4] floats
     const float* bias;    // cn floats or null
     const float* slope;   // cn floats or null
     const float* res;     // residual (same layout family as out) or null
     float* out;
-    int B, H, W, nchunk, cn;
+    int B, H, W, nstage_tile, cn;   // nstage_tile = stages (24 channels) per tile
     int res_mode;         // 0 none, 1 add before the activation, 2 add after it
-    int vec;              // NHWC out/res with 16-byte aligned pixel rows: float4 path
+    int vec;              // NHWC out/res: 1 = 16-byte aligned pixel rows (float4), 2 = 32-byte aligned (256-bit accesses)
     int64_t out_sb, out_sy, out_sx, out_sc;   // element strides of out
     int64_t res_sb, res_sy, res_sx, res_sc;
     int stages, tiles_x, tiles_y, n_tiles;
     int dbg;              // bring-up switches (VFI_CONV_DBG): 1 = no TMA loads, 2 = no epilogue stores, 4 = no MMAs
 };
 
-// weight (Cout, Cin, 3, 3) contiguous -> per Cout tile of T channels: [tap][chunk][k-half][n NPAD][4], RN-rounded to TF32
+// weight (Cout, Cin, 3, 3) contiguous -> per Cout tile of T channels:
+// [dx][chunk nchunkP][k-half][n = dy * NPAD + co][4], RN-rounded to TF32, zero where co / ci are padding
 __global__ void conv3x3_prep_kernel(const float* __restrict__ w, float* __restrict__ wprep, int Cout, int Cin, int T, int NPAD,
-                                    int n_nt) {
-    const int nchunk = (Cin + 7) / 8;
-    const int64_t per_tile = (int64_t)9 * nchunk * 2 * NPAD * 4;
+                                    int n_nt, int nchunkP) {
+    const int64_t per_tile = (int64_t)3 * nchunkP * 2 * 3 * NPAD * 4;
     const int64_t total = per_tile * n_nt;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         int64_t r = i;
         const int e = (int)(r % 4); r /= 4;
-        const int n = (int)(r % NPAD); r /= NPAD;
+        const int n = (int)(r % (3 * NPAD)); r /= 3 * NPAD;
         const int kh = (int)(r % 2); r /= 2;
-        const int c = (int)(r % nchunk); r /= nchunk;
-        const int tap = (int)(r % 9); r /= 9;
+        const int c = (int)(r % nchunkP); r /= nchunkP;
+        const int dx = (int)(r % 3); r /= 3;
         const int nt = (int)r;
-        const int co = nt * T + n, ci = c * 8 + kh * 4 + e;
+        const int dy = n / NPAD, nn = n - dy * NPAD;
+        const int co = nt * T + nn, ci = c * 8 + kh * 4 + e;
         float v = 0.0f;
-        if (n < T && co < Cout && ci < Cin) v = w[((int64_t)co * Cin + ci) * 9 + tap];
+        if (nn < T && co < Cout && ci < Cin) v = w[((int64_t)co * Cin + ci) * 9 + dy * 3 + dx];
         uint32_t t;
         asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(v));
         wprep[i] = __uint_as_float(t);
     }
+}
+
+// 256-bit global accesses (sm_100): one full 32-byte sector per thread
+__device__ __forceinline__ void ld_global_v8(const float* p, float* v) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void st_global_v8(float* p, const float* v) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+                 : "memory");
 }
 
 __device__ __forceinline__ bool elect_one() {
@@ -78,10 +103,13 @@ __device__ __forceinline__ bool elect_one() {
 
 template <int NPAD>
 __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArgs a, const __grid_constant__ CUtensorMap xmap) {
+    constexpr int N = 3 * NPAD;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    const uint32_t per_tap = (uint32_t)a.nchunk * NPAD * 32;
-    const uint32_t wbytes = 9 * per_tap;
+    const int nchunkP = a.nstage_tile * kCvKSteps;
+    constexpr uint32_t slab = 2 * N * 16;                       // one (dx, chunk) B slab
+    const uint32_t per_dx = (uint32_t)nchunkP * slab;
+    const uint32_t wbytes = 3 * per_dx;
     uint8_t* b_s = smem;
     uint8_t* a_ring = b_s + wbytes;
     float* bias_s = reinterpret_cast<float*>(a_ring + a.stages * kCvStageBytes);
@@ -102,7 +130,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         mbar_init(wfull, 1);
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tfull[s], 1);
-            mbar_init(&tempty[s], kCvM);
+            mbar_init(&tempty[s], 2 * kCvM);
         }
         fence_mbar_init();
         tma_prefetch_desc(&xmap);
@@ -122,21 +150,22 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         // ---- producer (whole warp converged, one elected lane issues): resident weights once, then the window ring ----
         if (elect_one()) {
             mbar_arrive_expect_tx(wfull, wbytes);
-            for (int t = 0; t < 9; ++t)
-                bulk_load_1d(b_s + t * per_tap, reinterpret_cast<const uint8_t*>(a.wprep) + (size_t)t * per_tap, per_tap, wfull);
+            for (int t = 0; t < 3; ++t)
+                bulk_load_1d(b_s + t * per_dx, reinterpret_cast<const uint8_t*>(a.wprep) + (size_t)t * per_dx, per_dx, wfull);
         }
         uint32_t s = 0, ph = 0;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
-            for (int c = 0; c < a.nchunk; ++c) {
+            for (int st = 0; st < a.nstage_tile; ++st) {
                 mbar_wait(&empty[s], ph ^ 1);
                 if (elect_one()) {
                     if (a.dbg & 1) {
                         mbar_arrive(&full[s]);
                     } else {
                         mbar_arrive_expect_tx(&full[s], kCvStageBytes);
-                        tma_load_5d(a_ring + s * kCvStageBytes, &xmap, &full[s], 0, tx * kCvTW - 1, ty * kCvTH - 1, 2 * c, b);
+                        // box {4 ch, 16 y, 10 x, 6 quads, 1 image} at (0, y0 - 1, x0 - 1, 6 st, b)
+                        tma_load_5d(a_ring + s * kCvStageBytes, &xmap, &full[s], 0, ty * kCvTH - 1, tx * kCvTW - 1, 2 * kCvKSteps * st, b);
                     }
                 }
                 __syncwarp();
@@ -145,11 +174,10 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         }
     } else if (warp == 1) {
         // ---- MMA issuer (whole warp converged; descriptors are warp-uniform, one elected lane issues) ----
-        constexpr uint32_t idesc = umma::idesc_tf32(kCvM, NPAD);
-        constexpr uint32_t lbo_a = kCvWinW * kCvWinH * 16, sbo_a = kCvWinW * 16;
-        // descriptors differ only in the 14-bit start-address field: keep the invariant words and add offsets >> 4
-        const uint64_t a_desc0 = umma::desc_kmajor(smem_u32(a_ring), (a.dbg & 16) ? 2048 : lbo_a, (a.dbg & 16) ? 128 : sbo_a);
-        const uint64_t b_desc0 = umma::desc_kmajor(smem_u32(b_s), NPAD * 16, 128);
+        constexpr uint32_t idesc = umma::idesc_tf32(kCvM, N);
+        // A: [quad][x][y][16 B]: k-halves kCvQuadBytes apart, 8-row groups 128 B apart; B: [k-half][n][16 B]
+        const uint64_t a_desc0 = umma::desc_kmajor(smem_u32(a_ring), kCvQuadBytes, 128);
+        const uint64_t b_desc0 = umma::desc_kmajor(smem_u32(b_s), N * 16, 128);
         mbar_wait(wfull, 0);
         uint32_t s = 0, ph = 0, i = 0;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++i) {
@@ -157,81 +185,115 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             mbar_wait(&tempty[acc], ((i >> 1) & 1) ^ 1);
             umma::fence_after();
             const uint32_t d = tmem_base + acc * kCvAccStride;
-            for (int c = 0; c < a.nchunk; ++c) {
+            for (int st = 0; st < a.nstage_tile; ++st) {
                 mbar_wait(&full[s], ph);
                 umma::fence_after();
                 if (elect_one()) {
                     const uint64_t ad0 = a_desc0 + (uint64_t)((s * kCvStageBytes) >> 4);
-                    const uint64_t bd0 = b_desc0 + (uint64_t)((c * (NPAD * 32)) >> 4);
+                    const uint64_t bd0 = b_desc0 + (uint64_t)((st * kCvKSteps * slab) >> 4);
                     if (!(a.dbg & 4)) {
 #pragma unroll
-                        for (int tap = 0; tap < 9; ++tap) {
-                            const uint64_t ad = ad0 + ((a.dbg & 32) ? (uint64_t)((tap / 3) * 8) : (uint64_t)(((tap / 3) * kCvWinW + (tap % 3))));
-                            const uint64_t bd = bd0 + (uint64_t)((tap * per_tap) >> 4);
-                            umma::mma_tf32((a.dbg & 8) ? tmem_base + (tap & 1) * kCvAccStride : d, ad, bd, idesc, tap == 0 ? (uint32_t)(c != 0) : 1u);
+                        for (int j = 0; j < kCvKSteps; ++j) {
+#pragma unroll
+                            for (int dx = 0; dx < 3; ++dx) {
+                                const uint64_t ad = ad0 + (uint64_t)((j * 2 * kCvQuadBytes + dx * kCvRows * 16) >> 4);
+                                const uint64_t bd = bd0 + (uint64_t)((dx * per_dx + j * slab) >> 4);
+                                umma::mma_tf32(d, ad, bd, idesc, (j == 0 && dx == 0) ? (uint32_t)(st != 0) : 1u);
+                            }
                         }
                     }
                     umma::commit(&empty[s]);
-                    if (c == a.nchunk - 1) umma::commit(&tfull[acc]);
+                    if (st == a.nstage_tile - 1) umma::commit(&tfull[acc]);
                 }
                 __syncwarp();
                 if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
             }
         }
     } else {
-        // ---- epilogue warps: TMEM lane group = warp % 4; lane = pixel ----
-        const int q = warp & 3;
-        const int m = q * 32 + lane, ly = m >> 3, lx = m & 7;
+        // ---- epilogue warps: TMEM lane group = warp % 4; lane = pixel (column-major: m = 16 * column + row) ----
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int m = q * 32 + lane, lx = m >> 4, ly = m & 15;
         uint32_t i = 0;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++i) {
             const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
             const uint32_t acc = i & 1;
             mbar_wait(&tfull[acc], (i >> 1) & 1);
-            __syncwarp();                  // ragged tiles leave lanes diverged; tcgen05.ld is .sync.aligned
+            __syncwarp();                  // tcgen05.ld and the shuffles below are warp-collective
             umma::fence_after();
-            float v[NPAD];
             const uint32_t taddr = tmem_base + acc * kCvAccStride + ((uint32_t)(q * 32) << 16);
-#pragma unroll
-            for (int j = 0; j < NPAD / 8; ++j) umma::tmem_ld8(taddr + j * 8, v + 8 * j);
-            umma::tmem_ld_wait();
-            umma::fence_before();
-            mbar_arrive(&tempty[acc]);     // accumulator is in registers: the MMA warp may overwrite it
-            const int y = ty * kCvTH + ly, x = tx * kCvTW + lx;
-            if (y >= a.H || x >= a.W || (a.dbg & 2)) continue;
+            const int y = ty * kCvTH + ly - 1, x = tx * kCvTW + lx;
+            const bool valid = ly >= 1 && ly <= kCvTH && y < a.H && x < a.W && !(a.dbg & 2);
             float* o = a.out + b * a.out_sb + y * a.out_sy + x * a.out_sx;
             const float* rp = a.res ? a.res + b * a.res_sb + y * a.res_sy + x * a.res_sx : nullptr;
-            if (a.vec) {
+            // two warps share each TMEM lane quadrant and take alternate 8-channel chunks (latency hiding: the
+            // TMEM-load -> shuffle -> store chain of one warp per scheduler cannot keep up with the MMAs)
+#pragma unroll 1
+            for (int c0 = 8 * half; c0 < a.cn; c0 += 16) {
+                float p0[8], p1[8], p2[8], t[8];
+                umma::tmem_ld8(taddr + c0, p0);
+                umma::tmem_ld8(taddr + NPAD + c0, p1);
+                umma::tmem_ld8(taddr + 2 * NPAD + c0, p2);
+                umma::tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < NPAD / 4; ++j) {
-                    if (4 * j < a.cn) {
-                        float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (a.res_mode) rr = __ldg(reinterpret_cast<const float4*>(rp) + j);
-                        const float rv[4] = {rr.x, rr.y, rr.z, rr.w};
-                        float t[4];
+                for (int k = 0; k < 8; ++k) {
+                    const float up = __shfl_up_sync(0xffffffffu, p0[k], 1);      // plane dy=-1 of the row above
+                    const float dn = __shfl_down_sync(0xffffffffu, p2[k], 1);    // plane dy=+1 of the row below
+                    t[k] = __fadd_rn(__fadd_rn(up, p1[k]), dn);
+                }
+                if (valid && a.vec) {
+                    // NHWC: lane = pixel, 8 consecutive channels = one 32-byte sector per thread
+                    float rv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                    const bool full8 = c0 + 8 <= a.cn;
+                    if (a.res_mode) {
+                        if (a.vec == 2 && full8) {
+                            ld_global_v8(rp + c0, rv);
+                        } else {
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            t[k] = __fadd_rn(v[4 * j + k], bias_s[4 * j + k]);
-                            if (a.res_mode == 1) t[k] = __fadd_rn(rv[k], t[k]);
-                            if (a.slope) t[k] = t[k] > 0.0f ? t[k] : __fmul_rn(slope_s[4 * j + k], t[k]);
-                            if (a.res_mode == 2) t[k] = __fadd_rn(rv[k], t[k]);
+                            for (int h = 0; h < 2; ++h)
+                                if (c0 + 4 * h < a.cn) {
+                                    const float4 rr = __ldg(reinterpret_cast<const float4*>(rp + c0) + h);
+                                    rv[4 * h] = rr.x; rv[4 * h + 1] = rr.y; rv[4 * h + 2] = rr.z; rv[4 * h + 3] = rr.w;
+                                }
                         }
-                        reinterpret_cast<float4*>(o)[j] = make_float4(t[0], t[1], t[2], t[3]);
                     }
-                }
-            } else {
+                    float u[8];
 #pragma unroll
-                for (int c = 0; c < NPAD; ++c) {
-                    if (c < a.cn) {
-                        float t = __fadd_rn(v[c], bias_s[c]);
-                        const float rv = a.res_mode ? __ldg(rp + c * a.res_sc) : 0.0f;
-                        if (a.res_mode == 1) t = __fadd_rn(rv, t);
-                        if (a.slope) t = t > 0.0f ? t : __fmul_rn(slope_s[c], t);
-                        if (a.res_mode == 2) t = __fadd_rn(rv, t);
-                        o[c * a.out_sc] = t;
+                    for (int k = 0; k < 8; ++k) {
+                        const int c = c0 + k;
+                        float w = __fadd_rn(t[k], bias_s[c]);
+                        if (a.res_mode == 1) w = __fadd_rn(rv[k], w);
+                        if (a.slope) w = w > 0.0f ? w : __fmul_rn(slope_s[c], w);
+                        if (a.res_mode == 2) w = __fadd_rn(rv[k], w);
+                        u[k] = w;
+                    }
+                    if (a.vec == 2 && full8) {
+                        st_global_v8(o + c0, u);
+                    } else {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+                            if (c0 + 4 * h < a.cn) reinterpret_cast<float4*>(o + c0)[h] = make_float4(u[4 * h], u[4 * h + 1], u[4 * h + 2], u[4 * h + 3]);
+                    }
+                } else if (valid) {
+                    // any other layout (planar NCHW, unaligned channel counts): one scalar store per channel
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int c = c0 + k;
+                        if (c < a.cn) {
+                            float u = __fadd_rn(t[k], bias_s[c]);
+                            const float rv = a.res_mode ? __ldg(rp + c * a.res_sc) : 0.0f;
+                            if (a.res_mode == 1) u = __fadd_rn(rv, u);
+                            if (a.slope) u = u > 0.0f ? u : __fmul_rn(slope_s[c], u);
+                            if (a.res_mode == 2) u = __fadd_rn(rv, u);
+                            o[c * a.out_sc] = u;
+                        }
                     }
                 }
+                __syncwarp();              // reconverge before the next warp-collective TMEM load
             }
+            __syncwarp();
+            umma::fence_before();
+            mbar_arrive(&tempty[acc]);     // every TMEM read of this tile is done: the MMA warp may overwrite it
         }
     }
     umma::fence_before();
@@ -240,28 +302,24 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------
-static int conv_n_gran() {
-    static int g = 0;
-    if (!g) {
-        const char* e = getenv("VFI_CONV_NGRAN");
-        g = (e && atoi(e) == 8) ? 8 : 16;
-    }
-    return g;
-}
 struct ConvTiling {
-    int T, NPAD, n_nt;
+    int T, NPAD, n_nt, nstage_tile, nchunkP;
+    size_t wbytes;      // resident weights of one Cout tile
 };
-static ConvTiling conv_tiling(int Cout) {
-    const int g = conv_n_gran();
+static ConvTiling conv_tiling(int Cout, int Cin) {
     ConvTiling t;
-    if (Cout <= 80) t.T = Cout;                         // one tile
-    else if (g == 8 && Cout % 72 == 0) t.T = 72;
+    if (Cout <= 72) t.T = Cout;                         // one tile
+    else if (Cout % 72 == 0) t.T = 72;
     else t.T = 64;
-    const int sizes[6] = {16, 32, 48, 64, 72, 80};      // instantiated N (72 needs the 8-granular UMMA N)
-    t.NPAD = 80;
-    for (int i = 5; i >= 0; --i)
-        if (sizes[i] >= t.T && (sizes[i] % g) == 0) t.NPAD = sizes[i];
+    const int sizes[5] = {16, 32, 48, 64, 72};          // instantiated Cout tiles (UMMA N = 3 * NPAD <= 216)
+    t.NPAD = 72;
+    for (int i = 4; i >= 0; --i)
+        if (sizes[i] >= t.T) t.NPAD = sizes[i];
     t.n_nt = (Cout + t.T - 1) / t.T;
+    const int nchunk = (Cin + 7) / 8;                   // a trailing half chunk is zero-filled by TMA (and by prep)
+    t.nstage_tile = (nchunk + kCvKSteps - 1) / kCvKSteps;
+    t.nchunkP = t.nstage_tile * kCvKSteps;
+    t.wbytes = (size_t)3 * t.nchunkP * 2 * 3 * t.NPAD * 16;
     return t;
 }
 static size_t conv_smem_fixed(int NPAD) { return 1024 + 2 * NPAD * 4 + (2 * kCvMaxStages + 5) * 8 + 16; }
@@ -284,18 +342,18 @@ static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, size_t smem, 
 extern "C" size_t vfi_conv3x3_prep_bytes(int Cout, int Cin) {
     using namespace vfi;
     if (Cout < 1 || Cin < 4 || Cin % 4) return 0;
-    const ConvTiling t = conv_tiling(Cout);
-    return (size_t)t.n_nt * 9 * ((Cin + 7) / 8) * 2 * t.NPAD * 4 * sizeof(float);
+    const ConvTiling t = conv_tiling(Cout, Cin);
+    return (size_t)t.n_nt * t.wbytes;
 }
 
 extern "C" int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout, int Cin, void* stream) {
     using namespace vfi;
     VFI_REQUIRE(weight && wprep, "vfi_conv3x3_prep_f32: null pointer");
     VFI_REQUIRE(Cout >= 1 && Cin >= 4 && Cin % 4 == 0, "vfi_conv3x3_prep_f32: Cin %d must be a positive multiple of 4", Cin);
-    const ConvTiling t = conv_tiling(Cout);
-    const int64_t total = (int64_t)t.n_nt * 9 * ((Cin + 7) / 8) * 2 * t.NPAD * 4;
+    const ConvTiling t = conv_tiling(Cout, Cin);
+    const int64_t total = (int64_t)t.n_nt * (int64_t)(t.wbytes / 4);
     const int blocks = (int)min64(ceil_div(total, 256), (int64_t)kNumSMs * 8);
-    conv3x3_prep_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(weight, wprep, Cout, Cin, t.T, t.NPAD, t.n_nt);
+    conv3x3_prep_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(weight, wprep, Cout, Cin, t.T, t.NPAD, t.n_nt, t.nchunkP);
     VFI_CHECK_LAUNCH("conv3x3_prep_kernel");
     return VFI_OK;
 }
@@ -303,9 +361,8 @@ extern "C" int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout,
 extern "C" int vfi_conv3x3_supported(int Cin, int x_pix_stride, int Cout) {
     using namespace vfi;
     if (Cin < 4 || Cin % 4 || x_pix_stride % 4 || x_pix_stride < Cin || Cout < 1) return 0;
-    const ConvTiling t = conv_tiling(Cout);
-    const size_t wbytes = (size_t)9 * ((Cin + 7) / 8) * t.NPAD * 32;
-    return wbytes + conv_smem_fixed(t.NPAD) + 3 * (size_t)kCvStageBytes <= (size_t)kCvSmemMax;
+    const ConvTiling t = conv_tiling(Cout, Cin);
+    return t.wbytes + conv_smem_fixed(t.NPAD) + 2 * (size_t)kCvStageBytes <= (size_t)kCvSmemMax;
 }
 
 extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* bias, const float* slope, const float* residual,
@@ -322,13 +379,14 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
     VFI_REQUIRE(out_c_total >= Cout && (residual_mode == 0 || res_c_total >= Cout), "vfi_conv3x3_f32: channel totals");
     if (B == 0) return VFI_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const ConvTiling t = conv_tiling(Cout);
+    const ConvTiling t = conv_tiling(Cout, Cin);
     CUtensorMap xmap;
     {
-        const uint64_t dims[5] = {4, (uint64_t)W, (uint64_t)H, (uint64_t)(Cin / 4), (uint64_t)B};
-        const uint64_t strides[4] = {(uint64_t)x_pix_stride * 4, (uint64_t)W * x_pix_stride * 4, 16,
+        // (4 channels, y, x, channel quad, image): y before x so that a box lands column-major in shared memory
+        const uint64_t dims[5] = {4, (uint64_t)H, (uint64_t)W, (uint64_t)(Cin / 4), (uint64_t)B};
+        const uint64_t strides[4] = {(uint64_t)W * x_pix_stride * 4, (uint64_t)x_pix_stride * 4, 16,
                                      (uint64_t)H * W * x_pix_stride * 4};
-        const uint32_t box[5] = {4, (uint32_t)kCvWinW, (uint32_t)kCvWinH, 2, 1};
+        const uint32_t box[5] = {4, (uint32_t)kCvRows, (uint32_t)kCvWinW, 2 * kCvKSteps, 1};
         const int rc = make_tmap_f32_nd(&xmap, x, 5, dims, strides, box);
         if (rc != VFI_OK) return rc;
     }
@@ -337,7 +395,8 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
         const char* e = getenv("VFI_CONV_DBG");
         a.dbg = e ? atoi(e) : 0;
     }
-    a.B = B; a.H = H; a.W = W; a.nchunk = (Cin + 7) / 8;   // a trailing half chunk is zero-filled by TMA (and by prep)
+    a.B = B; a.H = H; a.W = W;
+    a.nstage_tile = t.nstage_tile;
     a.res_mode = residual_mode;
     a.tiles_x = (W + kCvTW - 1) / kCvTW; a.tiles_y = (H + kCvTH - 1) / kCvTH;
     a.n_tiles = B * a.tiles_x * a.tiles_y;
@@ -349,21 +408,23 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
         a.out_sb = HW * out_c_total; a.out_sy = W; a.out_sx = 1; a.out_sc = HW;
         a.res_sb = HW * res_c_total; a.res_sy = W; a.res_sx = 1; a.res_sc = HW;
     }
-    const size_t wbytes = (size_t)9 * a.nchunk * t.NPAD * 32;
-    int stages = (int)(((size_t)kCvSmemMax - conv_smem_fixed(t.NPAD) - wbytes) / kCvStageBytes);
+    int stages = (int)(((size_t)kCvSmemMax - conv_smem_fixed(t.NPAD) - t.wbytes) / kCvStageBytes);
     if (stages > kCvMaxStages) stages = kCvMaxStages;
     a.stages = stages;
-    const size_t smem = wbytes + (size_t)stages * kCvStageBytes + conv_smem_fixed(t.NPAD);
+    const size_t smem = t.wbytes + (size_t)stages * kCvStageBytes + conv_smem_fixed(t.NPAD);
     for (int nt = 0; nt < t.n_nt; ++nt) {
         const int c0 = nt * t.T;
         a.cn = Cout - c0 < t.T ? Cout - c0 : t.T;
-        a.wprep = wprep + (size_t)nt * (wbytes / 4);
+        a.wprep = wprep + (size_t)nt * (t.wbytes / 4);
         a.bias = bias ? bias + c0 : nullptr;
         a.slope = slope ? slope + c0 : nullptr;
         a.out = out + c0 * a.out_sc;
         a.res = residual ? residual + c0 * a.res_sc : nullptr;
         const bool al = ((reinterpret_cast<uintptr_t>(a.out) & 15) == 0) && (a.res == nullptr || (reinterpret_cast<uintptr_t>(a.res) & 15) == 0);
         a.vec = out_channels_last && al && a.cn % 4 == 0 && out_c_total % 4 == 0 && (residual_mode == 0 || res_c_total % 4 == 0);
+        // vec 2: pixel rows of out / residual are 32-byte aligned too -> 256-bit accesses
+        auto al32 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; };
+        if (a.vec && al32(a.out) && out_c_total % 8 == 0 && (a.res == nullptr || (al32(a.res) && res_c_total % 8 == 0))) a.vec = 2;
         int rc;
         switch (t.NPAD) {
             case 16: rc = conv_launch<16>(a, xmap, smem, st); break;
@@ -371,7 +432,6 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
             case 48: rc = conv_launch<48>(a, xmap, smem, st); break;
             case 64: rc = conv_launch<64>(a, xmap, smem, st); break;
             case 72: rc = conv_launch<72>(a, xmap, smem, st); break;
-            case 80: rc = conv_launch<80>(a, xmap, smem, st); break;
             default:
                 set_error("vfi_conv3x3_f32: no kernel for a Cout tile padded to %d", t.NPAD);
                 return VFI_ERR_UNSUPPORTED;
