@@ -15,10 +15,10 @@
 // 9 x Cin/8 with N = 72.
 //
 // Persistent kernel, one CTA per SM, 10 warps:
-//   warp 0  producer : per tile and per 24-channel stage ONE 5-D TMA box {4 ch, 16 y, 10 x, 6 ch-quads, 1 image} of
-//                      the NHWC input (zero-filled outside the image = the conv padding).  It lands as
-//                      [ch-quad][x][y][16 B]: 8 vertically adjacent pixels x 16 B = one UMMA core matrix
-//                      (K-major, no swizzle), and the horizontal taps are descriptor offsets of 256 B -- no im2col.
+//   warp 0  producer : per tile and per 16-channel stage ONE 4-D TMA box {16 ch, 16 y, 10 x, 1 image} of the NHWC
+//                      input (zero-filled outside the image = the conv padding; SWIZZLE_64B).  It lands as
+//                      [x][y][64 B] = 160 pixel rows in UMMA's K-major 64-byte-swizzle layout, so the horizontal taps
+//                      are descriptor offsets of 1024 B and the second k-step of a stage is +32 B -- no im2col.
 //   warp 1  MMA      : tcgen05.mma.cta_group::1.kind::tf32, M = 128, N = 3 * (Cout tile), accumulating in one of two
 //                      TMEM accumulators.  The weights of the Cout tile (<= 187 KB, RN-rounded to TF32 and arranged by
 //                      conv3x3_prep_kernel) stay resident in shared memory for the life of the CTA.
@@ -36,11 +36,10 @@ constexpr int kCvTW = 8, kCvRows = 16;                  // tile: 8 columns x 16 
 constexpr int kCvTH = kCvRows - 2;                      // output rows per tile
 constexpr int kCvM = kCvTW * kCvRows;
 constexpr int kCvWinW = kCvTW + 2;
-constexpr int kCvKSteps = 3;                            // 8-channel k-steps per stage
-constexpr int kCvQuadBytes = kCvWinW * kCvRows * 16;    // one 4-channel quad of the window: 2560 B
-constexpr int kCvStageBytes = 2 * kCvKSteps * kCvQuadBytes;   // 15360 B
+constexpr int kCvKSteps = 2;                            // 8-channel k-steps per stage (16 channels = one 64-byte swizzle row)
+constexpr int kCvStageBytes = kCvWinW * kCvRows * 64;   // 160 pixel rows x 64 B = 10240 B
 constexpr int kCvThreads = 320;                         // producer warp, MMA warp, 8 epilogue warps
-constexpr int kCvMaxStages = 4;
+constexpr int kCvMaxStages = 6;
 constexpr int kCvSmemMax = 232448;                      // 227 KB opt-in limit
 constexpr int kCvAccStride = 256;                       // TMEM columns between the two accumulators
 
@@ -50,7 +49,7 @@ struct ConvArgs {
     const float* slope;   // cn floats or null
     const float* res;     // residual (same layout family as out) or null
     float* out;
-    int B, H, W, nstage_tile, cn;   // nstage_tile = stages (24 channels) per tile
+    int B, H, W, nstage_tile, nchunk, cn;   // nstage_tile = stages (16 channels) per tile, nchunk = 8-channel k-steps per tile
     int res_mode;         // 0 none, 1 add before the activation, 2 add after it
     int vec;              // NHWC out/res: 1 = 16-byte aligned pixel rows (float4), 2 = 32-byte aligned (256-bit accesses)
     int64_t out_sb, out_sy, out_sx, out_sc;   // element strides of out
@@ -106,12 +105,12 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
     constexpr int N = 3 * NPAD;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    const int nchunkP = a.nstage_tile * kCvKSteps;
+    const int nchunkP = a.nchunk;
     constexpr uint32_t slab = 2 * N * 16;                       // one (dx, chunk) B slab
     const uint32_t per_dx = (uint32_t)nchunkP * slab;
     const uint32_t wbytes = 3 * per_dx;
     uint8_t* b_s = smem;
-    uint8_t* a_ring = b_s + wbytes;
+    uint8_t* a_ring = b_s + ((wbytes + 1023u) & ~1023u);      // swizzled stages: 1024-byte aligned
     float* bias_s = reinterpret_cast<float*>(a_ring + a.stages * kCvStageBytes);
     float* slope_s = bias_s + NPAD;
     uint64_t* full = reinterpret_cast<uint64_t*>(slope_s + NPAD);
@@ -164,8 +163,8 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                         mbar_arrive(&full[s]);
                     } else {
                         mbar_arrive_expect_tx(&full[s], kCvStageBytes);
-                        // box {4 ch, 16 y, 10 x, 6 quads, 1 image} at (0, y0 - 1, x0 - 1, 6 st, b)
-                        tma_load_5d(a_ring + s * kCvStageBytes, &xmap, &full[s], 0, ty * kCvTH - 1, tx * kCvTW - 1, 2 * kCvKSteps * st, b);
+                        // box {16 ch, 16 y, 10 x, 1 image} at (16 st, y0 - 1, x0 - 1, b); channels >= Cin read as 0
+                        tma_load_4d(a_ring + s * kCvStageBytes, &xmap, &full[s], 16 * st, ty * kCvTH - 1, tx * kCvTW - 1, b);
                     }
                 }
                 __syncwarp();
@@ -175,8 +174,8 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
     } else if (warp == 1) {
         // ---- MMA issuer (whole warp converged; descriptors are warp-uniform, one elected lane issues) ----
         constexpr uint32_t idesc = umma::idesc_tf32(kCvM, N);
-        // A: [quad][x][y][16 B]: k-halves kCvQuadBytes apart, 8-row groups 128 B apart; B: [k-half][n][16 B]
-        const uint64_t a_desc0 = umma::desc_kmajor(smem_u32(a_ring), kCvQuadBytes, 128);
+        // A: [x][y][64 B] rows in the 64-byte swizzle (8-row groups 512 B apart); B: [k-half][n][16 B], no swizzle
+        const uint64_t a_desc0 = umma::desc_kmajor_sw64(smem_u32(a_ring), 512);
         const uint64_t b_desc0 = umma::desc_kmajor(smem_u32(b_s), N * 16, 128);
         mbar_wait(wfull, 0);
         uint32_t s = 0, ph = 0, i = 0;
@@ -194,11 +193,13 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                     if (!(a.dbg & 4)) {
 #pragma unroll
                         for (int j = 0; j < kCvKSteps; ++j) {
+                            if (st * kCvKSteps + j < a.nchunk) {      // the last stage of a tile may hold one k-step only
 #pragma unroll
-                            for (int dx = 0; dx < 3; ++dx) {
-                                const uint64_t ad = ad0 + (uint64_t)((j * 2 * kCvQuadBytes + dx * kCvRows * 16) >> 4);
-                                const uint64_t bd = bd0 + (uint64_t)((dx * per_dx + j * slab) >> 4);
-                                umma::mma_tf32(d, ad, bd, idesc, (j == 0 && dx == 0) ? (uint32_t)(st != 0) : 1u);
+                                for (int dx = 0; dx < 3; ++dx) {
+                                    const uint64_t ad = ad0 + (uint64_t)((j * 32 + dx * kCvRows * 64) >> 4);
+                                    const uint64_t bd = bd0 + (uint64_t)((dx * per_dx + j * slab) >> 4);
+                                    umma::mma_tf32(d, ad, bd, idesc, (j == 0 && dx == 0) ? (uint32_t)(st != 0) : 1u);
+                                }
                             }
                         }
                     }
@@ -318,11 +319,11 @@ static ConvTiling conv_tiling(int Cout, int Cin) {
     t.n_nt = (Cout + t.T - 1) / t.T;
     const int nchunk = (Cin + 7) / 8;                   // a trailing half chunk is zero-filled by TMA (and by prep)
     t.nstage_tile = (nchunk + kCvKSteps - 1) / kCvKSteps;
-    t.nchunkP = t.nstage_tile * kCvKSteps;
+    t.nchunkP = nchunk;
     t.wbytes = (size_t)3 * t.nchunkP * 2 * 3 * t.NPAD * 16;
     return t;
 }
-static size_t conv_smem_fixed(int NPAD) { return 1024 + 2 * NPAD * 4 + (2 * kCvMaxStages + 5) * 8 + 16; }
+static size_t conv_smem_fixed(int NPAD) { return 2048 + 2 * NPAD * 4 + (2 * kCvMaxStages + 5) * 8 + 16; }   // 2 x 1024 alignment slack
 
 template <int NPAD>
 static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, size_t smem, cudaStream_t st) {
@@ -382,12 +383,11 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
     const ConvTiling t = conv_tiling(Cout, Cin);
     CUtensorMap xmap;
     {
-        // (4 channels, y, x, channel quad, image): y before x so that a box lands column-major in shared memory
-        const uint64_t dims[5] = {4, (uint64_t)H, (uint64_t)W, (uint64_t)(Cin / 4), (uint64_t)B};
-        const uint64_t strides[4] = {(uint64_t)W * x_pix_stride * 4, (uint64_t)x_pix_stride * 4, 16,
-                                     (uint64_t)H * W * x_pix_stride * 4};
-        const uint32_t box[5] = {4, (uint32_t)kCvRows, (uint32_t)kCvWinW, 2 * kCvKSteps, 1};
-        const int rc = make_tmap_f32_nd(&xmap, x, 5, dims, strides, box);
+        // (channel, y, x, image): y before x so that a box lands column-major in shared memory; 64-byte swizzle
+        const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)H, (uint64_t)W, (uint64_t)B};
+        const uint64_t strides[3] = {(uint64_t)W * x_pix_stride * 4, (uint64_t)x_pix_stride * 4, (uint64_t)H * W * x_pix_stride * 4};
+        const uint32_t box[4] = {16, (uint32_t)kCvRows, (uint32_t)kCvWinW, 1};
+        const int rc = make_tmap_f32_nd(&xmap, x, 4, dims, strides, box, 64);
         if (rc != VFI_OK) return rc;
     }
     ConvArgs a = {};
@@ -397,6 +397,7 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
     }
     a.B = B; a.H = H; a.W = W;
     a.nstage_tile = t.nstage_tile;
+    a.nchunk = t.nchunkP;
     a.res_mode = residual_mode;
     a.tiles_x = (W + kCvTW - 1) / kCvTW; a.tiles_y = (H + kCvTH - 1) / kCvTH;
     a.n_tiles = B * a.tiles_x * a.tiles_y;

@@ -20,6 +20,20 @@ __device__ __forceinline__ uint64_t desc_kmajor(uint32_t saddr, uint32_t lbo, ui
     return d;
 }
 
+// K-major operand in the 64-byte swizzle layout (what a TMA box with a 64-byte inner extent and SWIZZLE_64B writes):
+// rows of 64 B at a 64-byte pitch, the four 16-byte chunks of a row XOR-ed with address bits 7..8; 8-row groups `sbo`
+// bytes apart (512 when dense).  The start address may be advanced by 32 B for the second tf32 k-step of a row and by
+// multiples of 512 B for row shifts; the buffer itself must be 512-byte aligned.
+__device__ __forceinline__ uint64_t desc_kmajor_sw64(uint32_t saddr, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)1 << 16;                               // LBO: unused while K stays inside one swizzle row
+    d |= (uint64_t)((sbo >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;                               // descriptor version (sm_100)
+    d |= (uint64_t)4 << 61;                               // layout type SWIZZLE_64B
+    return d;
+}
+
 // D = F32, A = B = TF32, both K-major
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
@@ -61,6 +75,13 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 }  // namespace umma
 
+// 4-D tiled TMA load (innermost coordinate first)
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* tmap, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
 // 5-D tiled TMA load (innermost coordinate first)
 __device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* tmap, uint64_t* bar, int c0, int c1, int c2, int c3, int c4) {
     asm volatile(
@@ -89,7 +110,8 @@ __device__ __forceinline__ void bulk_wait_group() { asm volatile("cp.async.bulk.
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 
 // fp32 tensor of rank <= 5 (innermost first), byte strides for dims 1.., box per dim; OOB reads give 0.
+// swizzle_bytes: 0 (none), 32, 64 or 128 (the inner box extent in bytes must not exceed it)
 int make_tmap_f32_nd(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                     const uint32_t* box);
+                     const uint32_t* box, int swizzle_bytes = 0);
 
 }  // namespace vfi
