@@ -165,13 +165,16 @@ int vfi_bias_act_f32(const float* y, const float* bias, const float* slope, cons
  *            channels [0, Cout) are written.  residual (mode 1: before the activation, 2: after) has the layout of
  *            out with res_c_total channels.  bias / slope (Cout) may be NULL.
  * vfi_conv3x3_supported: 1 when this (Cin, x_pix_stride, Cout) runs here (weights of a Cout tile must fit in shared
- * memory: Cin <= 72 for a 72-wide tile). */
-int vfi_conv3x3_supported(int Cin, int x_pix_stride, int Cout);
-size_t vfi_conv3x3_prep_bytes(int Cout, int Cin);
-int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout, int Cin, void* stream);
+ * memory: Cin <= 72 for a 72-wide tile).
+ * upscale = 2 fuses nn.PixelShuffle(2) behind the convolution (modules/generator.py:14-22: upconv1 -> pixel_shuffle ->
+ * prelu1): out is (B, Cout/4, 2H, 2W), out[b, c, 2y+i, 2x+j] = act(conv[b, 4c + 2i + j, y, x] + bias[4c + 2i + j]) with
+ * slope indexed by c (Cout/4 values); no residual.  wprep depends on upscale (same value in prep and conv calls). */
+int vfi_conv3x3_supported(int Cin, int x_pix_stride, int Cout, int upscale);
+size_t vfi_conv3x3_prep_bytes(int Cout, int Cin, int upscale);
+int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout, int Cin, int upscale, void* stream);
 int vfi_conv3x3_f32(const float* x, const float* wprep, const float* bias, const float* slope, const float* residual,
                     float* out, int B, int H, int W, int Cin, int x_pix_stride, int Cout, int out_channels_last,
-                    int out_c_total, int res_c_total, int residual_mode, void* stream);
+                    int out_c_total, int res_c_total, int residual_mode, int upscale, void* stream);
 
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */

@@ -116,3 +116,25 @@ def test_dat_forward_tc_convs_match_fp32_convs(tf32):
     assert n_tc != n_fp32, "the tensor-core conv path did not run"
     assert float((y_tc - y_fp32).abs().max()) <= 2e-2
     assert float((y_tc - y_fp32).abs().mean()) <= 2e-3
+
+
+@pytest.mark.parametrize("shape", [(1, 72, 288, 20, 12), (2, 72, 288, 15, 9), (1, 32, 64, 16, 8)])
+def test_conv3x3_fused_pixel_shuffle(tf32, shape):
+    """upconv1 -> PixelShuffle(2) -> PReLU of the generator (modules/generator.py:14-22) in one kernel."""
+    from videoframeinterpolation_b200 import conv as vc
+    B, Cin, Cout, H, W = shape
+    g = torch.Generator().manual_seed(5)
+    conv = nn.Conv2d(Cin, Cout, 3, 1, 1)
+    with torch.no_grad():
+        conv.weight.copy_(torch.randn(conv.weight.shape, generator=g) * 0.1)
+        conv.bias.copy_(torch.randn(Cout, generator=g))
+    conv = conv.cuda()
+    x = torch.randn(B, Cin, H, W, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    slope = torch.rand(Cout // 4, generator=g).cuda()
+    with torch.no_grad():
+        assert vc.eligible(conv, x, upscale=2)
+        y = vc.conv3x3(conv, x, slope, upscale=2)
+    assert y.shape == (B, Cout // 4, 2 * H, 2 * W) and y.is_contiguous(memory_format=torch.channels_last)
+    ref = torch.nn.functional.pixel_shuffle(oracle.conv3x3_tf32(x.cpu(), conv.weight.detach().cpu(), conv.bias.detach().cpu()), 2)
+    ref = torch.where(ref > 0, ref, slope.double().cpu().view(1, -1, 1, 1) * ref)
+    assert rel_err(y.double().cpu(), ref) <= 1e-5

@@ -36,10 +36,10 @@ SIGNATURES = {
     "vfi_dcn_f32": (c_int, [c_void_p] * 6 + [c_int] * 13 + [c_void_p, c_size_t, c_void_p]),
     "vfi_dcn_workspace_bytes": (c_size_t, [c_int] * 10),
     "vfi_bias_act_f32": (c_int, [c_void_p] * 5 + [c_int] * 6 + [c_void_p]),
-    "vfi_conv3x3_supported": (c_int, [c_int] * 3),
-    "vfi_conv3x3_prep_bytes": (c_size_t, [c_int] * 2),
-    "vfi_conv3x3_prep_f32": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p]),
-    "vfi_conv3x3_f32": (c_int, [c_void_p] * 6 + [c_int] * 10 + [c_void_p]),
+    "vfi_conv3x3_supported": (c_int, [c_int] * 4),
+    "vfi_conv3x3_prep_bytes": (c_size_t, [c_int] * 3),
+    "vfi_conv3x3_prep_f32": (c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p]),
+    "vfi_conv3x3_f32": (c_int, [c_void_p] * 6 + [c_int] * 11 + [c_void_p]),
     "vfi_launch_count": (c_int64, []),
     "vfi_launch_count_reset": (None, []),
 }

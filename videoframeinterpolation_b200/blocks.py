@@ -169,7 +169,11 @@ class BasicResPixelShuffleGenerator(nn.Module):
         self.conv_last = nn.Conv2d(nf, 3, 3, 1, 1)
 
     def forward(self, feat, m):
-        t = self.prelu1(self.pixel_shuffle(conv_bias_act(self.upconv1, self.reconstruction(feat))))
+        r = self.reconstruction(feat)
+        if _conv.eligible(self.upconv1, r, upscale=2):     # conv + PixelShuffle(2) + PReLU in one kernel
+            t = _conv.conv3x3(self.upconv1, r, self.prelu1.weight, upscale=2)
+        else:
+            t = self.prelu1(self.pixel_shuffle(conv_bias_act(self.upconv1, r)))
         return torch.clamp(conv_bias_act(self.conv_last, conv_bias_act(self.HRconv, t, self.prelu2)) + m, 0, 1)
 
 

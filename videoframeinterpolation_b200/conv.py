@@ -32,7 +32,7 @@ def _nhwc_pixel_stride(x: torch.Tensor) -> Optional[int]:
     return sw
 
 
-def eligible(conv: nn.Conv2d, x: torch.Tensor) -> bool:
+def eligible(conv: nn.Conv2d, x: torch.Tensor, upscale: int = 1) -> bool:
     if _algo() == "cudnn" or not torch.backends.cudnn.allow_tf32:
         return False
     if not (type(conv) is nn.Conv2d and conv.kernel_size == (3, 3) and conv.stride == (1, 1) and conv.padding == (1, 1)
@@ -43,40 +43,42 @@ def eligible(conv: nn.Conv2d, x: torch.Tensor) -> bool:
     ps = _nhwc_pixel_stride(x)
     if ps is None:
         return False
-    return bool(_lib.lib().vfi_conv3x3_supported(conv.in_channels, ps, conv.out_channels))
+    return bool(_lib.lib().vfi_conv3x3_supported(conv.in_channels, ps, conv.out_channels, upscale))
 
 
-def prepared_weight(conv: nn.Conv2d) -> torch.Tensor:
+def prepared_weight(conv: nn.Conv2d, upscale: int = 1) -> torch.Tensor:
     """TF32-rounded, UMMA-ordered copy of conv.weight, cached on the module and rebuilt when the weight changes."""
     w = conv.weight
-    key = (w.data_ptr(), w._version, str(w.device))
+    key = (w.data_ptr(), w._version, str(w.device), upscale)
     cached = getattr(conv, "_vfi_wprep", None)
     if cached is not None and cached[0] == key:
         return cached[1]
     cout, cin = w.shape[:2]
-    nbytes = _lib.lib().vfi_conv3x3_prep_bytes(cout, cin)
+    nbytes = _lib.lib().vfi_conv3x3_prep_bytes(cout, cin, upscale)
     wp = torch.empty(nbytes // 4, dtype=torch.float32, device=w.device)
     wc = w.detach().contiguous()          # (Cout, Cin, 3, 3) row-major whatever the module's memory format
-    _lib.call("vfi_conv3x3_prep_f32", w.device, wc.data_ptr(), wp.data_ptr(), cout, cin, _lib.stream_ptr(w.device))
+    _lib.call("vfi_conv3x3_prep_f32", w.device, wc.data_ptr(), wp.data_ptr(), cout, cin, upscale, _lib.stream_ptr(w.device))
     object.__setattr__(conv, "_vfi_wprep", (key, wp))
     return wp
 
 
 def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tensor] = None,
             residual: Optional[torch.Tensor] = None, residual_after_act: bool = False, use_bias: bool = True,
-            out_channels_last: bool = True) -> torch.Tensor:
-    """``act(residual + conv(x) + bias)`` in one kernel; x must satisfy :func:`eligible`."""
+            out_channels_last: bool = True, upscale: int = 1) -> torch.Tensor:
+    """``act(residual + conv(x) + bias)`` in one kernel; x must satisfy :func:`eligible`.  ``upscale=2`` returns
+    ``act(pixel_shuffle(conv(x) + bias, 2))`` (prelu_weight then has Cout/4 entries)."""
     dev = _lib.require_cuda(x, residual)
     B, Cin, H, W = x.shape
     Cout = conv.out_channels
     ps = _nhwc_pixel_stride(x)
     if ps is None:
         raise _lib.VfiError("conv3x3: x must be channels-last (or a channel slice of a channels-last tensor)")
-    wp = prepared_weight(conv)
+    wp = prepared_weight(conv, upscale)
+    Cs, Ho, Wo = Cout // (upscale * upscale), H * upscale, W * upscale
     if out_channels_last:
-        out = torch.empty((B, H, W, Cout), dtype=torch.float32, device=dev).permute(0, 3, 1, 2)
+        out = torch.empty((B, Ho, Wo, Cs), dtype=torch.float32, device=dev).permute(0, 3, 1, 2)
     else:
-        out = torch.empty((B, Cout, H, W), dtype=torch.float32, device=dev)
+        out = torch.empty((B, Cs, Ho, Wo), dtype=torch.float32, device=dev)
     res, res_c, mode = None, Cout, 0
     if residual is not None:
         if out_channels_last:
@@ -88,8 +90,8 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tenso
         mode = 2 if residual_after_act else 1
     slope = None
     if prelu_weight is not None:
-        slope = prelu_weight if prelu_weight.numel() == Cout else prelu_weight.expand(Cout).contiguous()
+        slope = prelu_weight if prelu_weight.numel() == Cs else prelu_weight.expand(Cs).contiguous()
     bias = conv.bias if use_bias else None
     _lib.call("vfi_conv3x3_f32", dev, x.data_ptr(), wp.data_ptr(), _lib.ptr(bias), _lib.ptr(slope), _lib.ptr(res), out.data_ptr(),
-              B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, Cout, res_c, mode, _lib.stream_ptr(dev))
+              B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, Cs, res_c, mode, upscale, _lib.stream_ptr(dev))
     return out

@@ -45,7 +45,7 @@ constexpr int kCvAccStride = 256;                       // TMEM columns between 
 
 struct ConvArgs {
     const float* wprep;   // this Cout tile: [dx 3][chunk nchunkP][k-half 2][n = dy * NPAD + co][4] floats
-    const float* bias;    // cn floats or null
+    const float* bias;    // cn floats (element stride bias_stride) or null
     const float* slope;   // cn floats or null
     const float* res;     // residual (same layout family as out) or null
     float* out;
@@ -55,13 +55,16 @@ struct ConvArgs {
     int64_t out_sb, out_sy, out_sx, out_sc;   // element strides of out
     int64_t res_sb, res_sy, res_sx, res_sc;
     int stages, tiles_x, tiles_y, n_tiles;
+    int bias_stride;
     int dbg;              // bring-up switches (VFI_CONV_DBG): 1 = no TMA loads, 2 = no epilogue stores, 4 = no MMAs
 };
 
 // weight (Cout, Cin, 3, 3) contiguous -> per Cout tile of T channels:
 // [dx][chunk nchunkP][k-half][n = dy * NPAD + co][4], RN-rounded to TF32, zero where co / ci are padding
+// up2 > 1 (fused PixelShuffle): tiles are ordered [sub-position][channel tile] and row nn of a tile is conv channel
+// (tile_c * T + nn) * up2 + sub, i.e. every tile produces all its channels for ONE of the up2 output pixels.
 __global__ void conv3x3_prep_kernel(const float* __restrict__ w, float* __restrict__ wprep, int Cout, int Cin, int T, int NPAD,
-                                    int n_nt, int nchunkP) {
+                                    int n_nt, int nchunkP, int up2) {
     const int64_t per_tile = (int64_t)3 * nchunkP * 2 * 3 * NPAD * 4;
     const int64_t total = per_tile * n_nt;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -73,9 +76,11 @@ __global__ void conv3x3_prep_kernel(const float* __restrict__ w, float* __restri
         const int dx = (int)(r % 3); r /= 3;
         const int nt = (int)r;
         const int dy = n / NPAD, nn = n - dy * NPAD;
-        const int co = nt * T + nn, ci = c * 8 + kh * 4 + e;
+        const int n_ct = n_nt / up2, sub = nt / n_ct, tc = nt - sub * n_ct;
+        const int cc = tc * T + nn;                      // channel after the shuffle (== conv channel when up2 == 1)
+        const int co = cc * up2 + sub, ci = c * 8 + kh * 4 + e;
         float v = 0.0f;
-        if (nn < T && co < Cout && ci < Cin) v = w[((int64_t)co * Cin + ci) * 9 + dy * 3 + dx];
+        if (nn < T && cc < Cout / up2 && ci < Cin) v = w[((int64_t)co * Cin + ci) * 9 + dy * 3 + dx];
         uint32_t t;
         asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(v));
         wprep[i] = __uint_as_float(t);
@@ -135,7 +140,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         tma_prefetch_desc(&xmap);
     }
     for (int i = tid; i < NPAD; i += kCvThreads) {
-        bias_s[i] = (a.bias && i < a.cn) ? a.bias[i] : 0.0f;
+        bias_s[i] = (a.bias && i < a.cn) ? a.bias[(size_t)i * a.bias_stride] : 0.0f;
         slope_s[i] = (a.slope && i < a.cn) ? a.slope[i] : 1.0f;
     }
     if (warp == 1) umma::tmem_alloc(tmem_slot, 2 * kCvAccStride);
@@ -340,47 +345,55 @@ static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, size_t smem, 
 
 }  // namespace vfi
 
-extern "C" size_t vfi_conv3x3_prep_bytes(int Cout, int Cin) {
+static bool conv_upscale_ok(int Cout, int upscale) { return upscale == 1 || (upscale == 2 && Cout % 4 == 0); }
+
+extern "C" size_t vfi_conv3x3_prep_bytes(int Cout, int Cin, int upscale) {
     using namespace vfi;
-    if (Cout < 1 || Cin < 4 || Cin % 4) return 0;
-    const ConvTiling t = conv_tiling(Cout, Cin);
-    return (size_t)t.n_nt * t.wbytes;
+    if (Cout < 1 || Cin < 4 || Cin % 4 || !conv_upscale_ok(Cout, upscale)) return 0;
+    const int up2 = upscale * upscale;
+    const ConvTiling t = conv_tiling(Cout / up2, Cin);
+    return (size_t)up2 * t.n_nt * t.wbytes;
 }
 
-extern "C" int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout, int Cin, void* stream) {
+extern "C" int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout, int Cin, int upscale, void* stream) {
     using namespace vfi;
     VFI_REQUIRE(weight && wprep, "vfi_conv3x3_prep_f32: null pointer");
     VFI_REQUIRE(Cout >= 1 && Cin >= 4 && Cin % 4 == 0, "vfi_conv3x3_prep_f32: Cin %d must be a positive multiple of 4", Cin);
-    const ConvTiling t = conv_tiling(Cout, Cin);
-    const int64_t total = (int64_t)t.n_nt * (int64_t)(t.wbytes / 4);
+    VFI_REQUIRE(conv_upscale_ok(Cout, upscale), "vfi_conv3x3_prep_f32: upscale %d with Cout %d", upscale, Cout);
+    const int up2 = upscale * upscale;
+    const ConvTiling t = conv_tiling(Cout / up2, Cin);
+    const int64_t total = (int64_t)up2 * t.n_nt * (int64_t)(t.wbytes / 4);
     const int blocks = (int)min64(ceil_div(total, 256), (int64_t)kNumSMs * 8);
-    conv3x3_prep_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(weight, wprep, Cout, Cin, t.T, t.NPAD, t.n_nt, t.nchunkP);
+    conv3x3_prep_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(weight, wprep, Cout, Cin, t.T, t.NPAD, up2 * t.n_nt,
+                                                                             t.nchunkP, up2);
     VFI_CHECK_LAUNCH("conv3x3_prep_kernel");
     return VFI_OK;
 }
 
-extern "C" int vfi_conv3x3_supported(int Cin, int x_pix_stride, int Cout) {
+extern "C" int vfi_conv3x3_supported(int Cin, int x_pix_stride, int Cout, int upscale) {
     using namespace vfi;
-    if (Cin < 4 || Cin % 4 || x_pix_stride % 4 || x_pix_stride < Cin || Cout < 1) return 0;
-    const ConvTiling t = conv_tiling(Cout, Cin);
+    if (Cin < 4 || Cin % 4 || x_pix_stride % 4 || x_pix_stride < Cin || Cout < 1 || !conv_upscale_ok(Cout, upscale)) return 0;
+    const ConvTiling t = conv_tiling(Cout / (upscale * upscale), Cin);
     return t.wbytes + conv_smem_fixed(t.NPAD) + 2 * (size_t)kCvStageBytes <= (size_t)kCvSmemMax;
 }
 
 extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* bias, const float* slope, const float* residual,
                                float* out, int B, int H, int W, int Cin, int x_pix_stride, int Cout, int out_channels_last,
-                               int out_c_total, int res_c_total, int residual_mode, void* stream) {
+                               int out_c_total, int res_c_total, int residual_mode, int upscale, void* stream) {
     using namespace vfi;
     VFI_REQUIRE(x && wprep && out, "vfi_conv3x3_f32: null pointer");
     VFI_REQUIRE(B >= 0 && H >= 1 && W >= 1, "vfi_conv3x3_f32: bad shape");
-    VFI_REQUIRE(vfi_conv3x3_supported(Cin, x_pix_stride, Cout), "vfi_conv3x3_f32: unsupported Cin %d / pixel stride %d / Cout %d",
-                Cin, x_pix_stride, Cout);
+    VFI_REQUIRE(vfi_conv3x3_supported(Cin, x_pix_stride, Cout, upscale),
+                "vfi_conv3x3_f32: unsupported Cin %d / pixel stride %d / Cout %d / upscale %d", Cin, x_pix_stride, Cout, upscale);
     VFI_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "vfi_conv3x3_f32: x must be 16-byte aligned");
     VFI_REQUIRE(residual_mode >= 0 && residual_mode <= 2 && (residual_mode == 0 || residual), "vfi_conv3x3_f32: residual_mode %d",
                 residual_mode);
-    VFI_REQUIRE(out_c_total >= Cout && (residual_mode == 0 || res_c_total >= Cout), "vfi_conv3x3_f32: channel totals");
+    VFI_REQUIRE(upscale == 1 || residual_mode == 0, "vfi_conv3x3_f32: a residual cannot be combined with the fused PixelShuffle");
+    const int up = upscale, up2 = up * up, Cs = Cout / up2;      // Cs = channels after the shuffle
+    VFI_REQUIRE(out_c_total >= Cs && (residual_mode == 0 || res_c_total >= Cout), "vfi_conv3x3_f32: channel totals");
     if (B == 0) return VFI_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const ConvTiling t = conv_tiling(Cout, Cin);
+    const ConvTiling t = conv_tiling(Cs, Cin);
     CUtensorMap xmap;
     {
         // (channel, y, x, image): y before x so that a box lands column-major in shared memory; 64-byte swizzle
@@ -399,45 +412,52 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
     a.nstage_tile = t.nstage_tile;
     a.nchunk = t.nchunkP;
     a.res_mode = residual_mode;
+    a.bias_stride = up2;
     a.tiles_x = (W + kCvTW - 1) / kCvTW; a.tiles_y = (H + kCvTH - 1) / kCvTH;
     a.n_tiles = B * a.tiles_x * a.tiles_y;
-    const int64_t HW = (int64_t)H * W;
+    // element strides of the output seen from a conv pixel (y, x): with the fused PixelShuffle conv pixel (y, x) owns the
+    // up x up output pixels (up*y + i, up*x + j) of a (B, Cs, up*H, up*W) tensor
+    const int64_t Ho = (int64_t)H * up, Wo = (int64_t)W * up, HWo = Ho * Wo, HW = (int64_t)H * W;
+    int64_t o_pix, o_row, o_c;      // strides of one OUTPUT pixel step, row step, channel step
     if (out_channels_last) {
-        a.out_sb = HW * out_c_total; a.out_sy = (int64_t)W * out_c_total; a.out_sx = out_c_total; a.out_sc = 1;
+        o_pix = out_c_total; o_row = Wo * out_c_total; o_c = 1;
         a.res_sb = HW * res_c_total; a.res_sy = (int64_t)W * res_c_total; a.res_sx = res_c_total; a.res_sc = 1;
     } else {
-        a.out_sb = HW * out_c_total; a.out_sy = W; a.out_sx = 1; a.out_sc = HW;
+        o_pix = 1; o_row = Wo; o_c = HWo;
         a.res_sb = HW * res_c_total; a.res_sy = W; a.res_sx = 1; a.res_sc = HW;
     }
+    a.out_sb = HWo * out_c_total; a.out_sy = o_row * up; a.out_sx = o_pix * up; a.out_sc = o_c;
     int stages = (int)(((size_t)kCvSmemMax - conv_smem_fixed(t.NPAD) - t.wbytes) / kCvStageBytes);
     if (stages > kCvMaxStages) stages = kCvMaxStages;
     a.stages = stages;
     const size_t smem = t.wbytes + (size_t)stages * kCvStageBytes + conv_smem_fixed(t.NPAD);
-    for (int nt = 0; nt < t.n_nt; ++nt) {
-        const int c0 = nt * t.T;
-        a.cn = Cout - c0 < t.T ? Cout - c0 : t.T;
-        a.wprep = wprep + (size_t)nt * (t.wbytes / 4);
-        a.bias = bias ? bias + c0 : nullptr;
-        a.slope = slope ? slope + c0 : nullptr;
-        a.out = out + c0 * a.out_sc;
-        a.res = residual ? residual + c0 * a.res_sc : nullptr;
-        const bool al = ((reinterpret_cast<uintptr_t>(a.out) & 15) == 0) && (a.res == nullptr || (reinterpret_cast<uintptr_t>(a.res) & 15) == 0);
-        a.vec = out_channels_last && al && a.cn % 4 == 0 && out_c_total % 4 == 0 && (residual_mode == 0 || res_c_total % 4 == 0);
-        // vec 2: pixel rows of out / residual are 32-byte aligned too -> 256-bit accesses
-        auto al32 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; };
-        if (a.vec && al32(a.out) && out_c_total % 8 == 0 && (a.res == nullptr || (al32(a.res) && res_c_total % 8 == 0))) a.vec = 2;
-        int rc;
-        switch (t.NPAD) {
-            case 16: rc = conv_launch<16>(a, xmap, smem, st); break;
-            case 32: rc = conv_launch<32>(a, xmap, smem, st); break;
-            case 48: rc = conv_launch<48>(a, xmap, smem, st); break;
-            case 64: rc = conv_launch<64>(a, xmap, smem, st); break;
-            case 72: rc = conv_launch<72>(a, xmap, smem, st); break;
-            default:
-                set_error("vfi_conv3x3_f32: no kernel for a Cout tile padded to %d", t.NPAD);
-                return VFI_ERR_UNSUPPORTED;
+    for (int sub = 0; sub < up2; ++sub) {
+        for (int nt = 0; nt < t.n_nt; ++nt) {
+            const int c0 = nt * t.T;                           // first channel (after the shuffle) of this tile
+            a.cn = Cs - c0 < t.T ? Cs - c0 : t.T;
+            a.wprep = wprep + (size_t)(sub * t.n_nt + nt) * (t.wbytes / 4);
+            a.bias = bias ? bias + (size_t)c0 * up2 + sub : nullptr;
+            a.slope = slope ? slope + c0 : nullptr;
+            a.out = out + c0 * o_c + (sub / up) * o_row + (sub % up) * o_pix;
+            a.res = residual ? residual + c0 * a.res_sc : nullptr;
+            const bool al = ((reinterpret_cast<uintptr_t>(a.out) & 15) == 0) && (a.res == nullptr || (reinterpret_cast<uintptr_t>(a.res) & 15) == 0);
+            a.vec = out_channels_last && al && a.cn % 4 == 0 && out_c_total % 4 == 0 && (residual_mode == 0 || res_c_total % 4 == 0);
+            // vec 2: pixel rows of out / residual are 32-byte aligned too -> 256-bit accesses
+            auto al32 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; };
+            if (a.vec && al32(a.out) && out_c_total % 8 == 0 && (a.res == nullptr || (al32(a.res) && res_c_total % 8 == 0))) a.vec = 2;
+            int rc;
+            switch (t.NPAD) {
+                case 16: rc = conv_launch<16>(a, xmap, smem, st); break;
+                case 32: rc = conv_launch<32>(a, xmap, smem, st); break;
+                case 48: rc = conv_launch<48>(a, xmap, smem, st); break;
+                case 64: rc = conv_launch<64>(a, xmap, smem, st); break;
+                case 72: rc = conv_launch<72>(a, xmap, smem, st); break;
+                default:
+                    set_error("vfi_conv3x3_f32: no kernel for a Cout tile padded to %d", t.NPAD);
+                    return VFI_ERR_UNSUPPORTED;
+            }
+            if (rc != VFI_OK) return rc;
         }
-        if (rc != VFI_OK) return rc;
     }
     return VFI_OK;
 }
