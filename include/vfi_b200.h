@@ -122,6 +122,8 @@ int vfi_attn_f32(const float* q, const float* kv, const float* Wq, const float* 
  * are already absolute displacements and ft0/ft1 are ignored.  ft0/ft1 (B,2,H,W) with strides ft_strides.
  * offs_bias (nG*nS*2 floats or NULL) is added to the raw offsets first (the bias of conv_res_offset, so the conv can
  * run bias-free); offs_channels_last != 0: offs0/offs1 are laid out (B, H, W, nG*nS*2) as a channels-last conv writes them.
+ * q_channels_last / out_channels_last != 0: q is read / out is written as (B, H, W, C) (feat0/feat1 stay planar: they
+ * are gathered).
  * Requires nG == nH (true for every block the reference instantiates; madat.py:121 asserts it).
  */
 int vfi_dattn_f32(const float* q, const float* feat0, const float* feat1, const float* offs0, const float* offs1,
@@ -129,7 +131,8 @@ int vfi_dattn_f32(const float* q, const float* feat0, const float* feat1, const 
                   const float* Wq, const float* bq, const float* Wk, const float* bk, const float* Wv,
                   const float* bv, const float* lin_x, const float* lin_y, float* out, float* score0,
                   float* score1, int B, int C, int H, int W, int nG, int nS, int nH, float offset_scale,
-                  int coords_final, const float* offs_bias, int offs_channels_last, void* stream);
+                  int coords_final, const float* offs_bias, int offs_channels_last, int q_channels_last,
+                  int out_channels_last, void* stream);
 
 /* ---- a6 / a7: modulated deformable convolution -- torchvision.ops.deform_conv2d semantics
  * (call sites modules/dcnv2.py:60-66, models/archive/DCNDAT.py:71-77).

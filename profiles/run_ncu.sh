@@ -5,7 +5,7 @@
 # 3. one --set full capture of the kernel named by the regex.
 set -u
 TAG=${1:-r1}; KRE=${2:-dattn_kernel}; SKIP=${3:-0}; CNT=${4:-3}
-CMD="python bench.py --steps 1 --warmup 3 --no-micro --no-cpu --no-e2e ${BENCH_EXTRA:-}"
+CMD="python bench.py --steps 1 --warmup 3 --no-micro --no-cpu --no-e2e --graph 0 ${BENCH_EXTRA:-}"
 mkdir -p gpurun_out
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_list.log 2>&1

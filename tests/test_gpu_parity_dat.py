@@ -165,6 +165,11 @@ def test_fused_dattn_vs_oracle(vfi, cfg):
     out_cl = fused_deformable_attention(*cu(q, f0, f1), r0, r1, *cu(ft0, ft1), *w, n_groups=nG, n_samples=nS, n_heads=nG,
                                         offset_scale=cfg["scale"], offs_bias=bias.cuda())
     assert_close(out_cl, ref, 2e-5, f"fused dattn, channels-last offsets + bias {cfg}")   # (raw - b) + b re-rounds the offsets
+    # channels-last q: read in place, and the output comes back channels-last with identical values
+    out_qcl = fused_deformable_attention(q.cuda().contiguous(memory_format=torch.channels_last), *cu(f0, f1, raw0, raw1, ft0, ft1), *w,
+                                         n_groups=nG, n_samples=nS, n_heads=nG, offset_scale=cfg["scale"])
+    assert out_qcl.is_contiguous(memory_format=torch.channels_last) and not out_qcl.is_contiguous()
+    assert torch.equal(out_qcl, out), "channels-last q / out must not change the arithmetic"
 
 
 def test_madat_golden(vfi, golden):

@@ -29,6 +29,7 @@ struct DattnArgs {
     const float *Wq, *bq, *Wk, *bk, *Wv, *bv, *lin_x, *lin_y;
     const float* obias;      // optional bias of the offset head (nG*nS*2), added before tanh
     int offs_cl;             // offsets are channels-last: (B, H, W, nG*nS*2)
+    int qo_cl;               // bit 0: q is channels-last (B, H, W, C); bit 1: out is written channels-last
     float *out, *score[2];
     int B, H, W, nS;
     float offset_scale;
@@ -107,9 +108,10 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
         __syncthreads();   // weights staged (first tile) / previous tile's epilogue reads done
         // ---- prologue ----
         {
-            const float* qpix = a.q + ((int64_t)b * C + g * GC) * HW + pix;
+            const int64_t q_sp = (a.qo_cl & 1) ? C : 1, q_sc = (a.qo_cl & 1) ? 1 : HW;
+            const float* qpix = a.q + (int64_t)b * C * HW + pix * q_sp + (g * GC) * q_sc;
 #pragma unroll
-            for (int j = 0; j < GC; ++j) q_s[(g * GC + j) * 32 + lane] = __ldg(qpix + (int64_t)j * HW);
+            for (int j = 0; j < GC; ++j) q_s[(g * GC + j) * 32 + lane] = __ldg(qpix + (int64_t)j * q_sc);
         }
         __syncthreads();
         float cb;
@@ -317,13 +319,14 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
             __syncthreads();
             if (g / Cfg::EPI_H == r) {
                 const int hh = g - r * Cfg::EPI_H;
-                float* op = a.out + ((int64_t)b * C + g * GC) * HW + pix;
+                const int64_t o_sp = (a.qo_cl & 2) ? C : 1, o_sc = (a.qo_cl & 2) ? 1 : HW;
+                float* op = a.out + (int64_t)b * C * HW + pix * o_sp + (g * GC) * o_sc;
 #pragma unroll
                 for (int j = 0; j < GC; ++j) {
                     float acc = epi[((hh * GC + j) * NG + 0) * 32 + lane];
 #pragma unroll
                     for (int gg = 1; gg < NG; ++gg) acc += epi[((hh * GC + j) * NG + gg) * 32 + lane];
-                    if (live) st_stream(op + (int64_t)j * HW, fmaf(acc, inv, __ldg(a.bv + g * GC + j)));
+                    if (live) st_stream(op + (int64_t)j * o_sc, fmaf(acc, inv, __ldg(a.bv + g * GC + j)));
                 }
             }
         }
@@ -359,7 +362,7 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
                              const float* Wk, const float* bk, const float* Wv, const float* bv, const float* lin_x,
                              const float* lin_y, float* out, float* score0, float* score1, int B, int C, int H, int W, int nG,
                              int nS, int nH, float offset_scale, int coords_final, const float* offs_bias, int offs_channels_last,
-                             void* stream) {
+                             int q_channels_last, int out_channels_last, void* stream) {
     using namespace vfi;
     VFI_REQUIRE(q && feat0 && feat1 && offs0 && offs1 && Wq && bq && Wk && bk && Wv && bv && lin_x && lin_y && out,
                 "vfi_dattn_f32: null pointer");
@@ -378,6 +381,7 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
     a.Wq = Wq; a.bq = bq; a.Wk = Wk; a.bk = bk; a.Wv = Wv; a.bv = bv;
     a.lin_x = lin_x; a.lin_y = lin_y;
     a.obias = offs_bias; a.offs_cl = offs_channels_last;
+    a.qo_cl = (q_channels_last ? 1 : 0) | (out_channels_last ? 2 : 0);
     a.out = out; a.score[0] = score0; a.score[1] = score1;
     a.B = B; a.H = H; a.W = W; a.nS = nS;
     a.offset_scale = offset_scale;

@@ -71,7 +71,13 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
     offset_scale*tanh(.) + ft*) or final displacements laid out (b, nG*nS, 2, h, w) (``coords_final=True``).
     """
     dev = _lib.require_cuda(q, feat0, feat1, offs0, offs1)
-    q, feat0, feat1 = _lib.f32c(q), _lib.f32c(feat0), _lib.f32c(feat1)
+    # q is read once per pixel and out written once: both are taken / produced channels-last when q arrives that way
+    # (the conv stacks around the block run NHWC); feat0 / feat1 are gathered and must be planar
+    q_cl = (q.dim() == 4 and q.dtype == torch.float32 and q.shape[1] > 1 and not q.is_contiguous()
+            and q.is_contiguous(memory_format=torch.channels_last))
+    if not q_cl:
+        q = _lib.f32c(q)
+    feat0, feat1 = _lib.f32c(feat0), _lib.f32c(feat1)
     # offsets are read in the layout the conv wrote them: channels-last (B,H,W,nG*nS*2) needs no transpose
     offs_cl = (offs0.dim() == 4 and offs0.dtype == torch.float32 and not offs0.is_contiguous()
                and offs0.is_contiguous(memory_format=torch.channels_last)
@@ -88,7 +94,10 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
         ft_strides = _lib.strides4(ft0)
     else:
         ft_strides = None
-    out = torch.empty((b, c, fh, fw), dtype=torch.float32, device=dev)
+    if q_cl:
+        out = torch.empty((b, fh, fw, c), dtype=torch.float32, device=dev).permute(0, 3, 1, 2)
+    else:
+        out = torch.empty((b, c, fh, fw), dtype=torch.float32, device=dev)
     s0 = s1 = None
     if want_scores:
         s0 = torch.empty((b * n_heads, n_samples, fh * fw), dtype=torch.float32, device=dev)
@@ -100,7 +109,7 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
                                         _lib.linspace_m11(fw, dev).data_ptr(), _lib.linspace_m11(fh, dev).data_ptr(),
                                         out.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), b, c, fh, fw, n_groups, n_samples, n_heads,
                                         float(offset_scale), 1 if coords_final else 0, _lib.ptr(offs_bias), 1 if offs_cl else 0,
-                                        _lib.stream_ptr(dev))
+                                        1 if q_cl else 0, 1 if q_cl else 0, _lib.stream_ptr(dev))
     return (out, s0, s1) if want_scores else out
 
 
