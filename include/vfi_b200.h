@@ -179,6 +179,18 @@ int vfi_conv3x3_f32(const float* x, const float* wprep, const float* bias, const
                     float* out, int B, int H, int W, int Cin, int x_pix_stride, int Cout, int out_channels_last,
                     int out_c_total, int res_c_total, int residual_mode, int upscale, void* stream);
 
+/* ---- a13 / f1: backward passes of the two warps (what train.py reaches through autograd) ----------------------
+ * vfi_splat_bwd_f32: gradients of the summation splat out = splat(in, flow) (softsplat_func.backward,
+ * modules/softsplat.py:364-533): grad_in (B,C,H,W) and grad_flow (B,2,H,W), either may be NULL.  Non-finite targets
+ * get zero gradients and corners are bounds-tested one by one, as in the forward kernel.
+ * vfi_bwarp_bwd_f32: gradients of bwarp (modules/warp.py:7-15) = autograd of F.grid_sample(bilinear, border,
+ * align_corners=True) through the flow -> grid arithmetic: grad_img (zero-filled by the call, then accumulated with
+ * atomics) and grad_flow; either may be NULL.  All tensors NCHW-contiguous fp32. */
+int vfi_splat_bwd_f32(const float* in, const float* flow, const float* grad_out, float* grad_in, float* grad_flow,
+                      int B, int C, int H, int W, void* stream);
+int vfi_bwarp_bwd_f32(const float* img, const float* flow, const float* grad_out, const float* lin_x, const float* lin_y,
+                      float* grad_img, float* grad_flow, int B, int C, int H, int W, void* stream);
+
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vfi_launch_count(void);

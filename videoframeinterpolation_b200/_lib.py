@@ -40,6 +40,8 @@ SIGNATURES = {
     "vfi_conv3x3_prep_bytes": (c_size_t, [c_int] * 3),
     "vfi_conv3x3_prep_f32": (c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p]),
     "vfi_conv3x3_f32": (c_int, [c_void_p] * 6 + [c_int] * 11 + [c_void_p]),
+    "vfi_splat_bwd_f32": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
+    "vfi_bwarp_bwd_f32": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
     "vfi_launch_count": (c_int64, []),
     "vfi_launch_count_reset": (None, []),
 }

@@ -101,9 +101,9 @@ def softsplat(tenIn: torch.Tensor, tenFlow: torch.Tensor, tenMetric: torch.Tenso
     """Forward splatting: 'sum' | 'avg' | 'linear[-eps]' | 'soft[-eps]', eps in addeps / zeroeps / clipeps."""
     head, eps = _check_mode(tenMetric, strMode)
     dev = _lib.require_cuda(tenIn, tenFlow, tenMetric)
-    if tenIn.requires_grad or tenFlow.requires_grad or (tenMetric is not None and tenMetric.requires_grad):
-        if torch.is_grad_enabled():
-            raise _lib.VfiError("vfi_b200 softsplat: backward is not built yet; call under torch.no_grad()")
+    if torch.is_grad_enabled() and (tenIn.requires_grad or tenFlow.requires_grad
+                                    or (tenMetric is not None and tenMetric.requires_grad)):
+        return _softsplat_autograd(tenIn, tenFlow, tenMetric, head, eps)
     B, C, H, W = tenIn.shape
     weight = {"sum": "none", "avg": "ones", "linear": "linear", "soft": "soft"}[head]
     if _fused_ok(B, C, H, W):
@@ -128,11 +128,60 @@ def softsplat(tenIn: torch.Tensor, tenFlow: torch.Tensor, tenMetric: torch.Tenso
     return splat_normalize(num, den, "add", 0.0)
 
 
+class _SplatSumFn(torch.autograd.Function):
+    """Summation splat with the backward of softsplat_func (modules/softsplat.py:364-533): vfi_splat_bwd_f32."""
+
+    @staticmethod
+    def forward(ctx, tenIn, tenFlow):
+        tin, tfl = _lib.f32c(tenIn), _lib.f32c(tenFlow)
+        ctx.save_for_backward(tin, tfl)
+        with torch.no_grad():
+            return softsplat_func.apply(tin, tfl)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        tin, tfl = ctx.saved_tensors
+        dev = tin.device
+        B, C, H, W = tin.shape
+        g = _lib.f32c(grad_out)
+        g_in = torch.empty_like(tin) if ctx.needs_input_grad[0] else None
+        g_flow = torch.empty_like(tfl) if ctx.needs_input_grad[1] else None
+        _lib.call("vfi_splat_bwd_f32", dev, tin.data_ptr(), tfl.data_ptr(), g.data_ptr(), _lib.ptr(g_in), _lib.ptr(g_flow),
+                  B, C, H, W, _lib.stream_ptr(dev))
+        return g_in, g_flow
+
+
+def _softsplat_autograd(tenIn, tenFlow, tenMetric, head: str, eps: Optional[str]):
+    """Training path: the reference's own composition (modules/softsplat.py:245-276) around the differentiable
+    summation splat, so that autograd reaches tenIn, tenFlow and tenMetric."""
+    if head == 'avg':
+        tenIn = torch.cat([tenIn, tenIn.new_ones([tenIn.shape[0], 1, tenIn.shape[2], tenIn.shape[3]])], 1)
+    elif head == 'linear':
+        tenIn = torch.cat([tenIn * tenMetric, tenMetric], 1)
+    elif head == 'soft':
+        e = tenMetric.exp()
+        tenIn = torch.cat([tenIn * e, e], 1)
+    out = _SplatSumFn.apply(tenIn, tenFlow)
+    if head == 'sum':
+        return out
+    norm = out[:, -1:, :, :]
+    if eps is None or eps == 'addeps':
+        norm = norm + 0.0000001
+    elif eps == 'zeroeps':
+        norm = torch.where(norm == 0.0, torch.ones_like(norm), norm)
+    elif eps == 'clipeps':
+        norm = norm.clip(0.0000001, None)
+    return out[:, :-1, :, :] / norm
+
+
 class softsplat_func:
-    """``softsplat_func.apply(tenIn, tenFlow)``: raw summation splat of every channel (forward only)."""
+    """``softsplat_func.apply(tenIn, tenFlow)``: raw summation splat of every channel (differentiable through
+    ``softsplat`` / ``_SplatSumFn``; this entry itself is the plain forward)."""
 
     @staticmethod
     def apply(tenIn: torch.Tensor, tenFlow: torch.Tensor) -> torch.Tensor:
+        if torch.is_grad_enabled() and (tenIn.requires_grad or tenFlow.requires_grad):
+            return _SplatSumFn.apply(tenIn, tenFlow)
         dev = _lib.require_cuda(tenIn, tenFlow)          # CPU tensors: the reference asserts False (352-353)
         B, C, H, W = tenIn.shape
         if _fused_ok(B, C, H, W):

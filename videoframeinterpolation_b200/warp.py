@@ -17,13 +17,43 @@ from .softsplat import softsplat, splat_accumulate, splat_normalize
 __all__ = ["bwarp", "fwarp", "fwarp_using_two_frames", "fwarp_mframes"]
 
 
+class _BwarpFn(torch.autograd.Function):
+    """bwarp with its backward (vfi_bwarp_bwd_f32): the gradients F.grid_sample's autograd gives the reference."""
+
+    @staticmethod
+    def forward(ctx, img, flow):
+        img_c, flow_c = _lib.f32c(img), _lib.f32c(flow)
+        ctx.save_for_backward(img_c, flow_c)
+        with torch.no_grad():
+            return _bwarp_forward(img_c, flow_c)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        img, flow = ctx.saved_tensors
+        dev = img.device
+        B, C, H, W = img.shape
+        g = _lib.f32c(grad_out)
+        g_img = torch.empty_like(img) if ctx.needs_input_grad[0] else None
+        g_flow = torch.empty_like(flow) if ctx.needs_input_grad[1] else None
+        _lib.call("vfi_bwarp_bwd_f32", dev, img.data_ptr(), flow.data_ptr(), g.data_ptr(), _lib.linspace_m11(W, dev).data_ptr(),
+                  _lib.linspace_m11(H, dev).data_ptr(), _lib.ptr(g_img), _lib.ptr(g_flow), B, C, H, W, _lib.stream_ptr(dev))
+        return g_img, g_flow
+
+
 def bwarp(img: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
     """Backward bilinear warp, border clamp.  img (B,C,H,W), flow (B,2,H,W) [ch0 = dx, ch1 = dy, pixels].
 
     NCHW-contiguous and channels-last inputs both run vectorised kernels; the output has the input's
     memory format.  Flow may be a non-contiguous channel slice (e.g. ``pred_scale_3[:, nf:nf+2]``,
-    models/DAT.py:82): strides are passed through, nothing is copied.
+    models/DAT.py:82): strides are passed through, nothing is copied.  Differentiable wrt both arguments.
     """
+    if torch.is_grad_enabled() and (img.requires_grad or flow.requires_grad):
+        _lib.require_cuda(img, flow)
+        return _BwarpFn.apply(img, flow)
+    return _bwarp_forward(img, flow)
+
+
+def _bwarp_forward(img: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
     dev = _lib.require_cuda(img, flow)
     B, _, H, W = flow.shape
     assert img.shape[0] == B and tuple(img.shape[2:]) == (H, W), "img / flow shape mismatch"
