@@ -387,7 +387,17 @@ def run_vfi(args):
         dist.destroy_process_group()
 
 
+def _quiet_native_stdout():
+    """Send file descriptor 1 to stderr for the rest of the run (NCCL prints its version banner to stdout) and return
+    a text stream on the original stdout for the one JSON line."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 def main():
+    _quiet_native_stdout()
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)

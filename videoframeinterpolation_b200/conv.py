@@ -62,18 +62,62 @@ def prepared_weight(conv: nn.Conv2d, upscale: int = 1) -> torch.Tensor:
     return wp
 
 
+def prepared_weight_slice(conv: nn.Conv2d, lo: int, hi: int, pad: int = 0) -> torch.Tensor:
+    """Prepared weights of the sub-convolution that sees input channels [lo, hi) of ``conv`` (plus ``pad`` zero
+    channels): a convolution is linear in its input channels, so conv(cat(a, b)) = conv_a(a) + conv_b(b)."""
+    w = conv.weight
+    key = (w.data_ptr(), w._version, str(w.device), lo, hi, pad)
+    cache = getattr(conv, "_vfi_wprep_slices", None)
+    if cache is None:
+        cache = {}
+        object.__setattr__(conv, "_vfi_wprep_slices", cache)
+    if key in cache:
+        return cache[key]
+    ws = w.detach()[:, lo:hi]
+    if pad:
+        ws = torch.nn.functional.pad(ws, (0, 0, 0, 0, 0, pad))
+    ws = ws.contiguous()
+    cout, cin = ws.shape[:2]
+    wp = torch.empty(_lib.lib().vfi_conv3x3_prep_bytes(cout, cin, 1) // 4, dtype=torch.float32, device=w.device)
+    _lib.call("vfi_conv3x3_prep_f32", w.device, ws.data_ptr(), wp.data_ptr(), cout, cin, 1, _lib.stream_ptr(w.device))
+    for k in [k for k in cache if k[:3] != key[:3]]:      # the weight changed: drop stale slices
+        del cache[k]
+    cache[key] = wp
+    return wp
+
+
+def part_eligible(conv: nn.Conv2d, x: torch.Tensor) -> bool:
+    """:func:`eligible` for a channel-slice pass (x holds only some of conv's input channels)."""
+    if _algo() == "cudnn" or not torch.backends.cudnn.allow_tf32:
+        return False
+    if not (type(conv) is nn.Conv2d and conv.kernel_size == (3, 3) and conv.stride == (1, 1) and conv.padding == (1, 1)
+            and conv.dilation == (1, 1) and conv.groups == 1 and conv.padding_mode == "zeros"):
+        return False
+    if not (x.is_cuda and x.dtype == torch.float32 and not torch.is_grad_enabled() and x.data_ptr() % 16 == 0):
+        return False
+    ps = _nhwc_pixel_stride(x)
+    return ps is not None and bool(_lib.lib().vfi_conv3x3_supported(x.shape[1], ps, conv.out_channels, 1))
+
+
 def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tensor] = None,
             residual: Optional[torch.Tensor] = None, residual_after_act: bool = False, use_bias: bool = True,
-            out_channels_last: bool = True, upscale: int = 1) -> torch.Tensor:
+            out_channels_last: bool = True, upscale: int = 1, in_slice=None) -> torch.Tensor:
     """``act(residual + conv(x) + bias)`` in one kernel; x must satisfy :func:`eligible`.  ``upscale=2`` returns
-    ``act(pixel_shuffle(conv(x) + bias, 2))`` (prelu_weight then has Cout/4 entries)."""
+    ``act(pixel_shuffle(conv(x) + bias, 2))`` (prelu_weight then has Cout/4 entries).  ``in_slice=(lo, hi, pad)``: x
+    holds input channels [lo, hi) of conv followed by ``pad`` zero-weighted channels (one term of a convolution split
+    over its input channels; add the terms through ``residual``)."""
     dev = _lib.require_cuda(x, residual)
     B, Cin, H, W = x.shape
     Cout = conv.out_channels
     ps = _nhwc_pixel_stride(x)
     if ps is None:
         raise _lib.VfiError("conv3x3: x must be channels-last (or a channel slice of a channels-last tensor)")
-    wp = prepared_weight(conv, upscale)
+    if in_slice is not None:
+        lo, hi, pad = in_slice
+        assert upscale == 1 and Cin == hi - lo + pad, "in_slice does not match x"
+        wp = prepared_weight_slice(conv, lo, hi, pad)
+    else:
+        wp = prepared_weight(conv, upscale)
     Cs, Ho, Wo = Cout // (upscale * upscale), H * upscale, W * upscale
     if out_channels_last:
         out = torch.empty((B, Ho, Wo, Cs), dtype=torch.float32, device=dev).permute(0, 3, 1, 2)

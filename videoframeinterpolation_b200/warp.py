@@ -53,13 +53,16 @@ def bwarp(img: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
     return _bwarp_forward(img, flow)
 
 
-def _bwarp_forward(img: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
+def _bwarp_forward(img: torch.Tensor, flow: torch.Tensor, out: torch.Tensor = None) -> torch.Tensor:
+    """``out``: optional (B,C,H,W) fp32 view to write into (any strides, e.g. a channel slice of a wider buffer)."""
     dev = _lib.require_cuda(img, flow)
     B, _, H, W = flow.shape
     assert img.shape[0] == B and tuple(img.shape[2:]) == (H, W), "img / flow shape mismatch"
     img, flow = _lib.f32(img), _lib.f32(flow)
     C = img.shape[1]
-    if img.stride(1) == 1 and C > 1:
+    if out is not None:
+        assert tuple(out.shape) == (B, C, H, W) and out.dtype == torch.float32 and out.device == dev, "bwarp: bad out"
+    elif img.stride(1) == 1 and C > 1:
         out = torch.empty_like(img, memory_format=torch.channels_last)
     else:
         out = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
