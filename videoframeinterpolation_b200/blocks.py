@@ -27,6 +27,16 @@ def conv_bias_act(conv: nn.Conv2d, x: torch.Tensor, prelu: nn.PReLU = None, resi
     tensors take the plain PyTorch route."""
     if _conv.eligible(conv, x):      # tcgen05 implicit GEMM with the epilogue fused (TF32, as cuDNN's default)
         return _conv.conv3x3(conv, x, None if prelu is None else prelu.weight, residual, residual_after_act)
+    cin = conv.in_channels
+    if cin < 8 and cin % 4 and x.dim() == 4 and x.is_cuda and not torch.is_grad_enabled():
+        # RGB-like inputs (the encoder's first conv): zero-pad the channels to 4 in NHWC so that the same kernel runs
+        pad = 4 - cin % 4
+        B, _, H, W = x.shape
+        xp = torch.zeros((B, H, W, cin + pad), dtype=x.dtype, device=x.device).permute(0, 3, 1, 2)
+        if _conv.part_eligible(conv, xp):
+            xp[:, :cin] = x
+            return _conv.conv3x3(conv, xp, None if prelu is None else prelu.weight, residual, residual_after_act,
+                                 in_slice=(0, cin, pad))
     if not _fusable(x, conv):
         y = conv(x)
         if residual is not None and not residual_after_act:
