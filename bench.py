@@ -31,7 +31,7 @@ METRIC = "DAT frames/sec @1080p"
 UNIT = "frames/s"
 H_RAW, W_RAW = 1080, 1920
 # dram__bytes_read.sum + dram__bytes_write.sum of the 1/2-res dattn launch, one ncu --set full capture (profiles/)
-TRAFFIC_DATTN_LV1 = None
+TRAFFIC_DATTN_LV1 = 4273428000 + 137034752     # profiles/r1o_dattn_lv1_ncu_full.txt
 CPU_SAMPLE_HW = (256, 448)        # BASELINE.json configs[0]: the reference's own CPU-runnable case
 
 
@@ -306,8 +306,11 @@ def run_vfi(args):
         clock = ClockSampler(local)
         clock.start()
         _lib.reset_launch_count()
+        from videoframeinterpolation_b200 import conv as vconv
+        vconv.flop_count(reset=True)
         tm = _lib.OpTimer()
         total_ms = timed(step_device, args.steps, tm)
+        conv_flops = vconv.flop_count() / args.steps
         launches = _lib.launch_count()
         clocks = clock.stop()
         ops = tm.summary()
@@ -351,6 +354,20 @@ def run_vfi(args):
                         "(gather floor ~4.3 ms) and fp32 FMA (~2.5 ms), not HBM (DESIGN.md 4.3); traffic from profiles/ ncu capture",
                 "traffic": TRAFFIC_DATTN_LV1 if (P == 1 and (ph, pw) == (1088, 1920)) else None}
     op_ms = {k: {"calls_per_step": c / args.steps, "ms_per_step": ms / args.steps} for k, (c, ms) in ops.items()}
+    # second kernel family of the step: the tensor-core 3x3 convolutions (all launches of a step together)
+    conv_ms = op_ms.get("vfi_conv3x3_f32", {}).get("ms_per_step", 0.0)
+    tf32_peak = 1130.0      # TFLOP/s dense TF32, nominal (B200_PROFILING.md); MEASURED_PEAKS.json has no TF32 entry
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            tf32_peak_meas = float(json.load(f)["bf16_tflops"]) / 2.0
+    except Exception:
+        tf32_peak_meas = None
+    conv_tf = conv_flops / conv_ms / 1e9 if conv_ms > 0 else 0.0
+    roofline_conv = {"kernel": "conv3x3_tc_kernel (tcgen05 kind::tf32, all 3x3 stride-1 convs of the step)", "bound": "tensor",
+                     "achieved": conv_tf, "peak": tf32_peak, "peak_source": "nominal dense TF32 (B200_PROFILING.md)",
+                     "peak_half_of_measured_bf16": tf32_peak_meas, "unit": "TFLOP/s", "frac": conv_tf / tf32_peak,
+                     "flops_per_step": conv_flops, "ms_per_step": conv_ms, "traffic": None,
+                     "note": "shared-memory operand feed of tcgen05.mma (~68 B/clk) bounds it, DESIGN.md 4.6"}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -362,7 +379,7 @@ def run_vfi(args):
                        "l2": "inputs + activations per step (>1 GB) exceed the 126 MB L2"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * h_x0.numel() * 4, "d2h_bytes_per_step": h_out.numel() * 4,
                     "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": int(launches),      # vfi_b200 kernels per K steps (counted on the eager pass; the graph replays the same kernels)
+            "roofline_conv3x3": roofline_conv, "gpu_launches": int(launches),      # vfi_b200 kernels per K steps (counted on the eager pass; the graph replays the same kernels)
             "clocks": clocks, "roofline": roofline, "vfi_ops_ms": op_ms}
 
     if rank == 0:

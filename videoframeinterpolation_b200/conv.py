@@ -15,6 +15,16 @@ import torch.nn as nn
 from . import _lib
 
 
+_flops = [0]     # multiply-add flops issued through conv3x3 since the last reset (bench.py's tensor-roofline object)
+
+
+def flop_count(reset: bool = False) -> int:
+    n = _flops[0]
+    if reset:
+        _flops[0] = 0
+    return n
+
+
 def _algo() -> str:
     return os.environ.get("VFI_CONV_ALGO", "auto")
 
@@ -136,6 +146,7 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tenso
     if prelu_weight is not None:
         slope = prelu_weight if prelu_weight.numel() == Cs else prelu_weight.expand(Cs).contiguous()
     bias = conv.bias if use_bias else None
+    _flops[0] += 2 * 9 * (Cin if in_slice is None else in_slice[1] - in_slice[0]) * Cout * B * H * W
     _lib.call("vfi_conv3x3_f32", dev, x.data_ptr(), wp.data_ptr(), _lib.ptr(bias), _lib.ptr(slope), _lib.ptr(res), out.data_ptr(),
               B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, Cs, res_c, mode, upscale, _lib.stream_ptr(dev))
     return out
