@@ -39,7 +39,7 @@ constexpr int kCvWinW = kCvTW + 2;
 constexpr int kCvKSteps = 2;                            // 8-channel k-steps per stage (16 channels = one 64-byte swizzle row)
 constexpr int kCvStageBytes = kCvWinW * kCvRows * 64;   // 160 pixel rows x 64 B = 10240 B
 constexpr int kCvThreads = 320;                         // producer warp, MMA warp, 8 epilogue warps
-constexpr int kCvMaxStages = 6;
+constexpr int kCvMaxStages = 12;
 constexpr int kCvSmemMax = 232448;                      // 227 KB opt-in limit
 constexpr int kCvAccStride = 256;                       // TMEM columns between the two accumulators
 
@@ -56,6 +56,7 @@ struct ConvArgs {
     int64_t res_sb, res_sy, res_sx, res_sc;
     int stages, tiles_x, tiles_y, n_tiles;
     int bias_stride;
+    int staged;           // CTA pairs, NHWC: output (and residual) tiles go through shared memory and TMA (omap / rmap)
     int dbg;              // bring-up switches (VFI_CONV_DBG): 1 = no TMA loads, 2 = no epilogue stores, 4 = no MMAs
 };
 
@@ -63,24 +64,29 @@ struct ConvArgs {
 // [dx][chunk nchunkP][k-half][n = dy * NPAD + co][4], RN-rounded to TF32, zero where co / ci are padding
 // up2 > 1 (fused PixelShuffle): tiles are ordered [sub-position][channel tile] and row nn of a tile is conv channel
 // (tile_c * T + nn) * up2 + sub, i.e. every tile produces all its channels for ONE of the up2 output pixels.
+// ctas = 2: the N rows (dy * NPAD + co, padded to `ntot`) are split in two halves, one block per CTA of the pair:
+// [tile][cta][dx][chunk][k-half][n_local ntot/ctas][4].
 __global__ void conv3x3_prep_kernel(const float* __restrict__ w, float* __restrict__ wprep, int Cout, int Cin, int T, int NPAD,
-                                    int n_nt, int nchunkP, int up2) {
-    const int64_t per_tile = (int64_t)3 * nchunkP * 2 * 3 * NPAD * 4;
+                                    int n_nt, int nchunkP, int up2, int ntot, int ctas) {
+    const int nh = ntot / ctas;
+    const int64_t per_tile = (int64_t)ctas * 3 * nchunkP * 2 * nh * 4;
     const int64_t total = per_tile * n_nt;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         int64_t r = i;
         const int e = (int)(r % 4); r /= 4;
-        const int n = (int)(r % (3 * NPAD)); r /= 3 * NPAD;
+        const int nl = (int)(r % nh); r /= nh;
         const int kh = (int)(r % 2); r /= 2;
         const int c = (int)(r % nchunkP); r /= nchunkP;
         const int dx = (int)(r % 3); r /= 3;
+        const int cta = (int)(r % ctas); r /= ctas;
         const int nt = (int)r;
+        const int n = cta * nh + nl;
         const int dy = n / NPAD, nn = n - dy * NPAD;
         const int n_ct = n_nt / up2, sub = nt / n_ct, tc = nt - sub * n_ct;
         const int cc = tc * T + nn;                      // channel after the shuffle (== conv channel when up2 == 1)
         const int co = cc * up2 + sub, ci = c * 8 + kh * 4 + e;
         float v = 0.0f;
-        if (nn < T && cc < Cout / up2 && ci < Cin) v = w[((int64_t)co * Cin + ci) * 9 + dy * 3 + dx];
+        if (dy < 3 && nn < T && cc < Cout / up2 && ci < Cin) v = w[((int64_t)co * Cin + ci) * 9 + dy * 3 + dx];
         uint32_t t;
         asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(v));
         wprep[i] = __uint_as_float(t);
@@ -105,13 +111,21 @@ __device__ __forceinline__ bool elect_one() {
     return p != 0;
 }
 
-template <int NPAD>
-__global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArgs a, const __grid_constant__ CUtensorMap xmap) {
-    constexpr int N = 3 * NPAD;
+// CTAS = 2: the kernel runs as CTA pairs (cluster of 2, tcgen05 cta_group::2): one MMA covers the two tiles of the pair
+// (M = 256), every CTA keeps only HALF of the weight rows in shared memory, and the tensor cores of each SM read
+// half as many B bytes per tile -- the shared-memory operand feed is what bounds this kernel.
+template <int NPAD, int CTAS, bool STAGED>
+__global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArgs a, const __grid_constant__ CUtensorMap xmap,
+                                                                   const __grid_constant__ CUtensorMap omap,
+                                                                   const __grid_constant__ CUtensorMap rmap) {
+    constexpr int N = CTAS == 1 ? 3 * NPAD : (3 * NPAD + 15) / 16 * 16;    // UMMA N (cta_group::2 wants a multiple of 16)
+    constexpr int NH = N / CTAS;                                          // B rows held by this CTA
+    const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
+    const bool leader = rank == 0;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int nchunkP = a.nchunk;
-    constexpr uint32_t slab = 2 * N * 16;                       // one (dx, chunk) B slab
+    constexpr uint32_t slab = 2 * NH * 16;                      // one (dx, chunk) B slab of this CTA
     const uint32_t per_dx = (uint32_t)nchunkP * slab;
     const uint32_t wbytes = 3 * per_dx;
     uint8_t* b_s = smem;
@@ -123,52 +137,77 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
     uint64_t* wfull = empty + kCvMaxStages;
     uint64_t* tfull = wfull + 1;     // [2]
     uint64_t* tempty = tfull + 2;    // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    uint64_t* pfull = tempty + 2;    // [stages] CTA pairs: "the peer's stage s is full", signalled by the peer's forwarding warp
+    uint64_t* rfull = pfull + kCvMaxStages;   // [2] staged epilogue: residual tile landed in staging buffer
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 2);
+    // staging buffers of the epilogue: 2 x [8 x][14 y][cn] floats, 128-byte aligned, after the barriers
+    float* stg = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot + 1) + 127) & ~(uintptr_t)127);
+    const int stg_floats = kCvTW * kCvTH * a.cn;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int s = 0; s < a.stages; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], 1);
+            mbar_init(&pfull[s], 1);
         }
         mbar_init(wfull, 1);
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tfull[s], 1);
-            mbar_init(&tempty[s], 2 * kCvM);
+            mbar_init(&tempty[s], CTAS * 8);  // one arrival per epilogue warp (of both CTAs, on the leader's barrier)
+            mbar_init(&rfull[s], 1);
         }
         fence_mbar_init();
         tma_prefetch_desc(&xmap);
+        if (STAGED) {
+            tma_prefetch_desc(&omap);
+            tma_prefetch_desc(&rmap);
+        }
     }
+    __syncthreads();      // barriers initialised before any thread of this CTA touches them
     for (int i = tid; i < NPAD; i += kCvThreads) {
         bias_s[i] = (a.bias && i < a.cn) ? a.bias[(size_t)i * a.bias_stride] : 0.0f;
         slope_s[i] = (a.slope && i < a.cn) ? a.slope[i] : 1.0f;
     }
-    if (warp == 1) umma::tmem_alloc(tmem_slot, 2 * kCvAccStride);
+    if (warp == 1) {
+        if (CTAS == 2) umma::tmem_alloc_2sm(tmem_slot, 2 * kCvAccStride);
+        else umma::tmem_alloc(tmem_slot, 2 * kCvAccStride);
+    }
+    if (warp == 0 && elect_one()) {      // resident weights of this CTA
+        mbar_arrive_expect_tx(wfull, wbytes);
+        const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(a.wprep) + (size_t)rank * wbytes;
+        for (int t = 0; t < 3; ++t) bulk_load_1d(b_s + t * per_dx, wsrc + (size_t)t * per_dx, per_dx, wfull);
+    }
     umma::fence_before();
-    __syncthreads();
+    if (CTAS == 2) {
+        mbar_wait(wfull, 0);             // the leader's MMAs read the peer's weights too: both halves before the pair starts
+        cluster_sync_all();
+    } else {
+        __syncthreads();
+    }
     umma::fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const int tiles_per_img = a.tiles_x * a.tiles_y;
+    // work unit = CTAS horizontally consecutive tiles; a unit past the end gives this CTA an all-padding tile
+    const int n_units = (a.n_tiles + CTAS - 1) / CTAS, unit0 = blockIdx.x / CTAS, unit_step = gridDim.x / CTAS;
 
     if (warp == 0) {
         // ---- producer (whole warp converged, one elected lane issues): resident weights once, then the window ring ----
-        if (elect_one()) {
-            mbar_arrive_expect_tx(wfull, wbytes);
-            for (int t = 0; t < 3; ++t)
-                bulk_load_1d(b_s + t * per_dx, reinterpret_cast<const uint8_t*>(a.wprep) + (size_t)t * per_dx, per_dx, wfull);
-        }
         uint32_t s = 0, ph = 0;
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        for (int unit = unit0; unit < n_units; unit += unit_step) {
+            const int tile = unit * CTAS + (int)rank;
             const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
             for (int st = 0; st < a.nstage_tile; ++st) {
                 mbar_wait(&empty[s], ph ^ 1);
                 if (elect_one()) {
+                    // box {16 ch, 16 y, 10 x, 1 image} at (16 st, y0 - 1, x0 - 1, b); channels >= Cin and images >= B read as 0
+                    // every CTA fills its own ring and signals its own barrier; in a pair the peer's warp 1 forwards
+                    // "stage full" to the leader's MMA warp
                     if (a.dbg & 1) {
                         mbar_arrive(&full[s]);
                     } else {
                         mbar_arrive_expect_tx(&full[s], kCvStageBytes);
-                        // box {16 ch, 16 y, 10 x, 1 image} at (16 st, y0 - 1, x0 - 1, b); channels >= Cin read as 0
                         tma_load_4d(a_ring + s * kCvStageBytes, &xmap, &full[s], 16 * st, ty * kCvTH - 1, tx * kCvTW - 1, b);
                     }
                 }
@@ -176,21 +215,22 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                 if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 && leader) {
         // ---- MMA issuer (whole warp converged; descriptors are warp-uniform, one elected lane issues) ----
-        constexpr uint32_t idesc = umma::idesc_tf32(kCvM, N);
+        constexpr uint32_t idesc = umma::idesc_tf32(kCvM * CTAS, N);
         // A: [x][y][64 B] rows in the 64-byte swizzle (8-row groups 512 B apart); B: [k-half][n][16 B], no swizzle
         const uint64_t a_desc0 = umma::desc_kmajor_sw64(smem_u32(a_ring), 512);
-        const uint64_t b_desc0 = umma::desc_kmajor(smem_u32(b_s), N * 16, 128);
+        const uint64_t b_desc0 = umma::desc_kmajor(smem_u32(b_s), NH * 16, 128);
         mbar_wait(wfull, 0);
         uint32_t s = 0, ph = 0, i = 0;
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++i) {
+        for (int unit = unit0; unit < n_units; unit += unit_step, ++i) {
             const uint32_t acc = i & 1;
             mbar_wait(&tempty[acc], ((i >> 1) & 1) ^ 1);
             umma::fence_after();
             const uint32_t d = tmem_base + acc * kCvAccStride;
             for (int st = 0; st < a.nstage_tile; ++st) {
                 mbar_wait(&full[s], ph);
+                if (CTAS == 2) mbar_wait(&pfull[s], ph);
                 umma::fence_after();
                 if (elect_one()) {
                     const uint64_t ad0 = a_desc0 + (uint64_t)((s * kCvStageBytes) >> 4);
@@ -203,33 +243,65 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                                 for (int dx = 0; dx < 3; ++dx) {
                                     const uint64_t ad = ad0 + (uint64_t)((j * 32 + dx * kCvRows * 64) >> 4);
                                     const uint64_t bd = bd0 + (uint64_t)((dx * per_dx + j * slab) >> 4);
-                                    umma::mma_tf32(d, ad, bd, idesc, (j == 0 && dx == 0) ? (uint32_t)(st != 0) : 1u);
+                                    const uint32_t accum = (j == 0 && dx == 0) ? (uint32_t)(st != 0) : 1u;
+                                    if (CTAS == 2) umma::mma_tf32_2sm(d, ad, bd, idesc, accum);
+                                    else umma::mma_tf32(d, ad, bd, idesc, accum);
                                 }
                             }
                         }
                     }
-                    umma::commit(&empty[s]);
-                    if (st == a.nstage_tile - 1) umma::commit(&tfull[acc]);
+                    if (CTAS == 2) {
+                        umma::commit_2sm(&empty[s], 0b11);
+                        if (st == a.nstage_tile - 1) umma::commit_2sm(&tfull[acc], 0b11);
+                    } else {
+                        umma::commit(&empty[s]);
+                        if (st == a.nstage_tile - 1) umma::commit(&tfull[acc]);
+                    }
                 }
                 __syncwarp();
                 if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
             }
         }
-    } else {
+    } else if (warp == 1) {
+        // ---- peer CTA of a pair: forward "my stage s is full" to the leader's MMA warp ----
+        uint32_t s = 0, ph = 0;
+        for (int unit = unit0; unit < n_units; unit += unit_step) {
+            for (int st = 0; st < a.nstage_tile; ++st) {
+                mbar_wait(&full[s], ph);
+                if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&pfull[s]), 0));
+                __syncwarp();
+                if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp >= 2) {
         // ---- epilogue warps: TMEM lane group = warp % 4; lane = pixel (column-major: m = 16 * column + row) ----
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int m = q * 32 + lane, lx = m >> 4, ly = m & 15;
+        const uint32_t lead_tempty0 = CTAS == 2 ? mapa_shared(smem_u32(&tempty[0]), 0) : 0u;
+        const bool io_thread = warp == 2 && lane == 0;         // issues the TMA stores / residual loads of the staged path
+        const bool stg_res = STAGED && a.res_mode != 0;
+        const uint32_t stg_bytes = (uint32_t)stg_floats * 4;
+        if (stg_res && io_thread && unit0 < n_units) {          // residual tile of the first unit
+            const int t0 = unit0 * CTAS + (int)rank, b0 = t0 / tiles_per_img, r0 = t0 - b0 * tiles_per_img;
+            mbar_arrive_expect_tx(&rfull[0], stg_bytes);
+            tma_load_4d(stg, &rmap, &rfull[0], 0, (r0 / a.tiles_x) * kCvTH, (r0 % a.tiles_x) * kCvTW, b0);
+        }
+        const bool rowok = ly >= 1 && ly <= kCvTH;
         uint32_t i = 0;
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++i) {
+        for (int unit = unit0; unit < n_units; unit += unit_step, ++i) {
+            const int tile = unit * CTAS + (int)rank;
             const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
             const uint32_t acc = i & 1;
+            float* sbuf = stg + (i & 1) * stg_floats;
+            float* slot = sbuf + (lx * kCvTH + ly - 1) * a.cn;
+            if (stg_res) mbar_wait(&rfull[i & 1], (i >> 1) & 1);
             mbar_wait(&tfull[acc], (i >> 1) & 1);
             __syncwarp();                  // tcgen05.ld and the shuffles below are warp-collective
             umma::fence_after();
             const uint32_t taddr = tmem_base + acc * kCvAccStride + ((uint32_t)(q * 32) << 16);
             const int y = ty * kCvTH + ly - 1, x = tx * kCvTW + lx;
-            const bool valid = ly >= 1 && ly <= kCvTH && y < a.H && x < a.W && !(a.dbg & 2);
+            const bool valid = ly >= 1 && ly <= kCvTH && y < a.H && x < a.W && tile < a.n_tiles && !(a.dbg & 2);
             float* o = a.out + b * a.out_sb + y * a.out_sy + x * a.out_sx;
             const float* rp = a.res ? a.res + b * a.res_sb + y * a.res_sy + x * a.res_sx : nullptr;
             // two warps share each TMEM lane quadrant and take alternate 8-channel chunks (latency hiding: the
@@ -247,7 +319,30 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                     const float dn = __shfl_down_sync(0xffffffffu, p2[k], 1);    // plane dy=+1 of the row below
                     t[k] = __fadd_rn(__fadd_rn(up, p1[k]), dn);
                 }
-                if (valid && a.vec) {
+                if (STAGED) {
+                    // NHWC through shared memory: [x][y][cn] tile, residual already there (TMA), result written in place
+                    if (rowok) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            if (c0 + 4 * h < a.cn) {
+                                float4* sp = reinterpret_cast<float4*>(slot + c0) + h;
+                                float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
+                                if (a.res_mode) rr = *sp;
+                                const float rv[4] = {rr.x, rr.y, rr.z, rr.w};
+                                float u[4];
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    const int c = c0 + 4 * h + k;
+                                    u[k] = __fadd_rn(t[4 * h + k], bias_s[c]);
+                                    if (a.res_mode == 1) u[k] = __fadd_rn(rv[k], u[k]);
+                                    if (a.slope) u[k] = u[k] > 0.0f ? u[k] : __fmul_rn(slope_s[c], u[k]);
+                                    if (a.res_mode == 2) u[k] = __fadd_rn(rv[k], u[k]);
+                                }
+                                *sp = make_float4(u[0], u[1], u[2], u[3]);
+                            }
+                        }
+                    }
+                } else if (valid && a.vec) {
                     // NHWC: lane = pixel, 8 consecutive channels = one 32-byte sector per thread
                     float rv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                     const bool full8 = c0 + 8 <= a.cn;
@@ -299,21 +394,56 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             }
             __syncwarp();
             umma::fence_before();
-            mbar_arrive(&tempty[acc]);     // every TMEM read of this tile is done: the MMA warp may overwrite it
+            if (lane == 0) {               // every TMEM read of this warp is done: the MMA warp may overwrite the accumulator
+                if (CTAS == 2) mbar_arrive_cluster(lead_tempty0 + acc * 8);
+                else mbar_arrive(&tempty[acc]);
+            }
+            if (STAGED) {
+                fence_proxy_async_smem();                       // my writes to the tile -> visible to the TMA store
+                if (io_thread) bulk_wait_group_read<0>();       // the previous tile's store has left the OTHER buffer
+                named_bar_sync(1, 8 * 32);
+                if (io_thread) {
+                    if (!(a.dbg & 2)) {
+                        tma_store_4d(&omap, sbuf, 0, ty * kCvTH, tx * kCvTW, b);     // clipped at the image border / dummy tiles
+                        bulk_commit_group();
+                    }
+                    const int nu = unit + unit_step;
+                    if (stg_res && nu < n_units) {              // residual of the next tile into the buffer that just became free
+                        const int t2 = nu * CTAS + (int)rank, b2 = t2 / tiles_per_img, r2 = t2 - b2 * tiles_per_img;
+                        mbar_arrive_expect_tx(&rfull[(i + 1) & 1], stg_bytes);
+                        tma_load_4d(stg + ((i + 1) & 1) * stg_floats, &rmap, &rfull[(i + 1) & 1], 0, (r2 / a.tiles_x) * kCvTH,
+                                    (r2 % a.tiles_x) * kCvTW, b2);
+                    }
+                }
+            }
         }
+        if (STAGED && io_thread) bulk_wait_group<0>();        // outstanding stores read shared memory: finish before exit
     }
     umma::fence_before();
-    __syncthreads();
-    if (warp == 1) umma::tmem_dealloc(tmem_base, 2 * kCvAccStride);
+    if (CTAS == 2) cluster_sync_all();
+    else __syncthreads();
+    if (warp == 1) {
+        if (CTAS == 2) umma::tmem_dealloc_2sm(tmem_base, 2 * kCvAccStride);
+        else umma::tmem_dealloc(tmem_base, 2 * kCvAccStride);
+    }
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------
+static int conv_ctas() {      // CTAs per MMA: 2 = CTA pairs (tcgen05 cta_group::2); VFI_CONV_CTAS=1 keeps single-CTA MMAs
+    static int c = 0;
+    if (!c) {
+        const char* e = getenv("VFI_CONV_CTAS");
+        c = (e && atoi(e) == 1) ? 1 : 2;
+    }
+    return c;
+}
 struct ConvTiling {
-    int T, NPAD, n_nt, nstage_tile, nchunkP;
-    size_t wbytes;      // resident weights of one Cout tile
+    int T, NPAD, n_nt, nstage_tile, nchunkP, ctas, ntot;
+    size_t wbytes;      // resident weights of one Cout tile IN ONE CTA
 };
 static ConvTiling conv_tiling(int Cout, int Cin) {
     ConvTiling t;
+    t.ctas = conv_ctas();
     if (Cout <= 72) t.T = Cout;                         // one tile
     else if (Cout % 72 == 0) t.T = 72;
     else t.T = 64;
@@ -325,22 +455,48 @@ static ConvTiling conv_tiling(int Cout, int Cin) {
     const int nchunk = (Cin + 7) / 8;                   // a trailing half chunk is zero-filled by TMA (and by prep)
     t.nstage_tile = (nchunk + kCvKSteps - 1) / kCvKSteps;
     t.nchunkP = nchunk;
-    t.wbytes = (size_t)3 * t.nchunkP * 2 * 3 * t.NPAD * 16;
+    t.ntot = t.ctas == 1 ? 3 * t.NPAD : (3 * t.NPAD + 15) / 16 * 16;
+    t.wbytes = (size_t)3 * t.nchunkP * 2 * (t.ntot / t.ctas) * 16;
     return t;
 }
-static size_t conv_smem_fixed(int NPAD) { return 2048 + 2 * NPAD * 4 + (2 * kCvMaxStages + 5) * 8 + 16; }   // 2 x 1024 alignment slack
+static size_t conv_smem_fixed(int NPAD) { return 2048 + 2 * NPAD * 4 + (3 * kCvMaxStages + 7) * 8 + 16 + 128; }
+static size_t conv_stg_bytes(int cn) { return (size_t)2 * kCvTW * kCvTH * cn * 4; }   // 2 x 1024 alignment slack
 
-template <int NPAD>
-static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, size_t smem, cudaStream_t st) {
+template <int NPAD, int CTAS, bool STAGED>
+static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& omap, const CUtensorMap& rmap, size_t smem,
+                       cudaStream_t st) {
     static bool attr = false;
     if (!attr) {
-        VFI_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<NPAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCvSmemMax));
+        VFI_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<NPAD, CTAS, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCvSmemMax));
         attr = true;
     }
-    const int grid = a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs;
-    conv3x3_tc_kernel<NPAD><<<grid, kCvThreads, smem, st>>>(a, xmap);
+    const int n_units = (a.n_tiles + CTAS - 1) / CTAS;
+    const int grid = CTAS * (n_units < kNumSMs / CTAS ? n_units : kNumSMs / CTAS);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kCvThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CTAS;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_tc_kernel<NPAD, CTAS, STAGED>, a, xmap, omap, rmap);
+    if (e != cudaSuccess) {
+        set_error("conv3x3_tc_kernel: launch failed: %s", cudaGetErrorString(e));
+        return VFI_ERR_CUDA;
+    }
     VFI_CHECK_LAUNCH("conv3x3_tc_kernel");
     return VFI_OK;
+}
+template <int NPAD>
+static int conv_launch_any(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& omap, const CUtensorMap& rmap, size_t smem,
+                           int ctas, cudaStream_t st) {
+    if (ctas == 2) return a.staged ? conv_launch<NPAD, 2, true>(a, xmap, omap, rmap, smem, st) : conv_launch<NPAD, 2, false>(a, xmap, omap, rmap, smem, st);
+    return conv_launch<NPAD, 1, false>(a, xmap, omap, rmap, smem, st);
 }
 
 }  // namespace vfi
@@ -352,7 +508,7 @@ extern "C" size_t vfi_conv3x3_prep_bytes(int Cout, int Cin, int upscale) {
     if (Cout < 1 || Cin < 4 || Cin % 4 || !conv_upscale_ok(Cout, upscale)) return 0;
     const int up2 = upscale * upscale;
     const ConvTiling t = conv_tiling(Cout / up2, Cin);
-    return (size_t)up2 * t.n_nt * t.wbytes;
+    return (size_t)up2 * t.n_nt * t.ctas * t.wbytes;
 }
 
 extern "C" int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout, int Cin, int upscale, void* stream) {
@@ -362,10 +518,10 @@ extern "C" int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout,
     VFI_REQUIRE(conv_upscale_ok(Cout, upscale), "vfi_conv3x3_prep_f32: upscale %d with Cout %d", upscale, Cout);
     const int up2 = upscale * upscale;
     const ConvTiling t = conv_tiling(Cout / up2, Cin);
-    const int64_t total = (int64_t)up2 * t.n_nt * (int64_t)(t.wbytes / 4);
+    const int64_t total = (int64_t)up2 * t.n_nt * t.ctas * (int64_t)(t.wbytes / 4);
     const int blocks = (int)min64(ceil_div(total, 256), (int64_t)kNumSMs * 8);
     conv3x3_prep_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(weight, wprep, Cout, Cin, t.T, t.NPAD, up2 * t.n_nt,
-                                                                             t.nchunkP, up2);
+                                                                             t.nchunkP, up2, t.ntot, t.ctas);
     VFI_CHECK_LAUNCH("conv3x3_prep_kernel");
     return VFI_OK;
 }
@@ -427,15 +583,14 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
         a.res_sb = HW * res_c_total; a.res_sy = W; a.res_sx = 1; a.res_sc = HW;
     }
     a.out_sb = HWo * out_c_total; a.out_sy = o_row * up; a.out_sx = o_pix * up; a.out_sc = o_c;
-    int stages = (int)(((size_t)kCvSmemMax - conv_smem_fixed(t.NPAD) - t.wbytes) / kCvStageBytes);
-    if (stages > kCvMaxStages) stages = kCvMaxStages;
-    a.stages = stages;
-    const size_t smem = t.wbytes + (size_t)stages * kCvStageBytes + conv_smem_fixed(t.NPAD);
+    // The staged epilogue (tile and residual through shared memory + TMA) is parity-green but measured slower than the
+    // direct 256-bit stores (72 -> 72 at 544x960: 115 vs 95 us, with residual 166 vs 157 us): opt-in, VFI_CONV_STAGED=1.
+    static const bool no_stage = !(getenv("VFI_CONV_STAGED") && atoi(getenv("VFI_CONV_STAGED")) == 1);
     for (int sub = 0; sub < up2; ++sub) {
         for (int nt = 0; nt < t.n_nt; ++nt) {
             const int c0 = nt * t.T;                           // first channel (after the shuffle) of this tile
             a.cn = Cs - c0 < t.T ? Cs - c0 : t.T;
-            a.wprep = wprep + (size_t)(sub * t.n_nt + nt) * (t.wbytes / 4);
+            a.wprep = wprep + (size_t)(sub * t.n_nt + nt) * t.ctas * (t.wbytes / 4);
             a.bias = bias ? bias + (size_t)c0 * up2 + sub : nullptr;
             a.slope = slope ? slope + c0 : nullptr;
             a.out = out + c0 * o_c + (sub / up) * o_row + (sub % up) * o_pix;
@@ -445,13 +600,37 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
             // vec 2: pixel rows of out / residual are 32-byte aligned too -> 256-bit accesses
             auto al32 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; };
             if (a.vec && al32(a.out) && out_c_total % 8 == 0 && (a.res == nullptr || (al32(a.res) && res_c_total % 8 == 0))) a.vec = 2;
+            // staged epilogue (CTA pairs leave room for it): the tile and its residual travel through shared memory and TMA
+            const size_t base = conv_smem_fixed(t.NPAD) + t.wbytes;
+            a.staged = (t.ctas == 2 && a.vec && !no_stage &&
+                        base + conv_stg_bytes(a.cn) + 3 * (size_t)kCvStageBytes <= (size_t)kCvSmemMax) ? 1 : 0;
+            const size_t stg = a.staged ? conv_stg_bytes(a.cn) : 0;
+            int stages = (int)(((size_t)kCvSmemMax - base - stg) / kCvStageBytes);
+            if (stages > kCvMaxStages) stages = kCvMaxStages;
+            if (const char* e = getenv("VFI_CONV_STAGES")) stages = atoi(e) >= 2 && atoi(e) < stages ? atoi(e) : stages;
+            a.stages = stages;
+            const size_t smem = base + stg + (size_t)stages * kCvStageBytes;
+            CUtensorMap omap = xmap, rmap = xmap;      // placeholders when the direct path runs
+            if (a.staged) {
+                // (channel, y, x, image) views of this Cout tile of out / residual; box = one output tile [8 x][14 y][cn]
+                const uint64_t dims[4] = {(uint64_t)a.cn, (uint64_t)H, (uint64_t)W, (uint64_t)B};
+                const uint32_t box[4] = {(uint32_t)a.cn, (uint32_t)kCvTH, (uint32_t)kCvTW, 1};
+                const uint64_t so[3] = {(uint64_t)a.out_sy * 4, (uint64_t)a.out_sx * 4, (uint64_t)a.out_sb * 4};
+                int rc2 = make_tmap_f32_nd(&omap, a.out, 4, dims, so, box, 0);
+                if (rc2 != VFI_OK) return rc2;
+                if (a.res) {
+                    const uint64_t sr[3] = {(uint64_t)a.res_sy * 4, (uint64_t)a.res_sx * 4, (uint64_t)a.res_sb * 4};
+                    rc2 = make_tmap_f32_nd(&rmap, a.res, 4, dims, sr, box, 0);
+                    if (rc2 != VFI_OK) return rc2;
+                }
+            }
             int rc;
             switch (t.NPAD) {
-                case 16: rc = conv_launch<16>(a, xmap, smem, st); break;
-                case 32: rc = conv_launch<32>(a, xmap, smem, st); break;
-                case 48: rc = conv_launch<48>(a, xmap, smem, st); break;
-                case 64: rc = conv_launch<64>(a, xmap, smem, st); break;
-                case 72: rc = conv_launch<72>(a, xmap, smem, st); break;
+                case 16: rc = conv_launch_any<16>(a, xmap, omap, rmap, smem, t.ctas, st); break;
+                case 32: rc = conv_launch_any<32>(a, xmap, omap, rmap, smem, t.ctas, st); break;
+                case 48: rc = conv_launch_any<48>(a, xmap, omap, rmap, smem, t.ctas, st); break;
+                case 64: rc = conv_launch_any<64>(a, xmap, omap, rmap, smem, t.ctas, st); break;
+                case 72: rc = conv_launch_any<72>(a, xmap, omap, rmap, smem, t.ctas, st); break;
                 default:
                     set_error("vfi_conv3x3_f32: no kernel for a Cout tile padded to %d", t.NPAD);
                     return VFI_ERR_UNSUPPORTED;
