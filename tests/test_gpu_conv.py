@@ -22,7 +22,7 @@ def tf32():
     torch.backends.cudnn.allow_tf32 = old
 
 
-def _case(B, Cin, Cout, H, W, prelu=False, res=0, ocl=True, slice_of=None, bias=True, seed=0):
+def _case(B, Cin, Cout, H, W, prelu=False, res=0, ocl=True, slice_of=None, bias=True, seed=0, res_slice_of=None):
     from videoframeinterpolation_b200 import conv as vc
     g = torch.Generator().manual_seed(seed)
     conv = nn.Conv2d(Cin, Cout, 3, 1, 1, bias=bias)
@@ -35,7 +35,10 @@ def _case(B, Cin, Cout, H, W, prelu=False, res=0, ocl=True, slice_of=None, bias=
     xfull = torch.randn(B, ctot, H, W, generator=g).cuda().contiguous(memory_format=torch.channels_last)
     x = xfull[:, ctot - Cin:]
     slope = torch.rand(Cout, generator=g).cuda() if prelu else None
-    r = torch.randn(B, Cout, H, W, generator=g).cuda().contiguous(memory_format=torch.channels_last) if res else None
+    r = None
+    if res:      # optionally the trailing channels of a wider channels-last tensor (pixel stride > Cout)
+        rtot = res_slice_of or Cout
+        r = torch.randn(B, rtot, H, W, generator=g).cuda().contiguous(memory_format=torch.channels_last)[:, rtot - Cout:]
     with torch.no_grad():
         assert vc.eligible(conv, x)
         y = vc.conv3x3(conv, x, slope, r, residual_after_act=(res == 2), out_channels_last=ocl)
@@ -61,6 +64,14 @@ def _case(B, Cin, Cout, H, W, prelu=False, res=0, ocl=True, slice_of=None, bias=
     dict(B=1, Cin=72, Cout=2, H=24, W=24),                               # flow head
     dict(B=1, Cin=36, Cout=36, H=32, W=24, prelu=True, slice_of=72),     # HalfChannelConv5ResBlock side conv (half chunk)
     dict(B=3, Cin=64, Cout=64, H=17, W=9, prelu=True),
+    # residual tiles staged through shared memory by TMA: odd tile count (dummy tile in the last CTA pair), Cout tile not
+    # a multiple of 8, residual = channel slice of a wider tensor, several Cout tiles, many tiles per CTA
+    dict(B=1, Cin=72, Cout=72, H=42, W=24, res=1),
+    dict(B=1, Cin=40, Cout=36, H=30, W=19, prelu=True, res=1),
+    dict(B=2, Cin=72, Cout=72, H=29, W=17, prelu=True, res=2, res_slice_of=144),
+    dict(B=1, Cin=72, Cout=144, H=31, W=23, res=1),
+    dict(B=1, Cin=16, Cout=16, H=300, W=333, prelu=True, res=1),
+    dict(B=1, Cin=72, Cout=72, H=20, W=12, res=1, ocl=False),            # planar residual: direct loads
 ])
 def test_conv3x3_vs_oracle(tf32, cfg):
     _case(**cfg)

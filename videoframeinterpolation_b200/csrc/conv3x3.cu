@@ -56,7 +56,7 @@ struct ConvArgs {
     int64_t res_sb, res_sy, res_sx, res_sc;
     int stages, tiles_x, tiles_y, n_tiles;
     int bias_stride;
-    int staged;           // CTA pairs, NHWC: output (and residual) tiles go through shared memory and TMA (omap / rmap)
+    int staged;           // NHWC residual tiles are prefetched into shared memory by TMA (rmap), one tile ahead of the epilogue
     int dbg;              // bring-up switches (VFI_CONV_DBG): 1 = no TMA loads, 2 = no epilogue stores, 4 = no MMAs
 };
 
@@ -114,9 +114,11 @@ __device__ __forceinline__ bool elect_one() {
 // CTAS = 2: the kernel runs as CTA pairs (cluster of 2, tcgen05 cta_group::2): one MMA covers the two tiles of the pair
 // (M = 256), every CTA keeps only HALF of the weight rows in shared memory, and the tensor cores of each SM read
 // half as many B bytes per tile -- the shared-memory operand feed is what bounds this kernel.
-template <int NPAD, int CTAS, bool STAGED>
+// RSTG: the residual tile [8 x][14 y][cn] of every output tile is fetched by the producer warp with one TMA box into one
+// of two shared-memory buffers while the previous tile is still in its epilogue (a residual read straight from global
+// memory in the epilogue exposes one HBM latency per 8-channel chunk: 157 vs 95 us for 72 -> 72 at 544x960).
+template <int NPAD, int CTAS, bool RSTG>
 __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArgs a, const __grid_constant__ CUtensorMap xmap,
-                                                                   const __grid_constant__ CUtensorMap omap,
                                                                    const __grid_constant__ CUtensorMap rmap) {
     constexpr int N = CTAS == 1 ? 3 * NPAD : (3 * NPAD + 15) / 16 * 16;    // UMMA N (cta_group::2 wants a multiple of 16)
     constexpr int NH = N / CTAS;                                          // B rows held by this CTA
@@ -138,11 +140,12 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
     uint64_t* tfull = wfull + 1;     // [2]
     uint64_t* tempty = tfull + 2;    // [2]
     uint64_t* pfull = tempty + 2;    // [stages] CTA pairs: "the peer's stage s is full", signalled by the peer's forwarding warp
-    uint64_t* rfull = pfull + kCvMaxStages;   // [2] staged epilogue: residual tile landed in staging buffer
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 2);
-    // staging buffers of the epilogue: 2 x [8 x][14 y][cn] floats, 128-byte aligned, after the barriers
-    float* stg = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot + 1) + 127) & ~(uintptr_t)127);
-    const int stg_floats = kCvTW * kCvTH * a.cn;
+    uint64_t* rfull = pfull + kCvMaxStages;   // [2] RSTG: residual tile landed in its buffer
+    uint64_t* rempty = rfull + 2;             // [2] RSTG: the 8 epilogue warps are done with the buffer
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rempty + 2);
+    // residual buffers: 2 x [8 x][14 y][cn] floats, 128-byte aligned, after the barriers
+    float* rbuf = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot + 1) + 127) & ~(uintptr_t)127);
+    const int rfloats = kCvTW * kCvTH * a.cn;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -156,13 +159,11 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             mbar_init(&tfull[s], 1);
             mbar_init(&tempty[s], CTAS * 8);  // one arrival per epilogue warp (of both CTAs, on the leader's barrier)
             mbar_init(&rfull[s], 1);
+            mbar_init(&rempty[s], 8);
         }
         fence_mbar_init();
         tma_prefetch_desc(&xmap);
-        if (STAGED) {
-            tma_prefetch_desc(&omap);
-            tma_prefetch_desc(&rmap);
-        }
+        if (RSTG) tma_prefetch_desc(&rmap);
     }
     __syncthreads();      // barriers initialised before any thread of this CTA touches them
     for (int i = tid; i < NPAD; i += kCvThreads) {
@@ -193,11 +194,21 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
 
     if (warp == 0) {
         // ---- producer (whole warp converged, one elected lane issues): resident weights once, then the window ring ----
-        uint32_t s = 0, ph = 0;
-        for (int unit = unit0; unit < n_units; unit += unit_step) {
+        uint32_t s = 0, ph = 0, i = 0;
+        for (int unit = unit0; unit < n_units; unit += unit_step, ++i) {
             const int tile = unit * CTAS + (int)rank;
             const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
+            if (RSTG) {
+                // residual tile of this output tile into the buffer the epilogue released two tiles ago (rows / columns
+                // / images outside the tensor read as 0 and still count their bytes)
+                mbar_wait(&rempty[i & 1], ((i >> 1) & 1) ^ 1);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(&rfull[i & 1], (uint32_t)rfloats * 4);
+                    tma_load_4d(rbuf + (i & 1) * rfloats, &rmap, &rfull[i & 1], 0, ty * kCvTH, tx * kCvTW, b);
+                }
+                __syncwarp();
+            }
             for (int st = 0; st < a.nstage_tile; ++st) {
                 mbar_wait(&empty[s], ph ^ 1);
                 if (elect_one()) {
@@ -278,24 +289,15 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int m = q * 32 + lane, lx = m >> 4, ly = m & 15;
         const uint32_t lead_tempty0 = CTAS == 2 ? mapa_shared(smem_u32(&tempty[0]), 0) : 0u;
-        const bool io_thread = warp == 2 && lane == 0;         // issues the TMA stores / residual loads of the staged path
-        const bool stg_res = STAGED && a.res_mode != 0;
-        const uint32_t stg_bytes = (uint32_t)stg_floats * 4;
-        if (stg_res && io_thread && unit0 < n_units) {          // residual tile of the first unit
-            const int t0 = unit0 * CTAS + (int)rank, b0 = t0 / tiles_per_img, r0 = t0 - b0 * tiles_per_img;
-            mbar_arrive_expect_tx(&rfull[0], stg_bytes);
-            tma_load_4d(stg, &rmap, &rfull[0], 0, (r0 / a.tiles_x) * kCvTH, (r0 % a.tiles_x) * kCvTW, b0);
-        }
-        const bool rowok = ly >= 1 && ly <= kCvTH;
         uint32_t i = 0;
         for (int unit = unit0; unit < n_units; unit += unit_step, ++i) {
             const int tile = unit * CTAS + (int)rank;
             const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
             const uint32_t acc = i & 1;
-            float* sbuf = stg + (i & 1) * stg_floats;
-            float* slot = sbuf + (lx * kCvTH + ly - 1) * a.cn;
-            if (stg_res) mbar_wait(&rfull[i & 1], (i >> 1) & 1);
+            // my pixel's residual in the shared-memory tile [x][y][cn] (rows 1..14 of the 16-row window are outputs)
+            const float* rslot = rbuf + (i & 1) * rfloats + (lx * kCvTH + ly - 1) * a.cn;
+            if (RSTG) mbar_wait(&rfull[i & 1], (i >> 1) & 1);
             mbar_wait(&tfull[acc], (i >> 1) & 1);
             __syncwarp();                  // tcgen05.ld and the shuffles below are warp-collective
             umma::fence_after();
@@ -319,34 +321,18 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                     const float dn = __shfl_down_sync(0xffffffffu, p2[k], 1);    // plane dy=+1 of the row below
                     t[k] = __fadd_rn(__fadd_rn(up, p1[k]), dn);
                 }
-                if (STAGED) {
-                    // NHWC through shared memory: [x][y][cn] tile, residual already there (TMA), result written in place
-                    if (rowok) {
-#pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            if (c0 + 4 * h < a.cn) {
-                                float4* sp = reinterpret_cast<float4*>(slot + c0) + h;
-                                float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
-                                if (a.res_mode) rr = *sp;
-                                const float rv[4] = {rr.x, rr.y, rr.z, rr.w};
-                                float u[4];
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) {
-                                    const int c = c0 + 4 * h + k;
-                                    u[k] = __fadd_rn(t[4 * h + k], bias_s[c]);
-                                    if (a.res_mode == 1) u[k] = __fadd_rn(rv[k], u[k]);
-                                    if (a.slope) u[k] = u[k] > 0.0f ? u[k] : __fmul_rn(slope_s[c], u[k]);
-                                    if (a.res_mode == 2) u[k] = __fadd_rn(rv[k], u[k]);
-                                }
-                                *sp = make_float4(u[0], u[1], u[2], u[3]);
-                            }
-                        }
-                    }
-                } else if (valid && a.vec) {
+                if (valid && a.vec) {
                     // NHWC: lane = pixel, 8 consecutive channels = one 32-byte sector per thread
                     float rv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                     const bool full8 = c0 + 8 <= a.cn;
-                    if (a.res_mode) {
+                    if (RSTG) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+                            if (c0 + 4 * h < a.cn) {
+                                const float4 rr = reinterpret_cast<const float4*>(rslot + c0)[h];
+                                rv[4 * h] = rr.x; rv[4 * h + 1] = rr.y; rv[4 * h + 2] = rr.z; rv[4 * h + 3] = rr.w;
+                            }
+                    } else if (a.res_mode) {
                         if (a.vec == 2 && full8) {
                             ld_global_v8(rp + c0, rv);
                         } else {
@@ -398,26 +384,8 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                 if (CTAS == 2) mbar_arrive_cluster(lead_tempty0 + acc * 8);
                 else mbar_arrive(&tempty[acc]);
             }
-            if (STAGED) {
-                fence_proxy_async_smem();                       // my writes to the tile -> visible to the TMA store
-                if (io_thread) bulk_wait_group_read<0>();       // the previous tile's store has left the OTHER buffer
-                named_bar_sync(1, 8 * 32);
-                if (io_thread) {
-                    if (!(a.dbg & 2)) {
-                        tma_store_4d(&omap, sbuf, 0, ty * kCvTH, tx * kCvTW, b);     // clipped at the image border / dummy tiles
-                        bulk_commit_group();
-                    }
-                    const int nu = unit + unit_step;
-                    if (stg_res && nu < n_units) {              // residual of the next tile into the buffer that just became free
-                        const int t2 = nu * CTAS + (int)rank, b2 = t2 / tiles_per_img, r2 = t2 - b2 * tiles_per_img;
-                        mbar_arrive_expect_tx(&rfull[(i + 1) & 1], stg_bytes);
-                        tma_load_4d(stg + ((i + 1) & 1) * stg_floats, &rmap, &rfull[(i + 1) & 1], 0, (r2 / a.tiles_x) * kCvTH,
-                                    (r2 % a.tiles_x) * kCvTW, b2);
-                    }
-                }
-            }
+            if (RSTG && lane == 0) mbar_arrive(&rempty[i & 1]);      // (after the __syncwarp above: all lanes have read it)
         }
-        if (STAGED && io_thread) bulk_wait_group<0>();        // outstanding stores read shared memory: finish before exit
     }
     umma::fence_before();
     if (CTAS == 2) cluster_sync_all();
@@ -459,15 +427,15 @@ static ConvTiling conv_tiling(int Cout, int Cin) {
     t.wbytes = (size_t)3 * t.nchunkP * 2 * (t.ntot / t.ctas) * 16;
     return t;
 }
-static size_t conv_smem_fixed(int NPAD) { return 2048 + 2 * NPAD * 4 + (3 * kCvMaxStages + 7) * 8 + 16 + 128; }
-static size_t conv_stg_bytes(int cn) { return (size_t)2 * kCvTW * kCvTH * cn * 4; }   // 2 x 1024 alignment slack
+static size_t conv_smem_fixed(int NPAD) { return 2048 + 2 * NPAD * 4 + (3 * kCvMaxStages + 9) * 8 + 16 + 128; }
+static size_t conv_rbuf_bytes(int cn) { return (size_t)2 * kCvTW * kCvTH * cn * 4; }   // two residual tiles
 
-template <int NPAD, int CTAS, bool STAGED>
-static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& omap, const CUtensorMap& rmap, size_t smem,
+template <int NPAD, int CTAS, bool RSTG>
+static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& rmap, size_t smem,
                        cudaStream_t st) {
     static bool attr = false;
     if (!attr) {
-        VFI_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<NPAD, CTAS, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCvSmemMax));
+        VFI_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<NPAD, CTAS, RSTG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCvSmemMax));
         attr = true;
     }
     const int n_units = (a.n_tiles + CTAS - 1) / CTAS;
@@ -484,7 +452,7 @@ static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtenso
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_tc_kernel<NPAD, CTAS, STAGED>, a, xmap, omap, rmap);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_tc_kernel<NPAD, CTAS, RSTG>, a, xmap, rmap);
     if (e != cudaSuccess) {
         set_error("conv3x3_tc_kernel: launch failed: %s", cudaGetErrorString(e));
         return VFI_ERR_CUDA;
@@ -493,10 +461,10 @@ static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtenso
     return VFI_OK;
 }
 template <int NPAD>
-static int conv_launch_any(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& omap, const CUtensorMap& rmap, size_t smem,
+static int conv_launch_any(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& rmap, size_t smem,
                            int ctas, cudaStream_t st) {
-    if (ctas == 2) return a.staged ? conv_launch<NPAD, 2, true>(a, xmap, omap, rmap, smem, st) : conv_launch<NPAD, 2, false>(a, xmap, omap, rmap, smem, st);
-    return conv_launch<NPAD, 1, false>(a, xmap, omap, rmap, smem, st);
+    if (ctas == 2) return a.staged ? conv_launch<NPAD, 2, true>(a, xmap, rmap, smem, st) : conv_launch<NPAD, 2, false>(a, xmap, rmap, smem, st);
+    return conv_launch<NPAD, 1, false>(a, xmap, rmap, smem, st);
 }
 
 }  // namespace vfi
@@ -583,9 +551,8 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
         a.res_sb = HW * res_c_total; a.res_sy = W; a.res_sx = 1; a.res_sc = HW;
     }
     a.out_sb = HWo * out_c_total; a.out_sy = o_row * up; a.out_sx = o_pix * up; a.out_sc = o_c;
-    // The staged epilogue (tile and residual through shared memory + TMA) is parity-green but measured slower than the
-    // direct 256-bit stores (72 -> 72 at 544x960: 115 vs 95 us, with residual 166 vs 157 us): opt-in, VFI_CONV_STAGED=1.
-    static const bool no_stage = !(getenv("VFI_CONV_STAGED") && atoi(getenv("VFI_CONV_STAGED")) == 1);
+    // VFI_CONV_RSTG=0: read the residual straight from global memory in the epilogue (A/B switch for the TMA-staged path)
+    static const bool no_rstg = getenv("VFI_CONV_RSTG") && atoi(getenv("VFI_CONV_RSTG")) == 0;
     for (int sub = 0; sub < up2; ++sub) {
         for (int nt = 0; nt < t.n_nt; ++nt) {
             const int c0 = nt * t.T;                           // first channel (after the shuffle) of this tile
@@ -600,37 +567,32 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
             // vec 2: pixel rows of out / residual are 32-byte aligned too -> 256-bit accesses
             auto al32 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; };
             if (a.vec && al32(a.out) && out_c_total % 8 == 0 && (a.res == nullptr || (al32(a.res) && res_c_total % 8 == 0))) a.vec = 2;
-            // staged epilogue (CTA pairs leave room for it): the tile and its residual travel through shared memory and TMA
+            // residual through shared memory (CTA pairs leave room for it): two tile buffers filled by TMA, one tile ahead
             const size_t base = conv_smem_fixed(t.NPAD) + t.wbytes;
-            a.staged = (t.ctas == 2 && a.vec && !no_stage &&
-                        base + conv_stg_bytes(a.cn) + 3 * (size_t)kCvStageBytes <= (size_t)kCvSmemMax) ? 1 : 0;
-            const size_t stg = a.staged ? conv_stg_bytes(a.cn) : 0;
-            int stages = (int)(((size_t)kCvSmemMax - base - stg) / kCvStageBytes);
+            a.staged = (t.ctas == 2 && a.vec && a.res && !no_rstg &&
+                        base + conv_rbuf_bytes(a.cn) + 3 * (size_t)kCvStageBytes <= (size_t)kCvSmemMax) ? 1 : 0;
+            const size_t rb = a.staged ? conv_rbuf_bytes(a.cn) : 0;
+            int stages = (int)(((size_t)kCvSmemMax - base - rb) / kCvStageBytes);
             if (stages > kCvMaxStages) stages = kCvMaxStages;
             if (const char* e = getenv("VFI_CONV_STAGES")) stages = atoi(e) >= 2 && atoi(e) < stages ? atoi(e) : stages;
             a.stages = stages;
-            const size_t smem = base + stg + (size_t)stages * kCvStageBytes;
-            CUtensorMap omap = xmap, rmap = xmap;      // placeholders when the direct path runs
+            const size_t smem = base + rb + (size_t)stages * kCvStageBytes;
+            CUtensorMap rmap = xmap;      // placeholder when the direct path runs
             if (a.staged) {
-                // (channel, y, x, image) views of this Cout tile of out / residual; box = one output tile [8 x][14 y][cn]
+                // (channel, y, x, image) view of this Cout tile of the residual; box = one output tile [8 x][14 y][cn]
                 const uint64_t dims[4] = {(uint64_t)a.cn, (uint64_t)H, (uint64_t)W, (uint64_t)B};
                 const uint32_t box[4] = {(uint32_t)a.cn, (uint32_t)kCvTH, (uint32_t)kCvTW, 1};
-                const uint64_t so[3] = {(uint64_t)a.out_sy * 4, (uint64_t)a.out_sx * 4, (uint64_t)a.out_sb * 4};
-                int rc2 = make_tmap_f32_nd(&omap, a.out, 4, dims, so, box, 0);
+                const uint64_t sr[3] = {(uint64_t)a.res_sy * 4, (uint64_t)a.res_sx * 4, (uint64_t)a.res_sb * 4};
+                const int rc2 = make_tmap_f32_nd(&rmap, a.res, 4, dims, sr, box, 0);
                 if (rc2 != VFI_OK) return rc2;
-                if (a.res) {
-                    const uint64_t sr[3] = {(uint64_t)a.res_sy * 4, (uint64_t)a.res_sx * 4, (uint64_t)a.res_sb * 4};
-                    rc2 = make_tmap_f32_nd(&rmap, a.res, 4, dims, sr, box, 0);
-                    if (rc2 != VFI_OK) return rc2;
-                }
             }
             int rc;
             switch (t.NPAD) {
-                case 16: rc = conv_launch_any<16>(a, xmap, omap, rmap, smem, t.ctas, st); break;
-                case 32: rc = conv_launch_any<32>(a, xmap, omap, rmap, smem, t.ctas, st); break;
-                case 48: rc = conv_launch_any<48>(a, xmap, omap, rmap, smem, t.ctas, st); break;
-                case 64: rc = conv_launch_any<64>(a, xmap, omap, rmap, smem, t.ctas, st); break;
-                case 72: rc = conv_launch_any<72>(a, xmap, omap, rmap, smem, t.ctas, st); break;
+                case 16: rc = conv_launch_any<16>(a, xmap, rmap, smem, t.ctas, st); break;
+                case 32: rc = conv_launch_any<32>(a, xmap, rmap, smem, t.ctas, st); break;
+                case 48: rc = conv_launch_any<48>(a, xmap, rmap, smem, t.ctas, st); break;
+                case 64: rc = conv_launch_any<64>(a, xmap, rmap, smem, t.ctas, st); break;
+                case 72: rc = conv_launch_any<72>(a, xmap, rmap, smem, t.ctas, st); break;
                 default:
                     set_error("vfi_conv3x3_f32: no kernel for a Cout tile padded to %d", t.NPAD);
                     return VFI_ERR_UNSUPPORTED;
