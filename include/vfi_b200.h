@@ -156,6 +156,12 @@ size_t vfi_dcn_workspace_bytes(int B, int Cin, int Cout, int H, int W, int kh, i
 int vfi_bias_act_f32(const float* y, const float* bias, const float* slope, const float* residual, float* out,
                      int B, int C, int H, int W, int channels_last, int residual_mode, void* stream);
 
+/* ---- layout change between the conv stacks (channels-last) and the gather kernels (planar): x is (B,H,W,C) with a
+ * pixel stride of x_pix_stride >= C floats (a channel slice of a wider channels-last tensor is fine), out (B,C,H,W)
+ * contiguous.  Replaces the `.contiguous()` PyTorch inserts when models/DAT.py:86-101 hands encoder features
+ * (modules/cnn_encoders.py:6-42) to modules/deformable_attn.py:91-101. */
+int vfi_nhwc_to_nchw_f32(const float* x, float* out, int B, int C, int H, int W, int64_t x_pix_stride, void* stream);
+
 /* ---- 3x3 / stride 1 / pad 1 convolution on the tensor cores (nn.Conv2d(k=3, s=1, p=1) in
  * modules/basic_blocks.py:13-73, modules/cnn_encoders.py:6-42, modules/generator.py:7-24, and conv_res_offset of
  * modules/deformable_attn.py:56-64) with the epilogue of vfi_bias_act_f32 fused in.  TF32 inputs (weights rounded

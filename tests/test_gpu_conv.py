@@ -149,3 +149,27 @@ def test_conv3x3_fused_pixel_shuffle(tf32, shape):
     ref = torch.nn.functional.pixel_shuffle(oracle.conv3x3_tf32(x.cpu(), conv.weight.detach().cpu(), conv.bias.detach().cpu()), 2)
     ref = torch.where(ref > 0, ref, slope.double().cpu().view(1, -1, 1, 1) * ref)
     assert rel_err(y.double().cpu(), ref) <= 1e-5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(1, 72, 36, 40, 27), (2, 32, 16, 19, 33)])
+def test_half_channel_block_without_concat(tf32, shape, monkeypatch):
+    """HalfChannelConv5ResBlock: the rolled-output / slice-input route equals the route with the two torch.cat."""
+    from videoframeinterpolation_b200.blocks import HalfChannelConv5ResBlock
+    B, C, S, H, W = shape
+    torch.manual_seed(3)
+    blk = HalfChannelConv5ResBlock(C, S).cuda()
+    with torch.no_grad():
+        for m in blk.modules():
+            if isinstance(m, nn.PReLU):
+                m.weight.copy_(torch.rand_like(m.weight))
+            if isinstance(m, nn.Conv2d):
+                m.bias.copy_(torch.randn_like(m.bias))
+    x = torch.randn(B, C, H, W, device="cuda").contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        assert blk._fused_ok(x)
+        y = blk(x)
+        monkeypatch.setattr(HalfChannelConv5ResBlock, "_fused_ok", lambda self, t: False)
+        ref = blk(x)
+    assert y.shape == ref.shape
+    assert torch.equal(y, ref) or rel_err(y, ref) <= 1e-6

@@ -36,6 +36,7 @@ SIGNATURES = {
     "vfi_dcn_f32": (c_int, [c_void_p] * 6 + [c_int] * 13 + [c_void_p, c_size_t, c_void_p]),
     "vfi_dcn_workspace_bytes": (c_size_t, [c_int] * 10),
     "vfi_bias_act_f32": (c_int, [c_void_p] * 5 + [c_int] * 6 + [c_void_p]),
+    "vfi_nhwc_to_nchw_f32": (c_int, [c_void_p] * 2 + [c_int] * 4 + [c_int64, c_void_p]),
     "vfi_conv3x3_supported": (c_int, [c_int] * 4),
     "vfi_conv3x3_prep_bytes": (c_size_t, [c_int] * 3),
     "vfi_conv3x3_prep_f32": (c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p]),
@@ -94,6 +95,20 @@ def f32c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     if t.dtype != torch.float32:
         t = t.float()
     return t if t.is_contiguous() else t.contiguous()
+
+
+def planar(t: torch.Tensor) -> torch.Tensor:
+    """fp32 planar NCHW copy of ``t``; a channels-last CUDA tensor (or a channel slice of one) goes through
+    vfi_nhwc_to_nchw_f32 instead of PyTorch's generic strided copy."""
+    if (t.dim() == 4 and t.is_cuda and t.dtype == torch.float32 and not t.is_contiguous() and not torch.is_grad_enabled()
+            and t.shape[1] > 1 and t.shape[1] <= 383 and t.shape[0] <= 65535):
+        B, C, H, W = t.shape
+        sb, sc, sh, sw = t.stride()
+        if sc == 1 and sw >= C and sh == W * sw and sb == H * W * sw:
+            out = torch.empty((B, C, H, W), dtype=torch.float32, device=t.device)
+            call("vfi_nhwc_to_nchw_f32", t.device, t.data_ptr(), out.data_ptr(), B, C, H, W, sw, stream_ptr(t.device))
+            return out
+    return f32c(t)
 
 
 def f32(t: torch.Tensor) -> torch.Tensor:

@@ -125,7 +125,32 @@ class HalfChannelConv5ResBlock(nn.Module):
         keep = t.shape[1] - self.side_c
         return torch.cat((t[:, :keep], conv(t[:, keep:])), dim=1)
 
+    def _fused_ok(self, x):
+        c, s = self.conv1[0].in_channels, self.side_c
+        if not (x.dim() == 4 and c % 8 == 0 and s % 4 == 0 and (c - s) % 4 == 0 and _conv.eligible(self.conv1[0], x)):
+            return False
+        ctot = (c + s + 7) // 8 * 8
+        ok = _lib.lib().vfi_conv3x3_supported
+        return bool(ok(s, ctot, s, 1)) and bool(ok(c, ctot, c, 1))
+
+    def _forward_no_cat(self, x):
+        """Same five convs without the two concatenations: the full convs write their channels ROLLED (side half first)
+        into a wider channels-last buffer [side | keep | side conv output], the side conv reads the first slice and
+        writes the third, and the next full conv reads [keep | side conv output] in place."""
+        B, c, H, W = x.shape
+        s, keep = self.side_c, c - self.side_c
+        ctot = (c + s + 7) // 8 * 8                     # pixel rows stay 32-byte aligned (256-bit stores)
+        t = x
+        for full, side in ((self.conv1, self.conv2), (self.conv3, self.conv4)):
+            buf = torch.empty((B, H, W, ctot), dtype=torch.float32, device=x.device).permute(0, 3, 1, 2)
+            _conv.conv3x3(full[0], t, prelu=full[1], out=buf[:, :c], roll=keep)
+            _conv.conv3x3(side[0], buf[:, :s], prelu=side[1], out=buf[:, c:c + s])
+            t = buf[:, s:c + s]
+        return _conv.conv3x3(self.conv5, t, self.prelu.weight, residual=x)
+
     def forward(self, x):
+        if self._fused_ok(x):
+            return self._forward_no_cat(x)
         t = self._side(self.conv1(x), self.conv2)
         t = self._side(self.conv3(t), self.conv4)
         return conv_bias_act(self.conv5, t, self.prelu, residual=x)

@@ -56,20 +56,38 @@ def eligible(conv: nn.Conv2d, x: torch.Tensor, upscale: int = 1) -> bool:
     return bool(_lib.lib().vfi_conv3x3_supported(conv.in_channels, ps, conv.out_channels, upscale))
 
 
-def prepared_weight(conv: nn.Conv2d, upscale: int = 1) -> torch.Tensor:
-    """TF32-rounded, UMMA-ordered copy of conv.weight, cached on the module and rebuilt when the weight changes."""
+def prepared_weight(conv: nn.Conv2d, upscale: int = 1, roll: int = 0) -> torch.Tensor:
+    """TF32-rounded, UMMA-ordered copy of conv.weight, cached on the module and rebuilt when the weight changes.
+    ``roll``: output channel j of the prepared convolution is channel (j + roll) % Cout of ``conv``."""
     w = conv.weight
-    key = (w.data_ptr(), w._version, str(w.device), upscale)
-    cached = getattr(conv, "_vfi_wprep", None)
-    if cached is not None and cached[0] == key:
-        return cached[1]
+    key = (w.data_ptr(), w._version, str(w.device), upscale, roll)
+    cache = getattr(conv, "_vfi_wprep", None)
+    if cache is None or cache[0] != key[:3]:
+        cache = (key[:3], {})
+        object.__setattr__(conv, "_vfi_wprep", cache)
+    if key in cache[1]:
+        return cache[1][key]
     cout, cin = w.shape[:2]
     nbytes = _lib.lib().vfi_conv3x3_prep_bytes(cout, cin, upscale)
     wp = torch.empty(nbytes // 4, dtype=torch.float32, device=w.device)
-    wc = w.detach().contiguous()          # (Cout, Cin, 3, 3) row-major whatever the module's memory format
+    wc = w.detach()
+    if roll:
+        wc = torch.roll(wc, -roll, 0)
+    wc = wc.contiguous()                  # (Cout, Cin, 3, 3) row-major whatever the module's memory format
     _lib.call("vfi_conv3x3_prep_f32", w.device, wc.data_ptr(), wp.data_ptr(), cout, cin, upscale, _lib.stream_ptr(w.device))
-    object.__setattr__(conv, "_vfi_wprep", (key, wp))
+    cache[1][key] = wp
     return wp
+
+
+def _rolled(owner: nn.Module, name: str, v: torch.Tensor, roll: int) -> torch.Tensor:
+    """torch.roll(v, -roll) cached on ``owner`` (per-channel bias / PReLU slope of a conv whose outputs are rolled)."""
+    key = (v.data_ptr(), v._version, str(v.device), roll)
+    cached = getattr(owner, name, None)
+    if cached is not None and cached[0] == key:
+        return cached[1]
+    r = torch.roll(v.detach(), -roll, 0).contiguous()
+    object.__setattr__(owner, name, (key, r))
+    return r
 
 
 def prepared_weight_slice(conv: nn.Conv2d, lo: int, hi: int, pad: int = 0) -> torch.Tensor:
@@ -111,11 +129,14 @@ def part_eligible(conv: nn.Conv2d, x: torch.Tensor) -> bool:
 
 def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tensor] = None,
             residual: Optional[torch.Tensor] = None, residual_after_act: bool = False, use_bias: bool = True,
-            out_channels_last: bool = True, upscale: int = 1, in_slice=None) -> torch.Tensor:
+            out_channels_last: bool = True, upscale: int = 1, in_slice=None, out: Optional[torch.Tensor] = None,
+            roll: int = 0, prelu: Optional[nn.Module] = None) -> torch.Tensor:
     """``act(residual + conv(x) + bias)`` in one kernel; x must satisfy :func:`eligible`.  ``upscale=2`` returns
     ``act(pixel_shuffle(conv(x) + bias, 2))`` (prelu_weight then has Cout/4 entries).  ``in_slice=(lo, hi, pad)``: x
     holds input channels [lo, hi) of conv followed by ``pad`` zero-weighted channels (one term of a convolution split
-    over its input channels; add the terms through ``residual``)."""
+    over its input channels; add the terms through ``residual``).  ``out``: a (B, Cout, H, W) channels-last view (e.g.
+    a channel slice of a wider buffer) to write into.  ``roll``: output channel j is channel (j + roll) % Cout of
+    ``conv`` (bias and the slopes of ``prelu`` are rolled with it; no residual)."""
     dev = _lib.require_cuda(x, residual)
     B, Cin, H, W = x.shape
     Cout = conv.out_channels
@@ -124,12 +145,17 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tenso
         raise _lib.VfiError("conv3x3: x must be channels-last (or a channel slice of a channels-last tensor)")
     if in_slice is not None:
         lo, hi, pad = in_slice
-        assert upscale == 1 and Cin == hi - lo + pad, "in_slice does not match x"
+        assert upscale == 1 and roll == 0 and Cin == hi - lo + pad, "in_slice does not match x"
         wp = prepared_weight_slice(conv, lo, hi, pad)
     else:
-        wp = prepared_weight(conv, upscale)
+        wp = prepared_weight(conv, upscale, roll)
     Cs, Ho, Wo = Cout // (upscale * upscale), H * upscale, W * upscale
-    if out_channels_last:
+    out_c = Cs
+    if out is not None:
+        out_c = _nhwc_pixel_stride(out)
+        assert out_channels_last and out_c is not None and tuple(out.shape) == (B, Cs, Ho, Wo) and out.dtype == torch.float32, \
+            "out must be a channels-last float32 view of the result's shape"
+    elif out_channels_last:
         out = torch.empty((B, Ho, Wo, Cs), dtype=torch.float32, device=dev).permute(0, 3, 1, 2)
     else:
         out = torch.empty((B, Cs, Ho, Wo), dtype=torch.float32, device=dev)
@@ -142,11 +168,19 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tenso
         else:
             res = residual.contiguous()
         mode = 2 if residual_after_act else 1
+    if prelu is not None:
+        prelu_weight = prelu.weight
     slope = None
     if prelu_weight is not None:
         slope = prelu_weight if prelu_weight.numel() == Cs else prelu_weight.expand(Cs).contiguous()
     bias = conv.bias if use_bias else None
+    if roll:
+        assert residual is None and upscale == 1, "roll: no residual / pixel shuffle"
+        if bias is not None:
+            bias = _rolled(conv, "_vfi_bias_rolled", bias, roll)
+        if slope is not None and prelu_weight.numel() == Cs:
+            slope = _rolled(prelu if prelu is not None else conv, "_vfi_slope_rolled", slope, roll)
     _flops[0] += 2 * 9 * (Cin if in_slice is None else in_slice[1] - in_slice[0]) * Cout * B * H * W
     _lib.call("vfi_conv3x3_f32", dev, x.data_ptr(), wp.data_ptr(), _lib.ptr(bias), _lib.ptr(slope), _lib.ptr(res), out.data_ptr(),
-              B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, Cs, res_c, mode, upscale, _lib.stream_ptr(dev))
+              B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, out_c, res_c, mode, upscale, _lib.stream_ptr(dev))
     return out

@@ -61,6 +61,39 @@ __global__ void __launch_bounds__(256) bias_act_scalar_kernel(const float* __res
     }
 }
 
+// channels-last (pixel stride `ps` floats) -> planar NCHW through a shared-memory tile: the gather kernels (dattn.cu,
+// dsample.cu) read planar features, the conv stacks produce channels-last ones.  Reads are contiguous pixel rows,
+// writes are P consecutive pixels of one plane; the +1 row padding keeps the transposed reads conflict-free.
+template <bool VEC4>
+__global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* __restrict__ x, float* __restrict__ out, int C,
+                                                           int64_t HW, int64_t ps, int P) {
+    extern __shared__ float tr_tile[];      // [P][C + 1]
+    const int b = blockIdx.y, ld = C + 1;
+    const int64_t p0 = (int64_t)blockIdx.x * P;
+    const int np = HW - p0 < (int64_t)P ? (int)(HW - p0) : P;
+    const float* src = x + ((int64_t)b * HW + p0) * ps;
+    if (VEC4) {
+        const int c4 = C / 4;
+        for (int i = threadIdx.x; i < np * c4; i += 256) {
+            const int px = i / c4, c = (i - px * c4) * 4;
+            const float4 v = __ldg(reinterpret_cast<const float4*>(src + (int64_t)px * ps + c));
+            float* t = tr_tile + px * ld + c;
+            t[0] = v.x; t[1] = v.y; t[2] = v.z; t[3] = v.w;
+        }
+    } else {
+        for (int i = threadIdx.x; i < np * C; i += 256) {
+            const int px = i / C, c = i - px * C;
+            tr_tile[px * ld + c] = __ldg(src + (int64_t)px * ps + c);
+        }
+    }
+    __syncthreads();
+    float* dst = out + (int64_t)b * C * HW + p0;
+    for (int i = threadIdx.x; i < C * P; i += 256) {
+        const int c = i / P, px = i - c * P;
+        if (px < np) dst[(int64_t)c * HW + px] = tr_tile[px * ld + c];
+    }
+}
+
 }  // namespace vfi
 
 extern "C" int vfi_bias_act_f32(const float* y, const float* bias, const float* slope, const float* residual, float* out, int B,
@@ -86,5 +119,25 @@ extern "C" int vfi_bias_act_f32(const float* y, const float* bias, const float* 
         bias_act_scalar_kernel<<<blocks, 256, 0, st>>>(y, bias, slope, residual, out, C, HW, total, channels_last, residual_mode);
         VFI_CHECK_LAUNCH("bias_act_scalar_kernel");
     }
+    return VFI_OK;
+}
+
+extern "C" int vfi_nhwc_to_nchw_f32(const float* x, float* out, int B, int C, int H, int W, int64_t x_pix_stride, void* stream) {
+    using namespace vfi;
+    VFI_REQUIRE(x && out, "vfi_nhwc_to_nchw_f32: null pointer");
+    VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && x_pix_stride >= C, "vfi_nhwc_to_nchw_f32: bad shape");
+    VFI_REQUIRE(B <= 65535, "vfi_nhwc_to_nchw_f32: batch %d too large", B);
+    if (B == 0) return VFI_OK;
+    const int64_t HW = (int64_t)H * W;
+    int P = 128;
+    while (P > 32 && (size_t)(C + 1) * P * 4 > 48 * 1024) P /= 2;
+    const size_t smem = (size_t)(C + 1) * P * 4;
+    VFI_REQUIRE(smem <= 48 * 1024, "vfi_nhwc_to_nchw_f32: %d channels do not fit a shared-memory tile", C);
+    const dim3 grid((unsigned)ceil_div(HW, (int64_t)P), B);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool vec = C % 4 == 0 && x_pix_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+    if (vec) nhwc_to_nchw_kernel<true><<<grid, 256, smem, st>>>(x, out, C, HW, x_pix_stride, P);
+    else nhwc_to_nchw_kernel<false><<<grid, 256, smem, st>>>(x, out, C, HW, x_pix_stride, P);
+    VFI_CHECK_LAUNCH("nhwc_to_nchw_kernel");
     return VFI_OK;
 }

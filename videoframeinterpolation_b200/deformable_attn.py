@@ -77,7 +77,7 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
             and q.is_contiguous(memory_format=torch.channels_last))
     if not q_cl:
         q = _lib.f32c(q)
-    feat0, feat1 = _lib.f32c(feat0), _lib.f32c(feat1)
+    feat0, feat1 = _lib.planar(feat0), _lib.planar(feat1)
     # offsets are read in the layout the conv wrote them: channels-last (B,H,W,nG*nS*2) needs no transpose
     offs_cl = (offs0.dim() == 4 and offs0.dtype == torch.float32 and not offs0.is_contiguous()
                and offs0.is_contiguous(memory_format=torch.channels_last)
