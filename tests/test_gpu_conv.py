@@ -173,3 +173,21 @@ def test_half_channel_block_without_concat(tf32, shape, monkeypatch):
         ref = blk(x)
     assert y.shape == ref.shape
     assert torch.equal(y, ref) or rel_err(y, ref) <= 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cfg", [(1, 72, 72, 260, 256, True), (2, 72, 2, 256, 257, False), (1, 76, 76, 300, 220, True), (1, 72, 72, 20, 13, True)])
+def test_conv_transpose_up2_on_tensor_cores(tf32, cfg):
+    """ConvTranspose2d(4, 2, 1) through the 3x3 kernel with the fused PixelShuffle vs PyTorch's own (fp64 on the CPU)."""
+    from videoframeinterpolation_b200 import conv as vc
+    B, cin, cout, H, W, ocl = cfg
+    torch.manual_seed(5)
+    ct = nn.ConvTranspose2d(cin, cout, 4, 2, 1).cuda()
+    x = torch.randn(B, cin, H, W, device="cuda").contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        assert vc.eligible(vc.transpose_as_conv(ct), x, upscale=2)
+        y = vc.conv_transpose_up2(ct, x, out_channels_last=ocl)
+        ref = nn.functional.conv_transpose2d(x.double().cpu(), ct.weight.double().cpu(), ct.bias.double().cpu(), 2, 1)
+    assert y.shape == ref.shape
+    assert y.is_contiguous() if not ocl else y.is_contiguous(memory_format=torch.channels_last)
+    assert rel_err(y.double().cpu(), ref) <= 3e-3      # TF32 inputs

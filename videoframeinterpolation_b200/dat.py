@@ -13,6 +13,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .blocks import BasicResPixelShuffleGenerator, SameChannelResEncoder, run_conv_chain
+from .conv import conv_transpose_up2
 from .dcnv2 import DeformableConv2d
 from .deformable_attn import CrossDeformableAttentionBlockwFlow
 
@@ -79,11 +80,11 @@ class DATwConstantnCv1(nn.Module):
         f0 = self.feature_encoder(x0)
         f1 = self.feature_encoder(x1)
         q4, ft0_4, ft1_4 = self.coarse_query_builder(f0[3], f1[3], t)
-        s3 = self.lv4_to_lv3(torch.cat((q4, ft0_4, ft1_4), dim=1))
+        s3 = conv_transpose_up2(self.lv4_to_lv3, torch.cat((q4, ft0_4, ft1_4), dim=1))
         q3, ft0_3, ft1_3 = s3[:, :nf], s3[:, nf:nf + 2], s3[:, nf + 2:nf + 4]
         a3, ft0_2, ft1_2 = self.dat_lv3(q3, f0[2], f1[2], ft0_3, ft1_3)
-        a2, ft0_1, ft1_1 = self.dat_lv2(self.lv3_to_lv2(a3), f0[1], f1[1], ft0_2, ft1_2)
-        a1 = self.dat_lv1(self.lv2_to_lv1(a2), f0[0], f1[0], ft0_1, ft1_1)
+        a2, ft0_1, ft1_1 = self.dat_lv2(conv_transpose_up2(self.lv3_to_lv2, a3), f0[1], f1[1], ft0_2, ft1_2)
+        a1 = self.dat_lv1(conv_transpose_up2(self.lv2_to_lv1, a2), f0[0], f1[0], ft0_1, ft1_1)
         img = self.pixel_geneartor(a1, mean_)
         if return_flows:
             return img, dict(ft0=[ft0_1, ft0_2, ft0_3, ft0_4], ft1=[ft1_1, ft1_2, ft1_3, ft1_4])

@@ -225,6 +225,6 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
         out = attended + self.mlp(attended)
         if not self.pred_res_flow:
             return out
-        up_ft0 = self.conv_res_flow(mv0) + 2.0 * resize(ft0, scale_factor=2.0)
-        up_ft1 = self.conv_res_flow(mv1) + 2.0 * resize(ft1, scale_factor=2.0)
+        up_ft0 = _conv.conv_transpose_up2(self.conv_res_flow, mv0, out_channels_last=False) + 2.0 * resize(ft0, scale_factor=2.0)
+        up_ft1 = _conv.conv_transpose_up2(self.conv_res_flow, mv1, out_channels_last=False) + 2.0 * resize(ft1, scale_factor=2.0)
         return out, up_ft0, up_ft1
