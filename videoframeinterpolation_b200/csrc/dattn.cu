@@ -36,6 +36,7 @@ struct DattnArgs {
     int coords_final;
     int tw_log2;              // tile = (1 << tw_log2) x (32 >> tw_log2) pixels per warp
     int tiles_x, tiles_y;
+    int zero;                 // always 0 (see the sampling loop)
 };
 
 constexpr int cmax(int a, int b) { return a > b ? a : b; }
@@ -58,7 +59,7 @@ struct DattnCfg {
     static constexpr int UNI = cmax(cmax(RED, 2 * C * 32), EPI);
     static constexpr int PB = NG * SC * 32;
     static constexpr int AB = NG * 32;
-    static constexpr int SMEM_FLOATS = WQ + 2 * WT + UNI + PB + AB;
+    static constexpr int SMEM_FLOATS = WQ + 2 * WT + UNI + PB + AB + 4;   // + rebase flags
     static constexpr int MIN_BLOCKS = NG <= 4 ? 2 : 1;
 };
 
@@ -71,8 +72,11 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
     float* WkT_s = Wq_s + Cfg::WQ;            // [g][r][GCP] = Wk[r][g*GC + cc]
     float* WvT_s = WkT_s + Cfg::WT;           // [g][r][GCP] = Wv[r][g*GC + cc]
     float* uni = WvT_s + Cfg::WT;             // q_s/qp_s | red | epilogue exchange
-    float* pbuf = uni + Cfg::UNI;             // [h][si][lane]
-    float* abuf = pbuf + Cfg::PB;             // [h][lane]
+    float* pbuf = uni + Cfg::UNI;             // [si][h/4][lane][h%4]  (128-bit reads of 4 heads)
+    float* abuf = pbuf + Cfg::PB;             // [h/4][lane][h%4]
+    int* rebase = reinterpret_cast<int*>(abuf + Cfg::AB);   // [chunk parity]: some head re-based its softmax shift
+    static_assert(NG % 4 == 0, "head pairs / quads");
+    constexpr int HP = NG / 2;                // head pairs: FFMA2 lanes = heads (2hp, 2hp+1)
 
     for (int i = threadIdx.x; i < C * C4; i += T) {
         const int r = i / C4, c = i - r * C4;
@@ -142,35 +146,45 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
             cb *= scale;
         }
         __syncthreads();
-        float kt[NG][GC];
+        f32x2 kt2[HP][GC];   // (kt[2hp][cc], kt[2hp+1][cc])
 #pragma unroll
-        for (int h = 0; h < NG; ++h) {
+        for (int hp = 0; hp < HP; ++hp) {
+            float ka[2][GCP];
 #pragma unroll
-            for (int cc = 0; cc < GC; ++cc) kt[h][cc] = 0.0f;
+            for (int e = 0; e < 2; ++e) {
+                const int h = 2 * hp + e;
 #pragma unroll
-            for (int j = 0; j < GC; ++j) {
-                const float qh = qp_s[(h * GC + j) * 32 + lane];
-                const float* wr = WkT_s + (g * C + h * GC + j) * GCP;
+                for (int cc = 0; cc < GCP; ++cc) ka[e][cc] = 0.0f;
 #pragma unroll
-                for (int c4 = 0; c4 < GCP; c4 += 4) {
-                    const float4 w = *reinterpret_cast<const float4*>(wr + c4);
-                    kt[h][c4] = fmaf(qh, w.x, kt[h][c4]);
-                    if (c4 + 1 < GC) kt[h][c4 + 1] = fmaf(qh, w.y, kt[h][c4 + 1]);
-                    if (c4 + 2 < GC) kt[h][c4 + 2] = fmaf(qh, w.z, kt[h][c4 + 2]);
-                    if (c4 + 3 < GC) kt[h][c4 + 3] = fmaf(qh, w.w, kt[h][c4 + 3]);
+                for (int j = 0; j < GC; ++j) {
+                    const float qh = qp_s[(h * GC + j) * 32 + lane];
+                    const float* wr = WkT_s + (g * C + h * GC + j) * GCP;
+#pragma unroll
+                    for (int c4 = 0; c4 < GCP; c4 += 4) {
+                        const float4 w = *reinterpret_cast<const float4*>(wr + c4);
+                        ka[e][c4] = fmaf(qh, w.x, ka[e][c4]);
+                        if (c4 + 1 < GC) ka[e][c4 + 1] = fmaf(qh, w.y, ka[e][c4 + 1]);
+                        if (c4 + 2 < GC) ka[e][c4 + 2] = fmaf(qh, w.z, ka[e][c4 + 2]);
+                        if (c4 + 3 < GC) ka[e][c4 + 3] = fmaf(qh, w.w, ka[e][c4 + 3]);
+                    }
                 }
             }
+#pragma unroll
+            for (int cc = 0; cc < GC; ++cc) kt2[hp][cc] = pack2(ka[0][cc], ka[1][cc]);
         }
+        if (threadIdx.x == 0) rebase[0] = rebase[1] = 0;
         __syncthreads();   // q_s / qp_s (aliased with red) fully consumed
 
-        float yv[NG][GC];
+        f32x2 yv2[HP][GC];   // (yv[2hp][cc], yv[2hp+1][cc])
 #pragma unroll
-        for (int h = 0; h < NG; ++h)
+        for (int hp = 0; hp < HP; ++hp)
 #pragma unroll
-            for (int cc = 0; cc < GC; ++cc) yv[h][cc] = 0.0f;
+            for (int cc = 0; cc < GC; ++cc) yv2[hp][cc] = 0ull;
+        int chunk = 0;
         float m_ref = -INFINITY, sum = 0.0f;
         const float lxv = __ldg(a.lin_x + x), lyv = __ldg(a.lin_y + y);
         float* red = uni;   // [si][h][g][lane]
+        const int plane_bytes = (int)(HW * 4), row_bytes = a.W * 4;   // GC * HW * 4 < 2^31 checked by the host
 
         for (int f = 0; f < 2; ++f) {
             float ftx = 0.0f, fty = 0.0f;
@@ -230,17 +244,28 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
                         dy = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dy)), fty);
                     }
                     const TapGeom tg = sampler_geom(dx, dy, lxv, lyv, a.H, a.W);
+                    const char* north0 = reinterpret_cast<const char*>(featp) + (int64_t)tg.o_nw * 4;
+                    const char* south0 = north0 + row_bytes;
+                    // a.zero == 0 at run time: makes the multiplicand sample-variant, otherwise ptxas hoists
+                    // plane_bytes * cc out of the loop and pays a 64-bit add (2 instructions) per tap row
+                    // (two distinct multiplicands: a shared product would again be split off into adds)
+                    const int pb_n = plane_bytes + tg.o_nw * a.zero, pb_s = plane_bytes + (tg.o_nw + 1) * a.zero;
 #pragma unroll
-                    for (int cc = 0; cc < GC; ++cc) xs[si][cc] = sample_plane(featp + (int64_t)cc * HW, tg, a.W);
+                    for (int cc = 0; cc < GC; ++cc) xs[si][cc] = sample_plane_rows(north0, south0, cc, pb_n, pb_s, tg);
 #pragma unroll
-                    for (int h = 0; h < NG; ++h) {
-                        float d = 0.0f;
+                    for (int hp = 0; hp < HP; ++hp) {
+                        f32x2 d2 = 0ull;
 #pragma unroll
-                        for (int cc = 0; cc < GC; ++cc) d = fmaf(kt[h][cc], xs[si][cc], d);
-                        red[((si * NG + h) * NG + g) * 32 + lane] = d;
+                        for (int cc = 0; cc < GC; ++cc) d2 = fma2s(kt2[hp][cc], xs[si][cc], d2);
+                        float d0, d1;
+                        unpack2(d2, d0, d1);
+                        red[((si * NG + 2 * hp) * NG + g) * 32 + lane] = d0;
+                        red[((si * NG + 2 * hp + 1) * NG + g) * 32 + lane] = d1;
                     }
                 }
                 if (s0 + SC < nS) load_offs(s0 + SC);
+                const int par = chunk & 1;
+                ++chunk;
                 __syncthreads();
                 // ---- C: head g: logits of this chunk, softmax state ----
                 {
@@ -264,33 +289,51 @@ __global__ void __launch_bounds__(DattnCfg<GC, NG>::THREADS, DattnCfg<GC, NG>::M
                         alpha = expf(m_ref - lmax);       // exp(-inf) = 0 on the first chunk
                         m_ref = lmax;
                         sum *= alpha;
+                        rebase[par] = 1;                  // rare: tells phase D to read the alphas
                     }
-                    abuf[g * 32 + lane] = alpha;
+                    abuf[((g >> 2) * 32 + lane) * 4 + (g & 3)] = alpha;
 #pragma unroll
                     for (int si = 0; si < SC; ++si) {
                         const float p = (s0 + si < nS) ? expf(l[si] - m_ref) : 0.0f;
                         sum += p;
-                        pbuf[(g * SC + si) * 32 + lane] = p;
+                        pbuf[((si * (NG / 4) + (g >> 2)) * 32 + lane) * 4 + (g & 3)] = p;
                     }
                 }
                 __syncthreads();
                 // ---- D: weighted accumulation for all heads ----
+                if (rebase[par] != 0) {       // CTA-uniform
 #pragma unroll
-                for (int h = 0; h < NG; ++h) {
-                    const float al = abuf[h * 32 + lane];
-                    if (al != 1.0f) {
+                    for (int h4 = 0; h4 < NG / 4; ++h4) {
+                        const float4 al = *reinterpret_cast<const float4*>(abuf + (h4 * 32 + lane) * 4);
+                        const f32x2 a01 = pack2(al.x, al.y), a23 = pack2(al.z, al.w);
 #pragma unroll
-                        for (int cc = 0; cc < GC; ++cc) yv[h][cc] *= al;
+                        for (int cc = 0; cc < GC; ++cc) {
+                            yv2[2 * h4][cc] = mul2(yv2[2 * h4][cc], a01);
+                            yv2[2 * h4 + 1][cc] = mul2(yv2[2 * h4 + 1][cc], a23);
+                        }
                     }
+                }
+                if (threadIdx.x == 0) rebase[par ^ 1] = 0;   // last read two barriers ago, next written after the next barrier
 #pragma unroll
-                    for (int si = 0; si < SC; ++si) {
-                        const float ph = pbuf[(h * SC + si) * 32 + lane];
+                for (int si = 0; si < SC; ++si) {
 #pragma unroll
-                        for (int cc = 0; cc < GC; ++cc) yv[h][cc] = fmaf(ph, xs[si][cc], yv[h][cc]);
+                    for (int h4 = 0; h4 < NG / 4; ++h4) {
+                        const float4 pv = *reinterpret_cast<const float4*>(pbuf + ((si * (NG / 4) + h4) * 32 + lane) * 4);
+                        const f32x2 p01 = pack2(pv.x, pv.y), p23 = pack2(pv.z, pv.w);
+#pragma unroll
+                        for (int cc = 0; cc < GC; ++cc) {
+                            yv2[2 * h4][cc] = fma2s(p01, xs[si][cc], yv2[2 * h4][cc]);
+                            yv2[2 * h4 + 1][cc] = fma2s(p23, xs[si][cc], yv2[2 * h4 + 1][cc]);
+                        }
                     }
                 }
             }
         }
+        float yv[NG][GC];
+#pragma unroll
+        for (int hp = 0; hp < HP; ++hp)
+#pragma unroll
+            for (int cc = 0; cc < GC; ++cc) unpack2(yv2[hp][cc], yv[2 * hp][cc], yv[2 * hp + 1][cc]);
 
         // ---- epilogue: out_h = Wv_h y_h / sum_h + bv_h; y_h is spread over the NG warps ----
         const float inv = 1.0f / sum;
@@ -370,6 +413,7 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && nG >= 1 && nS >= 1, "vfi_dattn_f32: bad shape");
     VFI_REQUIRE((score0 == nullptr) == (score1 == nullptr), "vfi_dattn_f32: score0/score1 must both be given or both NULL");
     if (nG != nH || C % nG != 0) VFI_UNSUPPORTED("vfi_dattn_f32: fused kernel needs nG == nH dividing C (got C=%d nG=%d nH=%d)", C, nG, nH);
+    if ((int64_t)H * W * 4 * (C / nG) >= (int64_t)1 << 31) VFI_UNSUPPORTED("vfi_dattn_f32: a group's planes exceed 2 GiB (H=%d W=%d)", H, W);
     if (B == 0) return VFI_OK;
     DattnArgs a;
     a.q = q;
@@ -386,7 +430,7 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
     a.B = B; a.H = H; a.W = W; a.nS = nS;
     a.offset_scale = offset_scale;
     a.coords_final = coords_final;
-    a.tw_log2 = 5; a.tiles_x = a.tiles_y = 0;
+    a.tw_log2 = 5; a.tiles_x = a.tiles_y = 0; a.zero = 0;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int gc = C / nG;
     int rc;

@@ -5,7 +5,7 @@
 namespace vfi {
 
 struct TapGeom {
-    int64_t o_nw;   // offset of the north-west tap inside a plane (may be out of range when !k_nw)
+    int o_nw;       // offset of the north-west tap inside a plane (may be out of range when !k_nw); H*W < 2^31
     float w_nw, w_ne, w_sw, w_se;
     bool k_nw, k_ne, k_sw, k_se;
     float gx, gy;
@@ -40,7 +40,7 @@ __device__ __forceinline__ TapGeom sampler_geom(float dx, float dy, float lin_x,
     g.w_ne = ey * tx;
     g.w_sw = ty * ex;
     g.w_se = ty * tx;
-    g.o_nw = (int64_t)y0 * W + x0;
+    g.o_nw = y0 * W + x0;
     return g;
 }
 
@@ -51,6 +51,21 @@ __device__ __forceinline__ float sample_plane(const float* __restrict__ plane, c
     if (g.k_ne) r += __ldg(p + 1) * g.w_ne;
     if (g.k_sw) r += __ldg(p + W) * g.w_sw;
     if (g.k_se) r += __ldg(p + W + 1) * g.w_se;
+    return r;
+}
+
+// Same taps, same arithmetic, for a loop over the planes of one group: the caller forms the byte pointers of the
+// north / south tap rows of plane 0 once per sample; plane cc is one 32x32->64-bit multiply-add away (IMAD.WIDE).
+__device__ __forceinline__ float sample_plane_rows(const char* __restrict__ north0, const char* __restrict__ south0,
+                                                   int cc, int plane_bytes_n, int plane_bytes_s, const TapGeom& g) {
+    const float *pn, *ps;
+    asm("mad.wide.s32 %0, %1, %2, %3;" : "=l"(pn) : "r"(plane_bytes_n), "r"(cc), "l"(north0));
+    asm("mad.wide.s32 %0, %1, %2, %3;" : "=l"(ps) : "r"(plane_bytes_s), "r"(cc), "l"(south0));
+    float r = 0.0f;
+    if (g.k_nw) r = __ldg(pn) * g.w_nw;
+    if (g.k_ne) r += __ldg(pn + 1) * g.w_ne;
+    if (g.k_sw) r += __ldg(ps) * g.w_sw;
+    if (g.k_se) r += __ldg(ps + 1) * g.w_se;
     return r;
 }
 

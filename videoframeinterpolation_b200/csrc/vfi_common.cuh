@@ -75,6 +75,34 @@ __device__ __forceinline__ void st_stream4(float* p, float4 v) {
 // gather loads through the read-only path (cached in L1: neighbouring lanes share lines)
 __device__ __forceinline__ float ld_gather(const float* p) { return __ldg(p); }
 
+// ---- packed fp32 pairs (sm_100a FFMA2: two IEEE fp32 FMAs per issue slot; a scalar operand broadcasts) ----------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+// pair * scalar + pair (ptxas folds the broadcast into the FFMA2 operand, no extra MOV)
+__device__ __forceinline__ f32x2 fma2s(f32x2 a, float b, f32x2 c) { return fma2(a, pack2(b, b), c); }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2s(f32x2 a, float b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(pack2(b, b)));
+    return d;
+}
+
 // Replay of the reference's normalise -> grid_sample unnormalise round trip, fp32, no FMA contraction
 // (reference: modules/warp.py:9-13 + ATen grid_sampler unnormalize, align_corners=True).
 //   g = lin + d / half_extent ;  i = ((g + 1) / 2) * (size - 1)
