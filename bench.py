@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs under ncu only)")
     ap.add_argument("--channels-last", type=int, default=1, help="run the cuDNN conv stacks around the hot path in NHWC (0 = NCHW)")
     ap.add_argument("--graph", type=int, default=1, help="replay the forward from a CUDA graph (0 = eager launches from Python)")
+    ap.add_argument("--torch-cuda-baseline", action="store_true",
+                    help="also time the reference's op composition on PyTorch-CUDA library ops (ATen grid_sample, torchvision "
+                         "deform_conv2d, cuDNN) at the full frame size on this GPU -> line['torch_cuda_baseline']")
     ap.add_argument("--tf32", type=int, default=1, help="allow TF32 in the cuDNN convs around the hot path (PyTorch default)")
     return ap.parse_args()
 
@@ -170,6 +173,46 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_sample_text(cores)},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def torch_cuda_baseline(args, dev, H, W):
+    """North-star comparison point: the reference's own op composition (oracle port of DATwConstantnCv1.inference, which
+    materialises the sampled kv tensors exactly as modules/deformable_attn.py does) executed by the PyTorch-CUDA library
+    ops the reference calls -- ATen grid_sample, torchvision deform_conv2d, cuDNN convs -- on the same GPU, same frame
+    size, same TF32 setting.  Opt-in (needs ~60 GB of HBM at 1080p)."""
+    import oracle
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.workloads import init_dat_weights, seed_for
+    torch.manual_seed(0)
+    net = init_dat_weights(v.DATwConstantnCv1(v.default_args()))
+    sd = {k: w.detach().clone().to(dev) for k, w in net.state_dict().items()}
+    del net
+    g = torch.Generator().manual_seed(seed_for(4, 0))
+    ph, pw = -(-H // 16) * 16, -(-W // 16) * 16
+    x0, x1 = (torch.rand(1, 3, ph, pw, generator=g).to(dev) for _ in range(2))
+    t = torch.full((1, 1, 1, 1), 0.5, device=dev)
+    try:
+        with torch.no_grad(), oracle.library_ops():
+            oracle.dat_forward(sd, x0, x1, t)
+            torch.cuda.synchronize()
+            ts = []
+            for _ in range(3):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                oracle.dat_forward(sd, x0, x1, t)
+                b.record()
+                torch.cuda.synchronize()
+                ts.append(a.elapsed_time(b))
+        ms = sorted(ts)[1]
+        peak_gb = torch.cuda.max_memory_allocated() / 1e9
+    except torch.OutOfMemoryError as e:
+        torch.cuda.empty_cache()
+        return {"unavailable": f"out of memory at {pw}x{ph}: {str(e)[:120]}"}
+    torch.cuda.empty_cache()
+    return {"value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "frame": f"{pw}x{ph}", "pairs": 1,
+            "ops": "ATen grid_sampler_2d, torchvision deform_conv2d, cuDNN convs (tf32=%d), eager PyTorch" % args.tf32,
+            "max_memory_allocated_gb": round(peak_gb, 1),
+            "sample": "oracle port of DATwConstantnCv1.inference with library ops on cuda:0, median of 3 after 1 warm-up"}
 
 
 def workload_name(args):
@@ -386,6 +429,8 @@ def run_vfi(args):
         if not args.no_micro:
             with torch.no_grad():
                 line["microbench"] = microbench(dev, hbm_peak)
+        if args.torch_cuda_baseline:
+            line["torch_cuda_baseline"] = torch_cuda_baseline(args, dev, H, W)
         if not args.no_cpu and world == 1:
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)

@@ -46,7 +46,10 @@ __device__ __forceinline__ BwarpGeom bwarp_geom(float fx, float fy, float lin_x,
     return g;
 }
 
-constexpr int kCUnroll = 4;
+#ifndef VFI_BWARP_CUNROLL
+#define VFI_BWARP_CUNROLL 4
+#endif
+constexpr int kCUnroll = VFI_BWARP_CUNROLL;
 
 // planar / generic-stride kernel: thread = one pixel, loops over a chunk of channels
 __global__ void __launch_bounds__(256) bwarp_planar_kernel(const float* __restrict__ img, const float* __restrict__ flow,
@@ -58,21 +61,26 @@ __global__ void __launch_bounds__(256) bwarp_planar_kernel(const float* __restri
     const int y = blockIdx.y * 8 + threadIdx.y;
     const int b = blockIdx.z / n_chunks;
     const int c_begin = (blockIdx.z % n_chunks) * c_chunk;
-    if (x >= W || y >= H) return;
+    // no early exit: the 8 rows of the CTA walk the planes in lockstep (barrier per channel group) so that row y's
+    // south taps and row y+1's north taps -- the same sectors -- meet in the L1 (measured on the splat gather: 2x on
+    // rough flows); out-of-frame threads compute on the clamped pixel and skip the store
+    const bool live = x < W && y < H;
+    const int xc = min(x, W - 1), yc = min(y, H - 1);
     const int c_end = min(C, c_begin + c_chunk);
 
-    const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
+    const float* fp = flow + b * sf.n + yc * sf.h + xc * sf.w;
     const float fx = ld_stream(fp), fy = ld_stream(fp + sf.c);
     const float half_w = (float)((W - 1.0) / 2.0), half_h = (float)((H - 1.0) / 2.0);
-    const BwarpGeom g = bwarp_geom(fx, fy, lin_x[x], lin_y[y], H, W, half_w, half_h);
+    const BwarpGeom g = bwarp_geom(fx, fy, lin_x[xc], lin_y[yc], H, W, half_w, half_h);
 
     const int64_t o_nw = g.y0 * si.h + g.x0 * si.w, o_ne = g.y0 * si.h + g.x1 * si.w;
     const int64_t o_sw = g.y1 * si.h + g.x0 * si.w, o_se = g.y1 * si.h + g.x1 * si.w;
     const float* ip = img + b * si.n + c_begin * si.c;
-    float* op = out + b * so.n + c_begin * so.c + y * so.h + x * so.w;
+    float* op = out + b * so.n + c_begin * so.c + yc * so.h + xc * so.w;
 
     int c = c_begin;
     for (; c + kCUnroll <= c_end; c += kCUnroll) {
+        __syncthreads();
         float v[kCUnroll][4];
 #pragma unroll
         for (int u = 0; u < kCUnroll; ++u) {
@@ -85,7 +93,7 @@ __global__ void __launch_bounds__(256) bwarp_planar_kernel(const float* __restri
 #pragma unroll
         for (int u = 0; u < kCUnroll; ++u) {
             const float r = v[u][0] * g.w_nw + v[u][1] * g.w_ne + v[u][2] * g.w_sw + v[u][3] * g.w_se;
-            st_stream(op + u * so.c, r);
+            if (live) st_stream(op + u * so.c, r);
         }
         ip += kCUnroll * si.c;
         op += kCUnroll * so.c;
@@ -93,7 +101,7 @@ __global__ void __launch_bounds__(256) bwarp_planar_kernel(const float* __restri
     for (; c < c_end; ++c) {
         const float r = ld_gather(ip + o_nw) * g.w_nw + ld_gather(ip + o_ne) * g.w_ne + ld_gather(ip + o_sw) * g.w_sw +
                         ld_gather(ip + o_se) * g.w_se;
-        st_stream(op, r);
+        if (live) st_stream(op, r);
         ip += si.c;
         op += so.c;
     }

@@ -16,6 +16,8 @@
 // Lists have no capacity limit (the node pool is exactly 4 per source pixel); overflow beyond the 4 kept in
 // registers is re-walked per channel.  Summation order is arbitrary, as it is in the reference.
 // Workspace per source pixel: 32 B slots + 4 B head + 32 B nodes.
+#include <stdlib.h>
+
 #include "vfi_common.cuh"
 
 namespace vfi {
@@ -73,17 +75,20 @@ __global__ void __launch_bounds__(256) splat_link_kernel(const float* __restrict
         const bool in_x0 = c.x0 >= 0, in_x1 = c.x0 + 1 < W, in_y0 = c.y0 >= 0, in_y1 = c.y0 + 1 < H;
         const int64_t q = (int64_t)b * HW + (int64_t)c.y0 * W + c.x0;     // output pixel of the north-west corner
         const int node0 = (int)(idx * 4);
-        auto push = [&](int64_t qq, int k, float w) {
-            if (atomicCAS(slot_src + qq * 4 + k, -1, (int)pix) == -1) {
-                slot_w[qq * 4 + k] = w;
-            } else {
-                nodes[node0 + k] = SplatNode{atomicExch(head + qq, node0 + k), w};
-            }
-        };
-        if (in_x0 && in_y0) push(q, 0, wm * c.w_nw);
-        if (in_x1 && in_y0) push(q + 1, 1, wm * c.w_ne);
-        if (in_x0 && in_y1) push(q + W, 2, wm * c.w_sw);
-        if (in_x1 && in_y1) push(q + W + 1, 3, wm * c.w_se);
+        // the four claims are independent: issue all four atomics before looking at any result (the kernel is bound
+        // by the atomic round trip, 4 in flight per thread instead of 1)
+        const bool on[4] = {in_x0 && in_y0, in_x1 && in_y0, in_x0 && in_y1, in_x1 && in_y1};
+        const int64_t qq[4] = {q, q + 1, q + W, q + W + 1};
+        const float wk[4] = {wm * c.w_nw, wm * c.w_ne, wm * c.w_sw, wm * c.w_se};
+        int prev[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) prev[k] = on[k] ? atomicCAS(slot_src + qq[k] * 4 + k, -1, (int)pix) : 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (!on[k]) continue;
+            if (prev[k] == -1) slot_w[qq[k] * 4 + k] = wk[k];
+            else nodes[node0 + k] = SplatNode{atomicExch(head + qq[k], node0 + k), wk[k]};
+        }
     }
 }
 
@@ -101,15 +106,16 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
                                                            const float* __restrict__ slot_w, const int* __restrict__ head,
                                                            const SplatNode* __restrict__ nodes, float* __restrict__ out, int C,
                                                            int H, int W, int c_chunk, int n_chunks, int normalize, int eps_mode,
-                                                           float eps) {
+                                                           float eps, int lockstep) {
     const int x = blockIdx.x * 32 + threadIdx.x;
     const int y = blockIdx.y * 8 + threadIdx.y;
     const int b = blockIdx.z / n_chunks;
     const int c_begin = (blockIdx.z % n_chunks) * c_chunk;
-    if (x >= W || y >= H) return;
+    const bool live = x < W && y < H;
+    if (!live && !lockstep) return;
     const int c_end = min(C, c_begin + c_chunk);
     const int64_t HW = (int64_t)H * W;
-    const int64_t q = (int64_t)b * HW + (int64_t)y * W + x;
+    const int64_t q = (int64_t)b * HW + (int64_t)min(y, H - 1) * W + min(x, W - 1);
     const int64_t base4 = (int64_t)b * HW * 4;   // node ids of this image start here
 
     constexpr int NT = 4 + kOvTaps;
@@ -150,64 +156,79 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
         den += __int_as_float(e.y);
         nd = e.x;
     }
-    const float div = normalize ? splat_divisor_f(den, eps_mode, eps) : 1.0f;
+    // one reciprocal per pixel instead of an IEEE division per (pixel, channel): <= 1.5 ulp from the reference's
+    // divide, far inside the 1e-4 splat tolerance (the summation order already differs from the atomics')
+    const float rdiv = normalize ? __frcp_rn(splat_divisor_f(den, eps_mode, eps)) : 1.0f;
 
-    const float* ip = in + ((int64_t)b * C + c_begin) * HW;
-    float* op = out + ((int64_t)b * C + c_begin) * HW + (int64_t)y * W + x;
-    int c = c_begin;
-    for (; c + kChUnroll <= c_end; c += kChUnroll) {
-        float v[kChUnroll][4];
+    // byte offsets of the source pixels inside a plane (32-bit: H*W*4 < 2^32); plane bases are block-uniform, so a
+    // tap is one IMAD.WIDE.U32 + one predicated LDG + one predicated FFMA
+    unsigned so[NT];   // source pixel index (0 when the tap is absent; its loads are predicated off)
+    bool on[NT];
 #pragma unroll
-        for (int u = 0; u < kChUnroll; ++u)
-#pragma unroll
-            for (int k = 0; k < 4; ++k) v[u][k] = src[k] >= 0 ? ld_gather(ip + (int64_t)u * HW + src[k]) : 0.0f;
+    for (int k = 0; k < NT; ++k) {
+        on[k] = src[k] >= 0;
+        so[k] = on[k] ? (unsigned)src[k] : 0u;
+    }
+    const int64_t plane_bytes = HW * 4;
+    const char* ibase = reinterpret_cast<const char*>(in) + ((int64_t)b * C + c_begin) * plane_bytes;
+    char* obase = reinterpret_cast<char*>(out) + ((int64_t)b * C + c_begin) * plane_bytes;
+    const unsigned oo = live ? (unsigned)(y * W + x) * 4u : 0u;
+    auto tap = [](const char* plane, unsigned pixel) {
+        const float* p;   // one IMAD.WIDE.U32 (left to itself the compiler re-loads the base and does a 3-term 64-bit add)
+        asm("mad.wide.u32 %0, %1, 4, %2;" : "=l"(p) : "r"(pixel), "l"(plane));
+        return ld_gather(p);
+    };
+    const int n_c = c_end - c_begin;
+    int c = 0;
+    for (; c + kChUnroll <= n_c; c += kChUnroll) {
+        // the 8 rows of the CTA walk the planes in lockstep: row y's south taps and row y+1's north taps are the same
+        // sectors, and they only meet in the L1 if the warps are on the same plane at the same time
+        if (lockstep) __syncthreads();
         float acc[kChUnroll];
 #pragma unroll
         for (int u = 0; u < kChUnroll; ++u) {
+            const char* pl = ibase + (int64_t)(c + u) * plane_bytes;
             acc[u] = 0.0f;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) acc[u] = fmaf(v[u][k], wgt[k], acc[u]);
+            for (int k = 0; k < 4; ++k)
+                if (on[k]) acc[u] = fmaf(tap(pl, so[k]), wgt[k], acc[u]);
         }
-        if (ov_any) {
+        if (ov_any) {                               // warp-uniform
 #pragma unroll
             for (int k = 0; k < kOvTaps; ++k) {
-                if (ov_any & (1u << k)) {          // warp-uniform
-                    if (src[4 + k] >= 0) {
+                if (ov_any & (1u << k)) {           // warp-uniform
 #pragma unroll
-                        for (int u = 0; u < kChUnroll; ++u)
-                            acc[u] = fmaf(ld_gather(ip + (int64_t)u * HW + src[4 + k]), wgt[4 + k], acc[u]);
-                    }
+                    for (int u = 0; u < kChUnroll; ++u)
+                        if (on[4 + k]) acc[u] = fmaf(tap(ibase + (int64_t)(c + u) * plane_bytes, so[4 + k]), wgt[4 + k], acc[u]);
                 }
             }
             if (rest_any) {
                 for (int nd = rest; nd >= 0;) {
                     const int2 e = __ldg(reinterpret_cast<const int2*>(nodes) + nd);
-                    const int sp = (int)(((int64_t)nd - base4) >> 2);
+                    const unsigned sp = (unsigned)(((int64_t)nd - base4) >> 2);
 #pragma unroll
                     for (int u = 0; u < kChUnroll; ++u)
-                        acc[u] = fmaf(ld_gather(ip + (int64_t)u * HW + sp), __int_as_float(e.y), acc[u]);
+                        acc[u] = fmaf(tap(ibase + (int64_t)(c + u) * plane_bytes, sp), __int_as_float(e.y), acc[u]);
                     nd = e.x;
                 }
             }
         }
 #pragma unroll
-        for (int u = 0; u < kChUnroll; ++u) st_stream(op + (int64_t)u * HW, normalize ? __fdiv_rn(acc[u], div) : acc[u]);
-        ip += kChUnroll * HW;
-        op += kChUnroll * HW;
+        for (int u = 0; u < kChUnroll; ++u)
+            if (live) st_stream(reinterpret_cast<float*>(obase + (int64_t)(c + u) * plane_bytes + oo), acc[u] * rdiv);
     }
-    for (; c < c_end; ++c) {
+    for (; c < n_c; ++c) {
+        const char* pl = ibase + (int64_t)c * plane_bytes;
         float acc = 0.0f;
 #pragma unroll
         for (int k = 0; k < NT; ++k)
-            if (src[k] >= 0) acc = fmaf(ld_gather(ip + src[k]), wgt[k], acc);
+            if (on[k]) acc = fmaf(tap(pl, so[k]), wgt[k], acc);
         for (int nd = rest; nd >= 0;) {
             const int2 e = __ldg(reinterpret_cast<const int2*>(nodes) + nd);
-            acc = fmaf(ld_gather(ip + (int)(((int64_t)nd - base4) >> 2)), __int_as_float(e.y), acc);
+            acc = fmaf(tap(pl, (unsigned)(((int64_t)nd - base4) >> 2)), __int_as_float(e.y), acc);
             nd = e.x;
         }
-        st_stream(op, normalize ? __fdiv_rn(acc, div) : acc);
-        ip += HW;
-        op += HW;
+        if (live) st_stream(reinterpret_cast<float*>(obase + (int64_t)c * plane_bytes + oo), acc * rdiv);
     }
 }
 
@@ -256,8 +277,10 @@ extern "C" int vfi_splat_fused_f32(const float* in, const float* flow, const flo
     n_chunks = (int)ceil_div(C, c_chunk);
     VFI_REQUIRE((int64_t)B * n_chunks <= 65535 && ceil_div(H, 8) <= 65535, "vfi_splat_fused_f32: grid too large");
     dim3 grid((unsigned)ceil_div(W, 32), (unsigned)ceil_div(H, 8), (unsigned)(B * n_chunks));
+    int lockstep = 1;
+    if (const char* e = getenv("VFI_SPLAT_LOCKSTEP")) lockstep = atoi(e);
     splat_gather_kernel<<<grid, dim3(32, 8), 0, st>>>(in, slot_src, slot_w, head, nodes, out, C, H, W, c_chunk, n_chunks,
-                                                      weight_mode == VFI_SPLAT_W_NONE ? 0 : 1, eps_mode, eps_value);
+                                                      weight_mode == VFI_SPLAT_W_NONE ? 0 : 1, eps_mode, eps_value, lockstep);
     VFI_CHECK_LAUNCH("splat_gather_kernel");
     return VFI_OK;
 }
