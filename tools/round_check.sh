@@ -9,4 +9,4 @@ timeout -s KILL 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_
 timeout -s KILL 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err; echo "ref rc=$?"
 timeout -s KILL 900 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench rc=$?"
 cat gpurun_out/${TAG}_bench_ref.json; cut -c1-1500 gpurun_out/${TAG}_bench.json
-timeout -s KILL 900 bash profiles/run_ncu.sh ${TAG} dattn_kernel 2 1
+timeout -s KILL 900 bash profiles/run_ncu.sh ${TAG} dattn_ 2 1
