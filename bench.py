@@ -253,11 +253,11 @@ def microbench(dev, hbm_peak):
             img = torch.rand(1, C, H, W, generator=g).to(dev)
             metric = torch.randn(1, 1, H, W, generator=g).to(dev)
             row = {"level": li, "C": C, "H": H, "W": W}
-            for kind in ("smooth", "iid"):
-                if kind == "iid" and not (li == 0 and C in (3, 64)):
+            for kind in ("smooth", "iid", "gentle"):
+                if kind != "smooth" and not (li == 0 and C in (3, 64)):
                     continue
                 flow = make_flow(1, H, W, 8.0 / (1 << li), g, kind=kind, device=dev)
-                sfx = "" if kind == "smooth" else "_iid"
+                sfx = "" if kind == "smooth" else "_" + kind
                 ms = time_op(lambda: v.bwarp(img, flow), 10, flush)
                 row["bwarp_gbs" + sfx] = bytes_bwarp(1, C, H, W) / ms / 1e6
                 ms = time_op(lambda: v.softsplat(img, flow, metric, "soft"), 10, flush)
@@ -266,7 +266,38 @@ def microbench(dev, hbm_peak):
     big = [r for r in res["cases"] if r["level"] == 0 and r["C"] == 64][0]
     res["bwarp_1080p_C64_frac_of_hbm"] = big["bwarp_gbs"] / hbm_peak
     res["softsplat_1080p_C64_frac_of_hbm"] = big["softsplat_gbs"] / hbm_peak
+    res["bwarp_1080p_C64_gentle_frac_of_hbm"] = big["bwarp_gbs_gentle"] / hbm_peak
+    res["softsplat_1080p_C64_gentle_frac_of_hbm"] = big["softsplat_gbs_gentle"] / hbm_peak
+    res["flow_kinds"] = ("smooth: 32 px correlation length (strain ~0.35 px/px) + 2% outliers; gentle: 256 px correlation "
+                         "length; iid: independent per pixel (SURVEY.md 8d literal)")
+    res["dcn_cfg3"] = dcn_cfg3(dev, hbm_peak, flush)
     return res
+
+
+def dcn_cfg3(dev, hbm_peak, flush):
+    """BASELINE configs[2]: DCNv2 dim 64 at 256x256 patches, batch 32, OG = WG = 8; torchvision's CUDA op beside it."""
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.workloads import bytes_dcn, make_flow, seed_for
+    B, C, H, W, OG, WG = 32, 64, 256, 256, 8, 8
+    g = torch.Generator().manual_seed(seed_for(3, 0))
+    x = torch.randn(B, C, H, W, generator=g).to(dev)
+    flow = make_flow(B, H, W, 2.0, g, device="cpu")
+    off = (2 * torch.tanh(torch.randn(B, OG * 18, H, W, generator=g)) + flow.flip(1).repeat(1, OG * 9, 1, 1)).to(dev)
+    mask = torch.sigmoid(torch.randn(B, OG * 9, H, W, generator=g)).to(dev)
+    wgt = (torch.randn(C, C // WG, 3, 3, generator=g) * 0.1).to(dev)
+    bias = torch.randn(C, generator=g).to(dev)
+    ms = time_op(lambda: v.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask), 5, flush)
+    nbytes = bytes_dcn(B, C, C, H, W, OG)
+    out = {"shape": "x (32,64,256,256), offset (32,144,256,256), mask (32,72,256,256), weight (64,8,3,3)", "ms": ms,
+           "gbs": nbytes / ms / 1e6, "frac_of_hbm": nbytes / ms / 1e6 / hbm_peak, "algorithmic_bytes": nbytes}
+    try:
+        import torchvision.ops as tvo
+        ms_tv = time_op(lambda: tvo.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask), 3, flush)
+        out["torchvision_cuda_ms"] = ms_tv
+    except Exception as e:      # library baseline only; never on the product path
+        out["torchvision_cuda_ms"] = None
+        out["torchvision_note"] = str(e)[:100]
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -429,8 +460,11 @@ def run_vfi(args):
         if not args.no_micro:
             with torch.no_grad():
                 line["microbench"] = microbench(dev, hbm_peak)
-        if args.torch_cuda_baseline:
-            line["torch_cuda_baseline"] = torch_cuda_baseline(args, dev, H, W)
+        if (args.torch_cuda_baseline or not args.no_cpu) and world == 1:
+            tb = torch_cuda_baseline(args, dev, H, W)
+            if "value" in tb:
+                tb["speedup_of_this_repo"] = (1e3 * args.pairs / line["ms_per_step"]) / tb["value"]   # per GPU, frames/s over frames/s
+            line["torch_cuda_baseline"] = tb
         if not args.no_cpu and world == 1:
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)

@@ -1,4 +1,6 @@
 """GPU parity for DCNv2, the grouped sampler, attention (unfused and fused), and the DAT forward."""
+import os
+
 import pytest
 import torch
 
@@ -170,6 +172,14 @@ def test_fused_dattn_vs_oracle(vfi, cfg):
                                          n_groups=nG, n_samples=nS, n_heads=nG, offset_scale=cfg["scale"])
     assert out_qcl.is_contiguous(memory_format=torch.channels_last) and not out_qcl.is_contiguous()
     assert torch.equal(out_qcl, out), "channels-last q / out must not change the arithmetic"
+    # the channel-split kernel variant (VFI_DATTN_ALGO=split: lane = pixel x channel half) computes the same thing
+    os.environ["VFI_DATTN_ALGO"] = "split"
+    try:
+        out_split = fused_deformable_attention(*cu(q, f0, f1, raw0, raw1, ft0, ft1), *w, n_groups=nG, n_samples=nS, n_heads=nG,
+                                               offset_scale=cfg["scale"])
+    finally:
+        del os.environ["VFI_DATTN_ALGO"]
+    assert_close(out_split, ref, TOL, f"fused dattn, channel-split kernel {cfg}")
 
 
 def test_madat_golden(vfi, golden):

@@ -1,0 +1,19 @@
+"""Which ATen ops are left in one eager 1080p forward (torch profiler, grouped by input shape)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch
+import videoframeinterpolation_b200 as v
+from videoframeinterpolation_b200.workloads import init_dat_weights
+from torch.profiler import profile, ProfilerActivity
+dev = torch.device("cuda")
+torch.manual_seed(0)
+net = init_dat_weights(v.DATwConstantnCv1(v.default_args())).to(dev).eval().to(memory_format=torch.channels_last)
+x0, x1 = (torch.rand(1, 3, 1088, 1920, device=dev).contiguous(memory_format=torch.channels_last) for _ in range(2))
+t = torch.full((1, 1, 1, 1), 0.5, device=dev)
+for _ in range(3):
+    net.inference(x0, x1, t)
+torch.cuda.synchronize()
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True, with_stack=False) as prof:
+    net.inference(x0, x1, t)
+    torch.cuda.synchronize()
+print(prof.key_averages(group_by_input_shape=True).table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=40, max_shapes_column_width=70))

@@ -10,6 +10,7 @@ from .deformable_attn import Attn, CrossDeformableAttentionBlockwFlow
 from .madat import DeformAttnwMotion, DATwithMotionEstimation
 from .dat import DATwConstantnCv1, DCNInterFeatBuilderwithT, InputPadder, default_args
 from .graph import GraphedInference
+from .checkpoint import load_reference_checkpoint, save_reference_checkpoint, strip_ddp_prefix
 
 FunctionSoftsplat = softsplat   # name used by BASELINE.json's north_star for the same four-argument call
 

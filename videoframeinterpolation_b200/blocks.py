@@ -169,6 +169,30 @@ class FeadForward(nn.Module):
     def forward(self, x):
         return self.fc2(self.act(self.fc1(x)))
 
+    def forward_residual(self, x):
+        """``x + fc2(gelu(fc1(x)))`` (the tail of modules/deformable_attn.py:130).  On channels-last CUDA tensors at
+        inference the two 1x1 convolutions are plain GEMMs over the (pixels, C) view with the bias in the GEMM epilogue
+        (cuBLASLt): cuDNN runs them as a conv plus a generic strided bias pass that costs more than the GEMM itself
+        (measured at 544x960: 298 + 175 us -> 4 kernels, profiles/r1x_aten_ops.txt).  Same math mode as the cuDNN
+        convs around it (TF32 iff cudnn.allow_tf32)."""
+        cl = (x.dim() == 4 and x.is_cuda and x.dtype == torch.float32 and not torch.is_grad_enabled()
+              and x.permute(0, 2, 3, 1).is_contiguous() and self.fc1.bias is not None and self.fc2.bias is not None)
+        if not cl:
+            return x + self.forward(x)
+        B, C, H, W = x.shape
+        x2 = x.permute(0, 2, 3, 1).reshape(B * H * W, C)
+        w1 = self.fc1.weight.reshape(self.fc1.out_channels, C)
+        w2 = self.fc2.weight.reshape(self.fc2.out_channels, self.fc1.out_channels)
+        prev = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = bool(torch.backends.cudnn.allow_tf32)
+        try:
+            h = F.gelu(torch.addmm(self.fc1.bias, x2, w1.t()))
+            y = torch.addmm(self.fc2.bias, h, w2.t())
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = prev
+        y += x2
+        return y.view(B, H, W, -1).permute(0, 3, 1, 2)
+
 
 class SameChannelResEncoder(nn.Module):
     """4-level feature pyramid at 1/2, 1/4, 1/8, 1/16 resolution, nf channels each."""

@@ -222,7 +222,7 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
             c1 = (self.offset_scale * torch.tanh(raw1)).view(shp) + ft1.unsqueeze(1)
             kv = torch.cat((self._get_ref_feats(feat0, c0), self._get_ref_feats(feat1, c1)), dim=2)
             attended = self.attn(feat_t, kv)
-        out = attended + self.mlp(attended)
+        out = self.mlp.forward_residual(attended)
         if not self.pred_res_flow:
             return out
         up_ft0 = _conv.conv_transpose_up2(self.conv_res_flow, mv0, out_channels_last=False) + 2.0 * resize(ft0, scale_factor=2.0)
