@@ -52,6 +52,10 @@ def parse_args():
     ap.add_argument("--torch-cuda-baseline", action="store_true",
                     help="also time the reference's op composition on PyTorch-CUDA library ops (ATen grid_sample, torchvision "
                          "deform_conv2d, cuDNN) at the full frame size on this GPU -> line['torch_cuda_baseline']")
+    ap.add_argument("--tile-grid", default="", help="ROWSxCOLS: BASELINE configs[4] mode -- ONE frame pair split into a grid of "
+                    "tiles with a halo, tiles dealt round-robin to the ranks (strong scaling, no collective); e.g. "
+                    "--height 2160 --width 3840 --tile-grid 2x4 --halo 64")
+    ap.add_argument("--halo", type=int, default=64)
     ap.add_argument("--tf32", type=int, default=1, help="allow TF32 in the cuDNN convs around the hot path (PyTorch default)")
     return ap.parse_args()
 
@@ -483,6 +487,83 @@ def run_vfi(args):
         dist.destroy_process_group()
 
 
+def run_tiled(args):
+    """BASELINE configs[4] / SURVEY.md 8(e): one 3840x2160 pair, spatial tiles with a halo over the ranks.  Every rank
+    holds the whole input pair, computes the global rgb mean itself (identical on all ranks: no all-reduce), runs the
+    forward on its tiles + halo and writes their interiors; the stitched frame is the union of the ranks' interiors
+    (gathering it is not on the timed path).  value = pairs/s of the WHOLE pair = 1 / max-over-ranks step time."""
+    import torch.distributed as dist
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200 import _lib
+    from videoframeinterpolation_b200.shard import tile_plan, tiles_of_rank
+    from videoframeinterpolation_b200.workloads import init_dat_weights, seed_for
+    rank, world, local = dist_env(args.gpus)
+    assert torch.cuda.is_available(), "bench.py needs a GPU"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cudnn.allow_tf32 = bool(args.tf32)
+    torch.backends.cudnn.benchmark = True
+    rows, cols = (int(x) for x in args.tile_grid.lower().split("x"))
+    torch.manual_seed(0)
+    net = init_dat_weights(v.DATwConstantnCv1(v.default_args())).to(dev).eval().to(memory_format=torch.channels_last)
+    H, W = args.height, args.width
+    g = torch.Generator().manual_seed(seed_for(5, 0))           # the same pair on every rank
+    h_x0, h_x1 = torch.rand(1, 3, H, W, generator=g).pin_memory(), torch.rand(1, 3, H, W, generator=g).pin_memory()
+    padder = v.InputPadder((H, W), divisor=16)
+    d_x0, d_x1 = padder.pad(h_x0.to(dev), h_x1.to(dev))
+    t = torch.full((1, 1, 1, 1), 0.5, device=dev)
+    ph, pw = d_x0.shape[-2:]
+    mine = tiles_of_rank(tile_plan(ph, pw, (rows, cols), args.halo), rank, world)
+    out_buf = torch.zeros((1, 3, ph, pw), device=dev)
+
+    def fn(a, b, tt):
+        return net.inference_tiled(a, b, tt, grid=(rows, cols), halo=args.halo, rank=rank, world=world, out=out_buf)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.no_grad():
+        graphed = v.GraphedInference(net, d_x0, d_x1, t, fn=fn)
+        _lib.reset_launch_count()
+        fn(d_x0, d_x1, t)
+        launches = _lib.launch_count()
+        for _ in range(max(args.warmup, 3)):
+            graphed.replay()
+        clock = ClockSampler(local)
+        clock.start()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            graphed.replay()
+        e1.record()
+        barrier()
+        clocks = clock.stop()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms_per_step = float(ms.item()) / args.steps
+    if rank == 0:
+        crop_px = sum((tl.crop[0].stop - tl.crop[0].start) * (tl.crop[1].stop - tl.crop[1].start) for tl in tile_plan(ph, pw, (rows, cols), args.halo))
+        line = {"metric": METRIC.replace("1080p", f"{W}x{H} tiled"), "value": 1e3 / ms_per_step, "unit": UNIT, "n_gpus": world,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"DAT inference on ONE synthetic {W}x{H} frame pair (padded to {pw}x{ph}), {rows}x{cols} tiles with a "
+                                       f"{args.halo}-px halo dealt round-robin to {world} rank(s) (BASELINE configs[4])",
+                           "tiles_per_rank": len(mine), "redundant_pixels": crop_px / float(ph * pw) - 1.0,
+                           "parallelism": f"spatial tiles x{world}, no collective", "launch": "CUDA graph replay",
+                           "l2": "inputs + activations per step exceed the 126 MB L2"},
+                "gpu_launches": int(launches) * args.steps, "clocks": clocks}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def _quiet_native_stdout():
     """Send file descriptor 1 to stderr for the rest of the run (NCCL prints its version banner to stdout) and return
     a text stream on the original stdout for the one JSON line."""
@@ -497,6 +578,8 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.tile_grid:
+        run_tiled(args)
     else:
         run_vfi(args)
 

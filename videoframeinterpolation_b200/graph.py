@@ -16,20 +16,23 @@ class GraphedInference:
     input buffers (they may be pinned host tensors: the copy is the H2D transfer), replays the graph and returns the
     static output tensor (valid until the next call)."""
 
-    def __init__(self, net, x0: torch.Tensor, x1: torch.Tensor, t: torch.Tensor, warmup: int = 3):
+    def __init__(self, net, x0: torch.Tensor, x1: torch.Tensor, t: torch.Tensor, warmup: int = 3, fn=None):
+        """``fn(x0, x1, t)``: what to capture instead of ``net.inference`` (e.g. this rank's tiles of
+        ``net.inference_tiled``); it must be capture-safe like the forward itself."""
         assert x0.is_cuda and x1.is_cuda and t.is_cuda, "GraphedInference needs CUDA example inputs"
         self.net = net
+        fn = fn if fn is not None else net.inference
         self.x0, self.x1, self.t = x0.clone(memory_format=torch.preserve_format), x1.clone(memory_format=torch.preserve_format), t.clone()
         side = torch.cuda.Stream(device=x0.device)
         side.wait_stream(torch.cuda.current_stream(x0.device))
         with torch.cuda.stream(side), torch.no_grad():
             for _ in range(max(warmup, 1)):          # cuDNN autotuning, lazy caches, allocator warm-up: outside the capture
-                net.inference(self.x0, self.x1, self.t)
+                fn(self.x0, self.x1, self.t)
         torch.cuda.current_stream(x0.device).wait_stream(side)
         torch.cuda.synchronize(x0.device)
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph), torch.no_grad():
-            self.out = net.inference(self.x0, self.x1, self.t)
+            self.out = fn(self.x0, self.x1, self.t)
 
     def replay(self) -> torch.Tensor:
         self.graph.replay()
