@@ -197,6 +197,27 @@ int vfi_splat_bwd_f32(const float* in, const float* flow, const float* grad_out,
 int vfi_bwarp_bwd_f32(const float* img, const float* flow, const float* grad_out, const float* lin_x, const float* lin_y,
                       float* grad_img, float* grad_flow, int B, int C, int H, int W, void* stream);
 
+/* ---- f1: backward of the grouped sampler (vfi_dsample_f32) -- the gradients torch autograd derives for
+ * modules/deformable_attn.py:88-101 (F.grid_sample bilinear / zeros / align_corners=True composed with the
+ * reference's coordinate arithmetic, x displacement scaled by 1/(2(W-1)) as at line 94).
+ * grad_out (B,C,nS,H*W); grad_feat (B,C,H,W) (zero-filled here, scattered with atomics) and/or grad_coords
+ * (B,nG*nS,2,H,W); either may be NULL. */
+int vfi_dsample_bwd_f32(const float* feat, const float* coords, const float* grad_out, const float* lin_x,
+                        const float* lin_y, float* grad_feat, float* grad_coords, int B, int C, int H, int W,
+                        int nG, int nS, void* stream);
+
+/* ---- f1: backward of the modulated deformable convolution -- torchvision deform_conv2d autograd semantics
+ * (modules/dcnv2.py:60-66, models/archive/DCNDAT.py:71-77).  Two data-dependent steps; the dense contractions between
+ * them (grad_weight = grad_out . columns^T and grad_columns = W^T . grad_out per weight group) are library GEMMs in the
+ * Python wrapper (training path only).
+ *   columns / grad_columns (B, Cin, kh*kw, Ho*Wo);  grad_x (B,Cin,H,W) zero-filled here, scattered with atomics;
+ *   grad_offset (B, OG*2*kh*kw, Ho, Wo);  grad_mask (B, OG*kh*kw, Ho, Wo);  any gradient pointer may be NULL. */
+int vfi_dcn_im2col_f32(const float* x, const float* offset, const float* mask, float* columns, int B, int Cin, int H,
+                       int W, int kh, int kw, int stride, int pad, int dil, int n_offset_grps, void* stream);
+int vfi_dcn_col2im_f32(const float* x, const float* offset, const float* mask, const float* grad_columns,
+                       float* grad_x, float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int kh,
+                       int kw, int stride, int pad, int dil, int n_offset_grps, void* stream);
+
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vfi_launch_count(void);

@@ -43,6 +43,9 @@ SIGNATURES = {
     "vfi_conv3x3_f32": (c_int, [c_void_p] * 6 + [c_int] * 11 + [c_void_p]),
     "vfi_splat_bwd_f32": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "vfi_bwarp_bwd_f32": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
+    "vfi_dsample_bwd_f32": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_void_p]),
+    "vfi_dcn_im2col_f32": (c_int, [c_void_p] * 4 + [c_int] * 10 + [c_void_p]),
+    "vfi_dcn_col2im_f32": (c_int, [c_void_p] * 7 + [c_int] * 10 + [c_void_p]),
     "vfi_launch_count": (c_int64, []),
     "vfi_launch_count_reset": (None, []),
 }

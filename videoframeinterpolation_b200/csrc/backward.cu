@@ -105,7 +105,87 @@ __global__ void __launch_bounds__(256) bwarp_bwd_kernel(const float* __restrict_
     }
 }
 
+// ---- grouped sampler backward (row f1): what autograd derives for modules/deformable_attn.py:88-101 --------------
+// out[b, g*gc+c, s, p] = bilinear_zeros(feat[b, g*gc+c], ix, iy),  ix = ((lin_x + (dx/(W-1))/2 + 1)/2)*(W-1),
+// iy = ((lin_y + dy/((H-1)/2) + 1)/2)*(H-1).  One thread per (pixel, group, sample) as in the forward kernel; the
+// feature gradient is scattered with atomics (grad_feat zero-filled by the entry point), the coordinate gradient is
+// d out/d ix = sum_c g_c ((v_ne - v_nw) ey + (v_se - v_sw) ty) with out-of-frame taps reading 0 (ATen
+// grid_sampler_2d_backward, padding_mode = zeros), chained through the reference's own scale factors.
+__global__ void __launch_bounds__(256) dsample_bwd_kernel(const float* __restrict__ feat, const float* __restrict__ coords,
+                                                          const float* __restrict__ gout, const float* __restrict__ lin_x,
+                                                          const float* __restrict__ lin_y, float* __restrict__ gfeat,
+                                                          float* __restrict__ gcoords, int C, int H, int W, int nG, int nS) {
+    const int64_t HW = (int64_t)H * W;
+    const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= HW) return;
+    const int gs = blockIdx.y, g = gs / nS, s = gs - g * nS, b = blockIdx.z;
+    const int y = (int)(pix / W), x = (int)(pix - (int64_t)y * W);
+    const int gc = C / nG;
+    const float* cp = coords + (((int64_t)b * nG * nS + gs) * 2) * HW + pix;
+    const float dx = __ldg(cp), dy = __ldg(cp + HW);
+    const float wm1 = (float)(W - 1), hm1 = (float)(H - 1), half_h = (float)((H - 1.0) / 2.0);
+    const float gxn = __fadd_rn(lin_x[x], __fmul_rn(__fdiv_rn(dx, wm1), 0.5f));
+    const float gyn = __fadd_rn(lin_y[y], __fdiv_rn(dy, half_h));
+    float ix = __fmul_rn(__fmul_rn(__fadd_rn(gxn, 1.0f), 0.5f), wm1);
+    float iy = __fmul_rn(__fmul_rn(__fadd_rn(gyn, 1.0f), 0.5f), hm1);
+    const bool finite = isfinite(ix) && isfinite(iy);
+    ix = fminf(fmaxf(finite ? ix : -2.0f, -2.0f), (float)W + 1.0f);
+    iy = fminf(fmaxf(finite ? iy : -2.0f, -2.0f), (float)H + 1.0f);
+    const float xf = floorf(ix), yf = floorf(iy);
+    const float tx = ix - xf, ty = iy - yf, ex = 1.0f - tx, ey = 1.0f - ty;
+    const int x0 = (int)xf, y0 = (int)yf;
+    const bool in_x0 = x0 >= 0 && x0 < W, in_x1 = x0 + 1 >= 0 && x0 + 1 < W;
+    const bool in_y0 = y0 >= 0 && y0 < H, in_y1 = y0 + 1 >= 0 && y0 + 1 < H;
+    const bool k_nw = in_x0 && in_y0, k_ne = in_x1 && in_y0, k_sw = in_x0 && in_y1, k_se = in_x1 && in_y1;
+    const int64_t o_nw = (int64_t)y0 * W + x0;
+    const float* fp = feat + ((int64_t)b * C + (int64_t)g * gc) * HW;
+    float* gf = gfeat ? gfeat + ((int64_t)b * C + (int64_t)g * gc) * HW : nullptr;
+    const float* gp = gout + (((int64_t)b * C + (int64_t)g * gc) * nS + s) * HW + pix;
+    float gx = 0.0f, gy = 0.0f;
+    for (int c = 0; c < gc; ++c) {
+        const float go = __ldg(gp);
+        if (gf) {
+            if (k_nw) atomicAdd(gf + o_nw, go * ey * ex);
+            if (k_ne) atomicAdd(gf + o_nw + 1, go * ey * tx);
+            if (k_sw) atomicAdd(gf + o_nw + W, go * ty * ex);
+            if (k_se) atomicAdd(gf + o_nw + W + 1, go * ty * tx);
+            gf += HW;
+        }
+        if (gcoords) {
+            const float v_nw = k_nw ? __ldg(fp + o_nw) : 0.0f, v_ne = k_ne ? __ldg(fp + o_nw + 1) : 0.0f;
+            const float v_sw = k_sw ? __ldg(fp + o_nw + W) : 0.0f, v_se = k_se ? __ldg(fp + o_nw + W + 1) : 0.0f;
+            gx += go * ((v_ne - v_nw) * ey + (v_se - v_sw) * ty);
+            gy += go * ((v_sw - v_nw) * ex + (v_se - v_ne) * tx);
+        }
+        fp += HW;
+        gp += (int64_t)nS * HW;
+    }
+    if (gcoords) {
+        float* gcp = gcoords + (((int64_t)b * nG * nS + gs) * 2) * HW + pix;
+        // unnormalise: d ix / d gx = (W-1)/2; then the reference's own (dx / (W-1)) / 2 and dy / ((H-1)/2)
+        gcp[0] = finite ? __fmul_rn(__fdiv_rn(gx * (wm1 * 0.5f), wm1), 0.5f) : 0.0f;
+        gcp[HW] = finite ? __fdiv_rn(gy * (hm1 * 0.5f), half_h) : 0.0f;
+    }
+}
+
 }  // namespace vfi
+
+extern "C" int vfi_dsample_bwd_f32(const float* feat, const float* coords, const float* grad_out, const float* lin_x,
+                                   const float* lin_y, float* grad_feat, float* grad_coords, int B, int C, int H, int W,
+                                   int nG, int nS, void* stream) {
+    using namespace vfi;
+    VFI_REQUIRE(feat && coords && grad_out && lin_x && lin_y, "vfi_dsample_bwd_f32: null pointer");
+    VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && nG >= 1 && nS >= 1 && C % nG == 0, "vfi_dsample_bwd_f32: bad shape");
+    VFI_REQUIRE((int64_t)nG * nS <= 65535 && B <= 65535, "vfi_dsample_bwd_f32: nG*nS or B exceeds grid limits");
+    if (B == 0 || (!grad_feat && !grad_coords)) return VFI_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (grad_feat) VFI_CUDA(cudaMemsetAsync(grad_feat, 0, sizeof(float) * (size_t)B * C * H * W, st));
+    const int64_t HW = (int64_t)H * W;
+    dim3 grid((unsigned)ceil_div(HW, 256), (unsigned)(nG * nS), (unsigned)B);
+    dsample_bwd_kernel<<<grid, 256, 0, st>>>(feat, coords, grad_out, lin_x, lin_y, grad_feat, grad_coords, C, H, W, nG, nS);
+    VFI_CHECK_LAUNCH("dsample_bwd_kernel");
+    return VFI_OK;
+}
 
 extern "C" int vfi_splat_bwd_f32(const float* in, const float* flow, const float* grad_out, float* grad_in, float* grad_flow,
                                  int B, int C, int H, int W, void* stream) {

@@ -30,9 +30,58 @@ def _pair(v: Union[int, Tuple[int, int]]) -> int:
     return int(v)
 
 
+class _DeformConvFn(torch.autograd.Function):
+    """deform_conv2d with torchvision's backward (row f1): vfi_dcn_im2col_f32 / vfi_dcn_col2im_f32 around the two
+    per-group GEMMs (cuBLAS through torch.einsum: a training-only path)."""
+
+    @staticmethod
+    def forward(ctx, x, offset, weight, bias, mask, s, p, d, algo):
+        x, offset, weight = _lib.f32c(x), _lib.f32c(offset), _lib.f32c(weight)
+        bias, mask = _lib.f32c(bias), _lib.f32c(mask)
+        ctx.save_for_backward(x, offset, weight, mask)
+        ctx.conf = (s, p, d, bias is not None)
+        with torch.no_grad():
+            return deform_conv2d(x, offset, weight, bias, s, p, d, mask, algo)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        x, offset, weight, mask = ctx.saved_tensors
+        s, p, d, has_bias = ctx.conf
+        dev = x.device
+        B, Cin, H, W = x.shape
+        Cout, cin_g, kh, kw = weight.shape
+        K, WG, OG = kh * kw, Cin // cin_g, offset.shape[1] // (2 * kh * kw)
+        g = _lib.f32c(grad_out)
+        Ho, Wo = g.shape[-2:]
+        Po = Ho * Wo
+        need_x, need_off, need_w, need_b, need_m = (ctx.needs_input_grad[i] for i in (0, 1, 2, 3, 4))
+        st = _lib.stream_ptr(dev)
+        g_w = None
+        gg = g.view(B, WG, Cout // WG, Po)
+        if need_w:
+            cols = torch.empty((B, Cin, K, Po), dtype=torch.float32, device=dev)
+            _lib.call("vfi_dcn_im2col_f32", dev, x.data_ptr(), offset.data_ptr(), _lib.ptr(mask), cols.data_ptr(), B, Cin, H, W,
+                      kh, kw, s, p, d, OG, st)
+            g_w = torch.einsum("bgop,bgkp->gok", gg, cols.view(B, WG, cin_g * K, Po)).reshape(Cout, cin_g, kh, kw)
+            del cols
+        g_x = g_off = g_m = None
+        if need_x or need_off or (need_m and mask is not None):
+            gcol = torch.einsum("gok,bgop->bgkp", weight.view(WG, Cout // WG, cin_g * K), gg).contiguous()
+            g_x = torch.empty_like(x) if need_x else None
+            g_off = torch.empty_like(offset) if need_off else None
+            g_m = torch.empty_like(mask) if (need_m and mask is not None) else None
+            _lib.call("vfi_dcn_col2im_f32", dev, x.data_ptr(), offset.data_ptr(), _lib.ptr(mask), gcol.data_ptr(), _lib.ptr(g_x),
+                      _lib.ptr(g_off), _lib.ptr(g_m), B, Cin, H, W, kh, kw, s, p, d, OG, st)
+        g_b = g.sum(dim=(0, 2, 3)) if (need_b and has_bias) else None
+        return g_x, g_off, g_w, g_b, g_m, None, None, None, None
+
+
 def deform_conv2d(input: torch.Tensor, offset: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None,
                   stride=1, padding=0, dilation=1, mask: Optional[torch.Tensor] = None, algo: str = "auto") -> torch.Tensor:
-    """Modulated deformable convolution with torchvision's exact semantics (groups inferred the same way)."""
+    """Modulated deformable convolution with torchvision's exact semantics (groups inferred the same way).
+    Differentiable wrt input, offset, weight, bias and mask."""
+    if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in (input, offset, weight, bias, mask)):
+        return _DeformConvFn.apply(input, offset, weight, bias, mask, _pair(stride), _pair(padding), _pair(dilation), algo)
     dev = _lib.require_cuda(input, offset, weight, bias, mask)
     x, offset, weight = _lib.f32c(input), _lib.f32c(offset), _lib.f32c(weight)
     bias, mask = _lib.f32c(bias), _lib.f32c(mask)

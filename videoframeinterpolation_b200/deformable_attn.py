@@ -25,8 +25,37 @@ from .warp import bwarp, _bwarp_forward
 __all__ = ["Attn", "CrossDeformableAttentionBlockwFlow", "grouped_sample", "attention_over_samples", "fused_deformable_attention"]
 
 
+class _GroupedSampleFn(torch.autograd.Function):
+    """grouped_sample with its backward (vfi_dsample_bwd_f32): the gradients autograd gives the reference's
+    ``_get_ref_feats`` (F.grid_sample + the coordinate arithmetic of modules/deformable_attn.py:88-101)."""
+
+    @staticmethod
+    def forward(ctx, feat, flow, n_groups, n_samples):
+        feat_c, flow_c = _lib.f32c(feat), _lib.f32c(flow)
+        ctx.save_for_backward(feat_c, flow_c)
+        ctx.ng, ctx.ns = n_groups, n_samples
+        with torch.no_grad():
+            return grouped_sample(feat_c, flow_c, n_groups, n_samples)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        feat, flow = ctx.saved_tensors
+        dev = feat.device
+        b, c, fh, fw = feat.shape
+        g = _lib.f32c(grad_out)
+        g_feat = torch.empty_like(feat) if ctx.needs_input_grad[0] else None
+        g_flow = torch.empty_like(flow) if ctx.needs_input_grad[1] else None
+        _lib.call("vfi_dsample_bwd_f32", dev, feat.data_ptr(), flow.data_ptr(), g.data_ptr(), _lib.linspace_m11(fw, dev).data_ptr(),
+                  _lib.linspace_m11(fh, dev).data_ptr(), _lib.ptr(g_feat), _lib.ptr(g_flow), b, c, fh, fw, ctx.ng, ctx.ns,
+                  _lib.stream_ptr(dev))
+        return g_feat, g_flow, None, None
+
+
 def grouped_sample(feat: torch.Tensor, flow: torch.Tensor, n_groups: int, n_samples: int, want_grid: bool = False):
-    """feat (b,c,h,w), flow (b, nG*nS, 2, h, w) absolute displacement -> samples (b, c, nS, h*w) [, grid (b,nG*nS,h*w,2)]."""
+    """feat (b,c,h,w), flow (b, nG*nS, 2, h, w) absolute displacement -> samples (b, c, nS, h*w) [, grid (b,nG*nS,h*w,2)].
+    Differentiable wrt feat and flow (the grid output is not: the reference only logs it)."""
+    if torch.is_grad_enabled() and (feat.requires_grad or flow.requires_grad) and not want_grid:
+        return _GroupedSampleFn.apply(feat, flow, n_groups, n_samples)
     dev = _lib.require_cuda(feat, flow)
     feat, flow = _lib.f32c(feat), _lib.f32c(flow)
     b, c, fh, fw = feat.shape
@@ -132,7 +161,20 @@ class Attn(nn.Module):
 
     def forward(self, q, kv):
         """q: b, c, fh, fw;  kv: b, c, nS, fh*fw  ->  b, out_c, fh, fw"""
+        if torch.is_grad_enabled() and (q.requires_grad or kv.requires_grad or self.q_proj.weight.requires_grad):
+            return self._forward_autograd(q, kv)
         return attention_over_samples(q, kv, *self._weights(), n_heads=self.n_head)
+
+    def _forward_autograd(self, q, kv):
+        """Training route: the projections and the two contractions as library ops (what modules/deformable_attn.py:26-40
+        runs), so that autograd reaches the sampler's and the warp's backward kernels."""
+        b, c, fh, fw = q.shape
+        S = kv.shape[2]
+        qp = self.q_proj(q).reshape(b * self.n_head, self.n_head_c, fh * fw)
+        k = self.k_proj(kv).reshape(b * self.n_head, self.n_head_c, S, fh * fw)
+        v = self.v_proj(kv).reshape(b * self.n_head, self.n_head_c, S, fh * fw)
+        w = F.softmax(torch.einsum("bcd,bcsd->bsd", qp, k) * self.scale, dim=1)
+        return torch.einsum("bsd,bcsd->bcd", w, v).reshape(b, self.out_c, fh, fw)
 
 
 class CrossDeformableAttentionBlockwFlow(nn.Module):
@@ -197,7 +239,23 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
                 and bool(_lib.lib().vfi_conv3x3_supported(C, 2 * C, me[1][0].out_channels, 1)))
 
     # -- fused forward ------------------------------------------------------------------------------
+    def _forward_autograd(self, feat_t, feat0, feat1, ft0, ft1):
+        """Training route (grad enabled): the reference's piecewise composition (modules/deformable_attn.py:103-133) over
+        the differentiable drop-ins -- bwarp and grouped_sample run the CUDA kernels forward and backward."""
+        mv0 = self._get_movement_feats(feat_t, feat0, ft0)
+        mv1 = self._get_movement_feats(feat_t, feat1, ft1)
+        kv = torch.cat((self._get_ref_feats(feat0, self._get_ref_coords(feat_t, ft0, mv0)),
+                        self._get_ref_feats(feat1, self._get_ref_coords(feat_t, ft1, mv1))), dim=2)
+        attended = self.attn(feat_t, kv)
+        out = attended + self.mlp(attended)
+        if not self.pred_res_flow:
+            return out
+        return (out, self.conv_res_flow(mv0) + 2.0 * resize(ft0, scale_factor=2.0),
+                self.conv_res_flow(mv1) + 2.0 * resize(ft1, scale_factor=2.0))
+
     def forward(self, feat_t, feat0, feat1, ft0, ft1):
+        if torch.is_grad_enabled():
+            return self._forward_autograd(feat_t, feat0, feat1, ft0, ft1)
         if self._split_ok(feat_t, feat0):
             mv0, mv1 = self._movement_feats_pair(feat_t, feat0, feat1, ft0, ft1)
         else:
