@@ -218,6 +218,19 @@ int vfi_dcn_col2im_f32(const float* x, const float* offset, const float* mask, c
                        float* grad_x, float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int kh,
                        int kw, int stride, int pad, int dil, int n_offset_grps, void* stream);
 
+/* ---- f3: frame I/O edge of the forward -- evaluate.py:138-142,187-191 (uint8 -> float / 255, pad, unpad),
+ * data/__init__.py:6-20 (InputPadder, replicate), models/BaseModel.py:14-17 (norm_w_rgb_mean over both padded frames),
+ * modules/generator.py:24 (clamp(out + mean, 0, 1)).
+ * vfi_frame_prep: x0, x1 (B,3,H,W) contiguous, fp32 in [0,1] or uint8 (is_u8) -> out0, out1 (B,Hp,Wp,4) channels-last
+ *   fp32 = replicate-padded frame minus mean[b], 4th channel 0; mean (B).  workspace: vfi_frame_prep_workspace_bytes.
+ * vfi_frame_finish: y (B,3,Hp,Wp) with element strides y_strides -> out (B,3,H,W) contiguous =
+ *   clamp(y + mean[b], 0, 1) cropped at (pad_top, pad_left); out_is_u8: round(255 * .) as uint8. */
+size_t vfi_frame_prep_workspace_bytes(int B);
+int vfi_frame_prep(const void* x0, const void* x1, int is_u8, float* out0, float* out1, float* mean, int B, int H, int W,
+                   int Hp, int Wp, int pad_top, int pad_left, void* workspace, size_t workspace_bytes, void* stream);
+int vfi_frame_finish(const float* y, const int64_t y_strides[4], const float* mean, void* out, int out_is_u8, int B, int H,
+                     int W, int Hp, int Wp, int pad_top, int pad_left, void* stream);
+
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vfi_launch_count(void);

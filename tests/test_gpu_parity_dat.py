@@ -258,3 +258,33 @@ def test_dat_tiled_inference_matches_whole_frame(vfi):
     parts = [net.inference_tiled(x0, x1, t, grid=(2, 2), halo=64, rank=r, world=2) for r in range(2)]
     d = float((parts[0] + parts[1] - tiled).abs().max())
     assert d <= 1e-6, f"rank-sharded tiles differ from the single-process tiled run by {d}"
+
+
+@pytest.mark.parametrize("hw", [(70, 100), (64, 96)])
+def test_frame_edge_interpolate_matches_pad_inference_unpad(vfi, hw):
+    """Row f3: uint8 -> float, InputPadder, norm_w_rgb_mean, clamp(out + mean) and unpad as the two fused passes of
+    ``interpolate`` against the reference's composition (evaluate.py:187-191) through the oracle."""
+    H, W = hw
+    kw = dict(nf=16, enc_res_blocks=1, dec_res_blocks=1)
+    net = vfi.DATwConstantnCv1(vfi.default_args(**kw))
+    sd = det.fill_state_dict(net.state_dict())
+    net.load_state_dict(sd)
+    net = net.cuda().eval()
+    u0 = (det.uniform(f"fe.u0.{hw}", (2, 3, H, W)) * 255).round().to(torch.uint8)
+    u1 = (det.uniform(f"fe.u1.{hw}", (2, 3, H, W)) * 255).round().to(torch.uint8)
+    f0, f1 = u0.float() / 255.0, u1.float() / 255.0
+    t = torch.full((2, 1, 1, 1), 0.5)
+    p0, pad = oracle.input_pad(f0)
+    p1, _ = oracle.input_pad(f1)
+    ref = oracle.input_unpad(oracle.dat_forward({k: w.cpu() for k, w in sd.items()}, p0, p1, t, oracle.dat_config(**kw)), pad)
+    out_f = net.interpolate(f0.cuda(), f1.cuda(), t.cuda())
+    assert out_f.shape == (2, 3, H, W) and out_f.dtype == torch.float32
+    assert_close(out_f, ref, 5e-5, "interpolate, float frames")
+    # the drop-in's own pad -> inference -> unpad composition gives the same frame
+    padder = vfi.InputPadder((H, W))
+    a, b = padder.pad(f0.cuda(), f1.cuda())
+    assert_close(out_f, padder.unpad(net.inference(a, b, t.cuda())), 2e-5, "interpolate vs pad/inference/unpad")
+    out_u = net.interpolate(u0.cuda(), u1.cuda(), t.cuda())
+    assert out_u.dtype == torch.uint8
+    q = (ref * 255.0).round()
+    assert int((out_u.cpu().float() - q).abs().max()) <= 1, "uint8 frames: at most one code value from the rounded reference"

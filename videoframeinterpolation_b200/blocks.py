@@ -28,6 +28,12 @@ def conv_bias_act(conv: nn.Conv2d, x: torch.Tensor, prelu: nn.PReLU = None, resi
     if _conv.eligible(conv, x):      # tcgen05 implicit GEMM with the epilogue fused (TF32, as cuDNN's default)
         return _conv.conv3x3(conv, x, None if prelu is None else prelu.weight, residual, residual_after_act)
     cin = conv.in_channels
+    if cin == 3 and x.dim() == 4 and x.shape[1] == 4 and x.is_cuda and not torch.is_grad_enabled():
+        # RGB0 channels-last frames from vfi_frame_prep: already in the padded layout the kernel reads
+        if _conv.part_eligible(conv, x):
+            return _conv.conv3x3(conv, x, None if prelu is None else prelu.weight, residual, residual_after_act,
+                                 in_slice=(0, 3, 1))
+        x = x[:, :3]
     if cin < 8 and cin % 4 and x.dim() == 4 and x.is_cuda and not torch.is_grad_enabled():
         # RGB-like inputs (the encoder's first conv): zero-pad the channels to 4 in NHWC so that the same kernel runs
         pad = 4 - cin % 4
@@ -228,12 +234,15 @@ class BasicResPixelShuffleGenerator(nn.Module):
         self.conv_last = nn.Conv2d(nf, 3, 3, 1, 1)
 
     def forward(self, feat, m):
+        """``m`` = the rgb mean to add back before the clamp; ``m is None`` returns the un-shifted, un-clamped frame
+        (the fused frame edge, vfi_frame_finish, applies mean + clamp + crop in its own pass)."""
         r = self.reconstruction(feat)
         if _conv.eligible(self.upconv1, r, upscale=2):     # conv + PixelShuffle(2) + PReLU in one kernel
             t = _conv.conv3x3(self.upconv1, r, self.prelu1.weight, upscale=2)
         else:
             t = self.prelu1(self.pixel_shuffle(conv_bias_act(self.upconv1, r)))
-        return torch.clamp(conv_bias_act(self.conv_last, conv_bias_act(self.HRconv, t, self.prelu2)) + m, 0, 1)
+        y = conv_bias_act(self.conv_last, conv_bias_act(self.HRconv, t, self.prelu2))
+        return y if m is None else torch.clamp(y + m, 0, 1)
 
 
 def resize(x, scale_factor):

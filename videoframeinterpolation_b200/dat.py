@@ -71,9 +71,11 @@ class DATwConstantnCv1(nn.Module):
         mean_ = torch.cat((x0, x1), dim=2).mean(1, keepdim=True).mean(2, keepdim=True).mean(3, keepdim=True)
         return x0 - mean_, x1 - mean_, mean_
 
-    def _generate_frame(self, x0, x1, t, return_flows: bool = False, mean_=None):
+    def _generate_frame(self, x0, x1, t, return_flows: bool = False, mean_=None, normalized: bool = False):
         nf = self.nf
-        if mean_ is None:
+        if normalized:      # vfi_frame_prep already subtracted the mean; the caller adds it back (vfi_frame_finish)
+            pass
+        elif mean_ is None:
             x0, x1, mean_ = self.norm_w_rgb_mean(x0, x1)
         else:       # tile of a larger frame: the mean is the GLOBAL one (models/BaseModel.py:14-17)
             x0, x1 = x0 - mean_, x1 - mean_
@@ -85,7 +87,7 @@ class DATwConstantnCv1(nn.Module):
         a3, ft0_2, ft1_2 = self.dat_lv3(q3, f0[2], f1[2], ft0_3, ft1_3)
         a2, ft0_1, ft1_1 = self.dat_lv2(conv_transpose_up2(self.lv3_to_lv2, a3), f0[1], f1[1], ft0_2, ft1_2)
         a1 = self.dat_lv1(conv_transpose_up2(self.lv2_to_lv1, a2), f0[0], f1[0], ft0_1, ft1_1)
-        img = self.pixel_geneartor(a1, mean_)
+        img = self.pixel_geneartor(a1, None if normalized else mean_)
         if return_flows:
             return img, dict(ft0=[ft0_1, ft0_2, ft0_3, ft0_4], ft1=[ft1_1, ft1_2, ft1_3, ft1_4])
         return img
@@ -97,6 +99,36 @@ class DATwConstantnCv1(nn.Module):
 
     def forward(self, x0, x1, t):
         return self._generate_frame(x0, x1, t)
+
+    @torch.no_grad()
+    def interpolate(self, img0, img1, t, out_uint8=None, divisor: int = 16):
+        """Frames in, frame out: img0, img1 (B,3,H,W) of ANY size, float32 in [0,1] or uint8 as
+        ``imread`` delivers them (evaluate.py:138-139).  Runs uint8 -> float / 255, ``InputPadder`` replicate padding,
+        ``norm_w_rgb_mean``, the forward, ``clamp(out + mean, 0, 1)`` and the unpad with two fused passes around the
+        forward (vfi_frame_prep / vfi_frame_finish) instead of ~10 full-frame PyTorch kernels, and returns (B,3,H,W) in the
+        input's dtype (``out_uint8`` overrides; uint8 = round(255 * frame))."""
+        from . import _lib
+        dev = _lib.require_cuda(img0, img1)
+        assert img0.shape == img1.shape and img0.dim() == 4 and img0.shape[1] == 3, "frames must be (B,3,H,W)"
+        assert img0.dtype == img1.dtype and img0.dtype in (torch.float32, torch.uint8), "frames must be float32 or uint8"
+        is_u8 = img0.dtype == torch.uint8
+        out_u8 = is_u8 if out_uint8 is None else bool(out_uint8)
+        img0, img1 = img0.contiguous(), img1.contiguous()
+        B, _, H, W = img0.shape
+        pad = InputPadder((H, W), divisor)._pad            # [left, right, top, bottom]
+        Hp, Wp = H + pad[2] + pad[3], W + pad[0] + pad[1]
+        x0 = torch.empty((B, Hp, Wp, 4), dtype=torch.float32, device=dev)
+        x1 = torch.empty_like(x0)
+        mean = torch.empty((B,), dtype=torch.float32, device=dev)
+        ws = torch.empty((B,), dtype=torch.float64, device=dev)
+        st = _lib.stream_ptr(dev)
+        _lib.call("vfi_frame_prep", dev, img0.data_ptr(), img1.data_ptr(), 1 if is_u8 else 0, x0.data_ptr(), x1.data_ptr(),
+                  mean.data_ptr(), B, H, W, Hp, Wp, pad[2], pad[0], ws.data_ptr(), ws.numel() * 8, st)
+        y = self._generate_frame(x0.permute(0, 3, 1, 2), x1.permute(0, 3, 1, 2), t, normalized=True)
+        out = torch.empty((B, 3, H, W), dtype=torch.uint8 if out_u8 else torch.float32, device=dev)
+        _lib.call("vfi_frame_finish", dev, y.data_ptr(), _lib.strides4(y), mean.data_ptr(), out.data_ptr(), 1 if out_u8 else 0,
+                  B, H, W, Hp, Wp, pad[2], pad[0], st)
+        return out
 
     @torch.no_grad()
     def inference_tiled(self, x0, x1, t, grid=(2, 4), halo=64, rank: int = 0, world: int = 1, out=None):
