@@ -172,14 +172,16 @@ def test_fused_dattn_vs_oracle(vfi, cfg):
                                          n_groups=nG, n_samples=nS, n_heads=nG, offset_scale=cfg["scale"])
     assert out_qcl.is_contiguous(memory_format=torch.channels_last) and not out_qcl.is_contiguous()
     assert torch.equal(out_qcl, out), "channels-last q / out must not change the arithmetic"
-    # the channel-split kernel variant (VFI_DATTN_ALGO=split: lane = pixel x channel half) computes the same thing
-    os.environ["VFI_DATTN_ALGO"] = "split"
-    try:
-        out_split = fused_deformable_attention(*cu(q, f0, f1, raw0, raw1, ft0, ft1), *w, n_groups=nG, n_samples=nS, n_heads=nG,
+    # the opt-in kernel variants (VFI_DATTN_ALGO=split: lane = pixel x channel half; =pipe: one barrier per chunk)
+    # compute the same thing
+    for algo in ("split", "pipe"):
+        os.environ["VFI_DATTN_ALGO"] = algo
+        try:
+            out_v = fused_deformable_attention(*cu(q, f0, f1, raw0, raw1, ft0, ft1), *w, n_groups=nG, n_samples=nS, n_heads=nG,
                                                offset_scale=cfg["scale"])
-    finally:
-        del os.environ["VFI_DATTN_ALGO"]
-    assert_close(out_split, ref, TOL, f"fused dattn, channel-split kernel {cfg}")
+        finally:
+            del os.environ["VFI_DATTN_ALGO"]
+        assert_close(out_v, ref, TOL, f"fused dattn, {algo} kernel {cfg}")
 
 
 def test_madat_golden(vfi, golden):
