@@ -32,6 +32,9 @@
 
 namespace vfi {
 
+// set by vfi_conv3x3_prep_f32, consumed by the next conv launch of this host thread (see the PDL note at the launch)
+static thread_local bool g_prep_pending = false;
+
 constexpr int kCvTW = 8, kCvRows = 16;                  // tile: 8 columns x 16 input rows (M = 128, column-major)
 constexpr int kCvTH = kCvRows - 2;                      // output rows per tile
 constexpr int kCvM = kCvTW * kCvRows;
@@ -166,10 +169,6 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         if (RSTG) tma_prefetch_desc(&rmap);
     }
     __syncthreads();      // barriers initialised before any thread of this CTA touches them
-    for (int i = tid; i < NPAD; i += kCvThreads) {
-        bias_s[i] = (a.bias && i < a.cn) ? a.bias[(size_t)i * a.bias_stride] : 0.0f;
-        slope_s[i] = (a.slope && i < a.cn) ? a.slope[i] : 1.0f;
-    }
     if (warp == 1) {
         if (CTAS == 2) umma::tmem_alloc_2sm(tmem_slot, 2 * kCvAccStride);
         else umma::tmem_alloc(tmem_slot, 2 * kCvAccStride);
@@ -178,6 +177,14 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         mbar_arrive_expect_tx(wfull, wbytes);
         const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(a.wprep) + (size_t)rank * wbytes;
         for (int t = 0; t < 3; ++t) bulk_load_1d(b_s + t * per_dx, wsrc + (size_t)t * per_dx, per_dx, wfull);
+    }
+    // PDL: let the next conv of the stream start its own weight prologue on the SMs this grid frees first, and do not
+    // read or write an activation before the previous kernel has completed and flushed
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    for (int i = tid; i < NPAD; i += kCvThreads) {
+        bias_s[i] = (a.bias && i < a.cn) ? a.bias[(size_t)i * a.bias_stride] : 0.0f;
+        slope_s[i] = (a.slope && i < a.cn) ? a.slope[i] : 1.0f;
     }
     umma::fence_before();
     if (CTAS == 2) {
@@ -445,13 +452,25 @@ static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtenso
     cfg.blockDim = dim3(kCvThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = CTAS;
     at[0].val.clusterDim.y = 1;
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
+    // programmatic dependent launch: this grid may become resident while the previous kernel of the stream drains its
+    // last tiles; it loads its resident weights (constants) and then waits (griddepcontrol.wait) before touching any
+    // activation.  The previous kernel releases it early only if it is one of ours (griddepcontrol.launch_dependents).
+    static const bool pdl = [] { const char* e = getenv("VFI_CONV_PDL"); return !(e && e[0] == '0'); }();
+    // the launch right after a weight preparation reads what that (PDL-unaware) kernel wrote before the wait: plain order
+    const bool after_prep = g_prep_pending;
+    g_prep_pending = false;
+    if (pdl && !after_prep) {
+        at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[1].val.programmaticStreamSerializationAllowed = 1;
+        cfg.numAttrs = 2;
+    }
     const cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_tc_kernel<NPAD, CTAS, RSTG>, a, xmap, rmap);
     if (e != cudaSuccess) {
         set_error("conv3x3_tc_kernel: launch failed: %s", cudaGetErrorString(e));
@@ -491,6 +510,7 @@ extern "C" int vfi_conv3x3_prep_f32(const float* weight, float* wprep, int Cout,
     conv3x3_prep_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(weight, wprep, Cout, Cin, t.T, t.NPAD, up2 * t.n_nt,
                                                                              t.nchunkP, up2, t.ntot, t.ctas);
     VFI_CHECK_LAUNCH("conv3x3_prep_kernel");
+    vfi::g_prep_pending = true;
     return VFI_OK;
 }
 
