@@ -339,8 +339,11 @@ def run_vfi(args):
     if args.channels_last:
         d_x0, d_x1 = d_x0.contiguous(memory_format=torch.channels_last), d_x1.contiguous(memory_format=torch.channels_last)
 
+    d_r0, d_r1 = h_x0.to(dev), h_x1.to(dev)          # the raw (unpadded) float32 frames, resident in HBM
+
     def step_device():
-        return net.inference(d_x0, d_x1, t)
+        # frames in, frame out: pad + rgb-mean normalisation + forward + clamp + unpad (the fused frame edge, row f3)
+        return net.interpolate(d_r0, d_r1, t)
 
     def step_e2e():
         a, b = padder.pad(h_x0.to(dev, non_blocking=True), h_x1.to(dev, non_blocking=True))
@@ -348,8 +351,7 @@ def run_vfi(args):
 
     graphed = None
 
-    def step_graph():
-        return graphed.replay()
+    step_graph = None
 
     def step_graph_e2e():
         a, b = padder.pad(h_x0.to(dev, non_blocking=True), h_x1.to(dev, non_blocking=True))
@@ -415,7 +417,9 @@ def run_vfi(args):
         torch.cuda.synchronize()
         eager_ms = total_ms / args.steps
         if args.graph:
-            graphed = v.GraphedInference(net, d_x0, d_x1, t)
+            graphed = v.GraphedInference(net, d_x0, d_x1, t)                      # float32 e2e leg (pad / unpad in PyTorch)
+            graphed_dev = v.GraphedInference(net, d_r0, d_r1, t, fn=net.interpolate)
+            step_graph = graphed_dev.replay
             for _ in range(3):
                 step_graph()
             total_ms = timed(step_graph, args.steps)
@@ -472,6 +476,7 @@ def run_vfi(args):
             "config": {"workload": workload_name(args), "pairs_per_gpu": P, "global_pairs_per_step": P * world,
                        "parallelism": f"frame-pair sharding x{world}, no collective", "conv_layout": "channels_last" if args.channels_last else "nchw", "conv_math": "tf32" if args.tf32 else "fp32",
                        "launch": "CUDA graph replay" if args.graph else "eager", "eager_ms_per_step": eager_ms,
+                       "api": "DATwConstantnCv1.interpolate(float32 frames resident in HBM): replicate pad, rgb-mean normalisation, forward, clamp, unpad",
                        "eager_host_enqueue_ms_per_step": host_ms,
                        "l2": "inputs + activations per step (>1 GB) exceed the 126 MB L2"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * h_u0.numel(), "d2h_bytes_per_step": h_out_u8.numel(),

@@ -17,3 +17,8 @@ with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_sh
     net.inference(x0, x1, t)
     torch.cuda.synchronize()
 print(prof.key_averages(group_by_input_shape=True).table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=40, max_shapes_column_width=70))
+print("==== ATen ops that launch kernels, by shape ====")
+rows = [e for e in prof.key_averages(group_by_input_shape=True) if e.key.startswith("aten::") and e.device_time_total > 0
+        and not any(k in e.key for k in ("conv", "addmm", "gelu", "cudnn"))]
+for e in sorted(rows, key=lambda e: -e.device_time_total)[:60]:
+    print(f"{e.key:28s} n={e.count:3d} cuda_us={e.device_time_total:9.1f} shapes={str(e.input_shapes)[:110]}")
