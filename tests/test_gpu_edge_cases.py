@@ -1,0 +1,87 @@
+"""Edge cases of the hot-path ops through the C ABI: empty batches, one- and two-pixel frames, ragged sizes that are no
+multiple of any tile, flows that are non-finite or far outside the frame -- each against the oracle."""
+import pytest
+import torch
+
+import _det as det
+import oracle
+from _util import assert_close
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def vfi():
+    import videoframeinterpolation_b200 as v
+    return v
+
+
+def cu(*ts):
+    return [None if t is None else t.cuda() for t in ts]
+
+
+def test_empty_batch_returns_empty(vfi):
+    img, flow, metric = torch.zeros(0, 5, 9, 11), torch.zeros(0, 2, 9, 11), torch.zeros(0, 1, 9, 11)
+    assert vfi.bwarp(*cu(img, flow)).shape == (0, 5, 9, 11)
+    assert vfi.softsplat(*cu(img, flow, metric), "soft").shape == (0, 5, 9, 11)
+    assert vfi.softsplat(*cu(img, flow), None, "avg").shape == (0, 5, 9, 11)
+    from videoframeinterpolation_b200.deformable_attn import grouped_sample
+    assert grouped_sample(torch.zeros(0, 8, 6, 7).cuda(), torch.zeros(0, 4 * 3, 2, 6, 7).cuda(), 4, 3).shape == (0, 8, 3, 42)
+    out = vfi.deform_conv2d(torch.zeros(0, 8, 6, 7).cuda(), torch.zeros(0, 18, 6, 7).cuda(), torch.zeros(8, 8, 3, 3).cuda(), padding=1)
+    assert out.shape == (0, 8, 6, 7)
+
+
+@pytest.mark.parametrize("hw", [(1, 1), (1, 2), (2, 1), (2, 3), (3, 37), (41, 1)])
+def test_tiny_and_ragged_frames(vfi, hw):
+    H, W = hw
+    img = det.normal(f"edge.img.{hw}", (2, 6, H, W))
+    flow = det.normal(f"edge.flow.{hw}", (2, 2, H, W), std=1.5)
+    metric = det.normal(f"edge.m.{hw}", (2, 1, H, W))
+    if H > 1 and W > 1:          # the reference's grid normalisation divides by (size - 1): undefined for a 1-pixel axis
+        assert_close(vfi.bwarp(*cu(img, flow)), oracle.bwarp(img, flow), 1e-5, f"bwarp {hw}")
+    for mode in ("sum", "avg", "soft"):
+        m = metric if mode == "soft" else None
+        assert_close(vfi.softsplat(*cu(img, flow, m), mode), oracle.fwarp(img, flow, m, mode), 1e-4, f"splat {mode} {hw}")
+
+
+def test_nonfinite_and_far_flows(vfi):
+    B, C, H, W = 1, 8, 24, 40
+    img = det.normal("edge.nf.img", (B, C, H, W))
+    flow = det.normal("edge.nf.flow", (B, 2, H, W), std=2.0)
+    flow[0, 0, 3, 4] = float("nan")
+    flow[0, 1, 5, 6] = float("inf")
+    flow[0, 0, 7, 8] = -float("inf")
+    flow[0, :, 9, 10] = 1.0e9
+    flow[0, :, 11, 12] = -3.0e6
+    metric = det.normal("edge.nf.m", (B, 1, H, W))
+    # splat: non-finite targets are skipped (modules/softsplat.py:306-307), far ones land outside and vanish
+    for mode in ("sum", "soft", "linear"):
+        m = None if mode == "sum" else (metric.abs() + 0.1 if mode == "linear" else metric)
+        out = vfi.softsplat(*cu(img, flow, m), mode)
+        assert torch.isfinite(out).all(), mode
+        assert_close(out, oracle.fwarp(img, flow, m, mode), 1e-4, f"splat {mode}, non-finite flows")
+    # backward warp: finite-but-huge flows clamp to the border like F.grid_sample(padding_mode='border')
+    big = flow.clone()
+    big[~torch.isfinite(big)] = 0.0
+    assert_close(vfi.bwarp(*cu(img, big)), oracle.bwarp(img, big), 1e-5, "bwarp, far flows")
+
+
+def test_sampler_and_dcn_far_outside(vfi):
+    from videoframeinterpolation_b200.deformable_attn import grouped_sample
+    B, C, H, W, nG, nS = 1, 8, 10, 14, 4, 3
+    feat = det.normal("edge.ds.feat", (B, C, H, W))
+    flow = det.normal("edge.ds.flow", (B, nG * nS, 2, H, W), std=2.0)
+    flow[0, 0] = 1.0e7                     # every tap outside: zeros padding
+    flow[0, 1, 0] = -1.0e7
+    with oracle.library_ops():
+        ref = oracle.dsample(feat, flow, nG, nS)
+    out = grouped_sample(*cu(feat, flow), nG, nS)
+    assert_close(out, ref, 1e-5, "grouped sampler, far offsets")
+    assert float(out[0, :2, 0].abs().max()) == 0.0
+    x = det.normal("edge.dcn.x", (1, 8, 9, 11))
+    off = det.normal("edge.dcn.off", (1, 2 * 2 * 9, 9, 11), std=1.0)
+    off[0, :2] = 5.0e4
+    wgt = det.normal("edge.dcn.w", (8, 4, 3, 3), std=0.2)
+    with oracle.library_ops():
+        ref = oracle.deform_conv2d(x, off, wgt, None, padding=1)
+    assert_close(vfi.deform_conv2d(*cu(x, off, wgt), None, padding=1), ref, 1e-5, "DCN, far offsets, no mask, no bias")

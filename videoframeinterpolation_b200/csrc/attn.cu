@@ -103,6 +103,7 @@ extern "C" int vfi_attn_f32(const float* q, const float* kv, const float* Wq, co
                             const float* Wv, const float* bv, float* out, float* score0, float* score1, int B, int C, int H,
                             int W, int S, int nH, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(q && kv && Wq && bq && Wk && bk && Wv && bv && out, "vfi_attn_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && S >= 1 && nH >= 1, "vfi_attn_f32: bad shape");
     VFI_REQUIRE(C % nH == 0, "vfi_attn_f32: C=%d not divisible by nH=%d", C, nH);

@@ -174,6 +174,7 @@ extern "C" int vfi_dsample_bwd_f32(const float* feat, const float* coords, const
                                    const float* lin_y, float* grad_feat, float* grad_coords, int B, int C, int H, int W,
                                    int nG, int nS, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(feat && coords && grad_out && lin_x && lin_y, "vfi_dsample_bwd_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && nG >= 1 && nS >= 1 && C % nG == 0, "vfi_dsample_bwd_f32: bad shape");
     VFI_REQUIRE((int64_t)nG * nS <= 65535 && B <= 65535, "vfi_dsample_bwd_f32: nG*nS or B exceeds grid limits");
@@ -190,6 +191,7 @@ extern "C" int vfi_dsample_bwd_f32(const float* feat, const float* coords, const
 extern "C" int vfi_splat_bwd_f32(const float* in, const float* flow, const float* grad_out, float* grad_in, float* grad_flow,
                                  int B, int C, int H, int W, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(in && flow && grad_out, "vfi_splat_bwd_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1, "vfi_splat_bwd_f32: bad shape");
     if (B == 0 || (!grad_in && !grad_flow)) return VFI_OK;
@@ -203,6 +205,7 @@ extern "C" int vfi_splat_bwd_f32(const float* in, const float* flow, const float
 extern "C" int vfi_bwarp_bwd_f32(const float* img, const float* flow, const float* grad_out, const float* lin_x,
                                  const float* lin_y, float* grad_img, float* grad_flow, int B, int C, int H, int W, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(img && flow && grad_out && lin_x && lin_y, "vfi_bwarp_bwd_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1, "vfi_bwarp_bwd_f32: bad shape");
     if (B == 0 || (!grad_img && !grad_flow)) return VFI_OK;

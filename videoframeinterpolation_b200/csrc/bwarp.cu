@@ -355,6 +355,7 @@ extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* l
                              int B, int C, int H, int W, const int64_t img_strides[4], const int64_t flow_strides[4],
                              const int64_t out_strides[4], void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(img && flow && lin_x && lin_y && out, "vfi_bwarp_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 0 && H >= 1 && W >= 1, "vfi_bwarp_f32: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
     VFI_REQUIRE(img_strides && flow_strides && out_strides, "vfi_bwarp_f32: null strides");

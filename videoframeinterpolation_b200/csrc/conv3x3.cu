@@ -525,6 +525,7 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
                                float* out, int B, int H, int W, int Cin, int x_pix_stride, int Cout, int out_channels_last,
                                int out_c_total, int res_c_total, int residual_mode, int upscale, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(x && wprep && out, "vfi_conv3x3_f32: null pointer");
     VFI_REQUIRE(B >= 0 && H >= 1 && W >= 1, "vfi_conv3x3_f32: bad shape");
     VFI_REQUIRE(vfi_conv3x3_supported(Cin, x_pix_stride, Cout, upscale),

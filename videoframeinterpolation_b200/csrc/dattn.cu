@@ -1152,6 +1152,7 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
                              int nS, int nH, float offset_scale, int coords_final, const float* offs_bias, int offs_channels_last,
                              int q_channels_last, int out_channels_last, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(q && feat0 && feat1 && offs0 && offs1 && Wq && bq && Wk && bk && Wv && bv && lin_x && lin_y && out,
                 "vfi_dattn_f32: null pointer");
     VFI_REQUIRE(coords_final || (ft0 && ft1 && ft_strides), "vfi_dattn_f32: raw offsets need ft0/ft1 and their strides");

@@ -125,6 +125,7 @@ extern "C" int vfi_dcn_f32(const float* x, const float* offset, const float* mas
                            int n_weight_grps, int n_offset_grps, int algo, void* workspace, size_t workspace_bytes,
                            void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(x && offset && weight && out, "vfi_dcn_f32: null pointer");
     VFI_REQUIRE(B >= 0 && B <= 65535, "vfi_dcn_f32: bad batch %d", B);
     DcnParams p;

@@ -112,6 +112,7 @@ static int dcn_bwd_params(DcnParams& P, int B, int Cin, int H, int W, int kh, in
 extern "C" int vfi_dcn_im2col_f32(const float* x, const float* offset, const float* mask, float* columns, int B, int Cin, int H,
                                   int W, int kh, int kw, int stride, int pad, int dil, int n_offset_grps, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(x && offset && columns, "vfi_dcn_im2col_f32: null pointer");
     DcnParams P;
     if (int rc = dcn_bwd_params(P, B, Cin, H, W, kh, kw, stride, pad, dil, n_offset_grps, "vfi_dcn_im2col_f32")) return rc;
@@ -126,6 +127,7 @@ extern "C" int vfi_dcn_col2im_f32(const float* x, const float* offset, const flo
                                   float* grad_x, float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int kh,
                                   int kw, int stride, int pad, int dil, int n_offset_grps, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(x && offset && grad_columns, "vfi_dcn_col2im_f32: null pointer");
     VFI_REQUIRE(grad_mask == nullptr || mask != nullptr, "vfi_dcn_col2im_f32: grad_mask without a mask");
     DcnParams P;

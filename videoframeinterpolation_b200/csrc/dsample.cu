@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(256) dsample_kernel(const float* __restrict__ 
 extern "C" int vfi_dsample_f32(const float* feat, const float* coords, const float* lin_x, const float* lin_y, float* out,
                                float* grid_out, int B, int C, int H, int W, int nG, int nS, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(feat && coords && lin_x && lin_y && out, "vfi_dsample_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && nG >= 1 && nS >= 1, "vfi_dsample_f32: bad shape");
     VFI_REQUIRE(C % nG == 0, "vfi_dsample_f32: C=%d not divisible by nG=%d", C, nG);

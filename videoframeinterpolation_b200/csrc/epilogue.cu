@@ -99,6 +99,7 @@ __global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const float* __restri
 extern "C" int vfi_bias_act_f32(const float* y, const float* bias, const float* slope, const float* residual, float* out, int B,
                                 int C, int H, int W, int channels_last, int residual_mode, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(y && out, "vfi_bias_act_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1, "vfi_bias_act_f32: bad shape");
     VFI_REQUIRE(residual_mode >= 0 && residual_mode <= 2, "vfi_bias_act_f32: residual_mode %d", residual_mode);
@@ -124,6 +125,7 @@ extern "C" int vfi_bias_act_f32(const float* y, const float* bias, const float* 
 
 extern "C" int vfi_nhwc_to_nchw_f32(const float* x, float* out, int B, int C, int H, int W, int64_t x_pix_stride, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(x && out, "vfi_nhwc_to_nchw_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && x_pix_stride >= C, "vfi_nhwc_to_nchw_f32: bad shape");
     VFI_REQUIRE(B <= 65535, "vfi_nhwc_to_nchw_f32: batch %d too large", B);

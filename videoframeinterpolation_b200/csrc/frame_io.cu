@@ -105,6 +105,7 @@ extern "C" size_t vfi_frame_prep_workspace_bytes(int B) { return B > 0 ? (size_t
 extern "C" int vfi_frame_prep(const void* x0, const void* x1, int is_u8, float* out0, float* out1, float* mean, int B, int H, int W,
                               int Hp, int Wp, int pad_top, int pad_left, void* workspace, size_t workspace_bytes, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(x0 && x1 && out0 && out1 && mean, "vfi_frame_prep: null pointer");
     FramePad g;
     if (int rc = frame_geom(g, B, H, W, Hp, Wp, pad_top, pad_left, "vfi_frame_prep")) return rc;
@@ -134,6 +135,7 @@ extern "C" int vfi_frame_prep(const void* x0, const void* x1, int is_u8, float* 
 extern "C" int vfi_frame_finish(const float* y, const int64_t y_strides[4], const float* mean, void* out, int out_is_u8, int B, int H,
                                 int W, int Hp, int Wp, int pad_top, int pad_left, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(y && y_strides && mean && out, "vfi_frame_finish: null pointer");
     FramePad g;
     if (int rc = frame_geom(g, B, H, W, Hp, Wp, pad_top, pad_left, "vfi_frame_finish")) return rc;

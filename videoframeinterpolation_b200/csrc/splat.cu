@@ -110,6 +110,7 @@ extern "C" int vfi_splat_f32(const float* in, const float* flow, const float* me
     using namespace vfi;
     (void)workspace;
     (void)workspace_bytes;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(in && flow && num, "vfi_splat_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 0 && H >= 1 && W >= 1, "vfi_splat_f32: bad shape");
     VFI_REQUIRE(weight_mode >= VFI_SPLAT_W_NONE && weight_mode <= VFI_SPLAT_W_SOFT_CLIP_T, "vfi_splat_f32: bad weight_mode %d",
@@ -134,6 +135,7 @@ extern "C" int vfi_splat_f32(const float* in, const float* flow, const float* me
 extern "C" int vfi_splat_normalize_f32(const float* num, const float* den, float* out, uint8_t* blank_mask, int B, int C, int H,
                                        int W, int eps_mode, float eps_value, float blank_threshold, void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(num && den && out, "vfi_splat_normalize_f32: null pointer");
     VFI_REQUIRE(eps_mode >= VFI_EPS_ADD && eps_mode <= VFI_EPS_CLIP, "vfi_splat_normalize_f32: bad eps_mode %d", eps_mode);
     if (B == 0) return VFI_OK;

@@ -245,6 +245,7 @@ extern "C" int vfi_splat_fused_f32(const float* in, const float* flow, const flo
                                    int weight_mode, int eps_mode, float eps_value, void* workspace, size_t workspace_bytes,
                                    void* stream) {
     using namespace vfi;
+    if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(in && flow && out, "vfi_splat_fused_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 0 && H >= 1 && W >= 1, "vfi_splat_fused_f32: bad shape");
     VFI_REQUIRE(weight_mode >= VFI_SPLAT_W_NONE && weight_mode <= VFI_SPLAT_W_SOFT, "vfi_splat_fused_f32: bad weight_mode %d",
