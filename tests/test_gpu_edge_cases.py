@@ -85,3 +85,26 @@ def test_sampler_and_dcn_far_outside(vfi):
     with oracle.library_ops():
         ref = oracle.deform_conv2d(x, off, wgt, None, padding=1)
     assert_close(vfi.deform_conv2d(*cu(x, off, wgt), None, padding=1), ref, 1e-5, "DCN, far offsets, no mask, no bias")
+
+
+def test_more_than_2_31_elements_identity(vfi):
+    """Maximum sizes: tensors past 2^31 elements (the reference's splat kernel indexes with int32 and cannot do this).
+    Size-independent property: zero flow is the identity for the backward warp and for the summation splat."""
+    B, C, H, W = 1, 70, 4096, 7504
+    assert B * C * H * W > 2 ** 31
+    free, _ = torch.cuda.mem_get_info()
+    if free < 30 * 2 ** 30:
+        pytest.skip("needs ~20 GB of free HBM")
+    img = torch.empty((B, C, H, W), device="cuda")
+    row = torch.arange(W, device="cuda", dtype=torch.float32) * 1e-3
+    for c in range(C):                                   # cheap, position-dependent content without a 9 GB host tensor
+        img[0, c] = row.view(1, W) + float(c) + torch.arange(H, device="cuda", dtype=torch.float32).view(H, 1) * 1e-2
+    flow = torch.zeros((B, 2, H, W), device="cuda")
+    out = vfi.bwarp(img, flow)
+    # (the reference's fp32 normalise -> unnormalise round trip lands ~1e-4 px off the integer positions, SURVEY.md H1:
+    # identity up to that interpolation; a wrong 32-bit index would be off by whole planes)
+    for c in (0, C // 2, C - 1):
+        assert float((out[0, c] - img[0, c]).abs().max()) <= 1e-3, c
+    del out
+    out = vfi.softsplat(img, flow, None, "sum")
+    assert float((out[0, -1] - img[0, -1]).abs().max()) == 0.0 and float((out[0, 0] - img[0, 0]).abs().max()) == 0.0
