@@ -108,3 +108,64 @@ def test_more_than_2_31_elements_identity(vfi):
     del out
     out = vfi.softsplat(img, flow, None, "sum")
     assert float((out[0, -1] - img[0, -1]).abs().max()) == 0.0 and float((out[0, 0] - img[0, 0]).abs().max()) == 0.0
+
+
+def test_dcn_cfg3_full_size_reduces_to_grouped_conv(vfi):
+    """BASELINE configs[2] at full size, x (32,64,256,256), OG = WG = 8: with zero offsets and a unit mask the modulated
+    deformable convolution IS the grouped 3x3 convolution (size-independent property; the oracle is too slow here)."""
+    torch.backends.cudnn.allow_tf32 = False
+    B, C, H, W, G = 32, 64, 256, 256, 8
+    g = torch.Generator().manual_seed(20260302)
+    x = torch.randn(B, C, H, W, generator=g).cuda()
+    wgt = (torch.randn(C, C // G, 3, 3, generator=g) * 0.1).cuda()
+    bias = torch.randn(C, generator=g).cuda()
+    off = torch.zeros(B, G * 18, H, W, device="cuda")
+    mask = torch.ones(B, G * 9, H, W, device="cuda")
+    out = vfi.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask)
+    ref = torch.nn.functional.conv2d(x, wgt, bias, padding=1, groups=G)
+    assert_close(out, ref, 1e-5, "DCN cfg3, zero offsets == grouped conv")
+    # integer offsets shift the taps: offset (dy, dx) = (1, -2) for every tap equals the conv of the shifted input
+    off[:, 0::2] = 1.0
+    off[:, 1::2] = -2.0
+    shifted = torch.zeros_like(x)
+    shifted[:, :, :H - 1, 2:] = x[:, :, 1:, :W - 2]
+    out = vfi.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask)
+    ref = torch.nn.functional.conv2d(shifted, wgt, bias, padding=1, groups=G)
+    # (taps that the shift moves out of the frame read 0 in both; the frame border rows/columns differ by the padding rule)
+    assert_close(out[:, :, 2:H - 3, 3:W - 3], ref[:, :, 2:H - 3, 3:W - 3], 1e-5, "DCN cfg3, integer offsets == shifted conv")
+
+
+def test_fused_attention_half_res_1080p_uniform_softmax(vfi):
+    """The dominant launch at its BASELINE shape (C = 72, nG = nH = 8, nS = 32 at 544x960): with Wk = 0 every logit is
+    equal, the softmax is uniform and the block must return Wv * mean(samples) + bv; with integer sampling offsets the
+    samples are shifted copies of the feature maps, so the reference value is a 1x1 convolution of a box-filtered sum."""
+    from videoframeinterpolation_b200.deformable_attn import fused_deformable_attention
+    B, C, H, W, nG, nS = 1, 72, 544, 960, 8, 32
+    g = torch.Generator().manual_seed(20260403)
+    q = torch.randn(B, C, H, W, generator=g).cuda()
+    f0, f1 = torch.randn(B, C, H, W, generator=g).cuda(), torch.randn(B, C, H, W, generator=g).cuda()
+    wq, wv = (torch.randn(C, C, generator=g) * C ** -0.5).cuda(), (torch.randn(C, C, generator=g) * C ** -0.5).cuda()
+    bq, bk, bv = [(torch.randn(C, generator=g) * 0.1).cuda() for _ in range(3)]
+    wk = torch.zeros(C, C, device="cuda")
+    # final coordinates (coords_final): sample s of every group displaced by the integer s // 8 - 2 pixels in y;
+    # x displacements are avoided because of the reference's x scale quirk (dx is divided by 2(W-1), not (W-1)/2)
+    dy = torch.tensor([float(s // 8 - 2) for s in range(nS)], device="cuda")
+    coords = torch.zeros(B, nG * nS, 2, H, W, device="cuda")
+    coords[:, :, 1] = dy.repeat(nG).view(1, nG * nS, 1, 1)
+    out = fused_deformable_attention(q, f0, f1, coords.view(B, -1, H, W), coords.view(B, -1, H, W), None, None, wq, bq, wk, bk, wv, bv,
+                                     n_groups=nG, n_samples=nS, n_heads=nG, offset_scale=8.0, coords_final=True)
+    acc = torch.zeros_like(f0)
+    for s in range(nS):
+        d = s // 8 - 2
+        for f in (f0, f1):
+            sh = torch.zeros_like(f)
+            if d >= 0:
+                sh[:, :, :H - d] = f[:, :, d:]
+            else:
+                sh[:, :, -d:] = f[:, :, :H + d]
+            acc += sh
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref = torch.einsum("oc,bchw->bohw", wv, acc / (2 * nS)) + bv.view(1, C, 1, 1)
+    # the fp32 coordinate round trip lands ~1e-4 px off the integer rows: compare away from exactness, tightly enough to
+    # catch any wrong plane / sample / head
+    assert_close(out[:, :, 4:H - 4], ref[:, :, 4:H - 4], 2e-3, "fused attention at 544x960, uniform softmax")
