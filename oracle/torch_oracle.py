@@ -27,7 +27,7 @@ __all__ = [
     "library_ops", "grid_sample_bilinear", "bwarp", "splat_sum", "fwarp", "softsplat",
     "fwarp_using_two_frames", "fwarp_mframes", "deform_conv2d", "dcn_block", "dcn_given_offset",
     "ref_coords", "dsample", "attn", "dat_block", "madat_ref_feats", "madat_attn",
-    "layer_norm_c", "conv3x3_tf32", "tf32_truncate", "tf32_round", "dat_forward", "dat_config", "dat_param_shapes", "input_pad", "input_unpad", "count_params",
+    "layer_norm_c", "conv3x3_tf32", "tf32_truncate", "tf32_round", "dat_forward", "dcndat_forward", "dcndat_config", "dcndat_block", "dat_config", "dat_param_shapes", "input_pad", "input_unpad", "count_params",
 ]
 
 _USE_LIBRARY = False
@@ -548,6 +548,81 @@ def dat_forward(sd: Dict[str, torch.Tensor], x0, x1, t, cfg: Optional[dict] = No
     if return_flows:
         return img, dict(ft0=[ft0_1, ft0_2, ft0_3, ft0_4], ft1=[ft1_1, ft1_2, ft1_3, ft1_4])
     return img
+
+
+# ----------------------------------------------------------------------------------------------
+# DCNDATv1 (models/archive/DCNDAT.py), read as repaired by SURVEY.md Note B
+# ----------------------------------------------------------------------------------------------
+
+def dcndat_config(nf=64, enc_res_blocks=5, dec_res_blocks=10, mlp_ratio=2):
+    """configs/archive/DCNDAT.yaml:4-8 + the per-level constants of models/archive/DCNDAT.py:209-218."""
+    return dict(nf=nf, enc_res_blocks=enc_res_blocks, dec_res_blocks=dec_res_blocks, mlp_ratio=mlp_ratio,
+                levels=dict(scale3=dict(n_samples=9, n_groups=8, n_heads=8), scale2=dict(n_samples=9, n_groups=4, n_heads=4),
+                            scale1=dict(n_samples=9, n_groups=4, n_heads=4)))
+
+
+def dcndat_block(p: _P, feat_t, feat0, feat1, ft0, ft1, n_samples, n_groups, n_heads, pred_res_flow=True):
+    """``CrossDeformableAttentionBlockwFlow.forward`` of the DCN flavour -- models/archive/DCNDAT.py:146-199."""
+    b, c, fh, fw = feat_t.shape
+
+    def movement(feat_x, ftx):                        # lines 146-148
+        h = torch.cat((feat_t, bwarp(feat_x, ftx), ftx), dim=1)
+        m = p.sub("conv_res_feat")
+        h = _prelu(m, "0.1", _conv(m, "0.0", h))
+        h = _prelu(m, "1.1", _conv(m, "1.0", h))
+        return _res5(m.sub("2"), h, c // 2)
+
+    def coords_mask(ftx, mv):                          # lines 150-157
+        o1, o2, mask = torch.chunk(_conv(p, "conv_res_offset_mask", mv), 3, dim=1)
+        res = 2.0 * torch.tanh(torch.cat((o1, o2), dim=1))
+        return res.view(b, n_groups * n_samples, 2, fh, fw) + ftx.unsqueeze(1), mask
+
+    mv0 = movement(feat0, ft0)
+    c0, m0 = coords_mask(ft0, mv0)
+    mv1 = movement(feat1, ft1)
+    c1, m1 = coords_mask(ft1, mv1)
+    w, bias = p["query_enhancer_dcn.regular_conv.weight"], p["query_enhancer_dcn.regular_conv.bias"]
+    q = _conv(p, "query_blender", torch.cat((dcn_given_offset(w, bias, feat0, c0, m0), feat_t,
+                                             dcn_given_offset(w, bias, feat1, c1, m1)), dim=1), padding=0)
+    kv = torch.cat((dsample(feat0, c0, n_groups, n_samples), dsample(feat1, c1, n_groups, n_samples)), dim=2)
+    a = attn(p.sub("attn"), q, kv, n_heads)
+    mlp = p.sub("mlp")
+    out = a + _conv(mlp, "fc2", F.gelu(_conv(mlp, "fc1", a, padding=0)), padding=0)
+    if not pred_res_flow:
+        return out
+    return out, _deconv(p, "conv_res_flow", mv0) + 2.0 * _resize2(ft0), _deconv(p, "conv_res_flow", mv1) + 2.0 * _resize2(ft1)
+
+
+def dcndat_forward(sd: Dict[str, torch.Tensor], x0, x1, t, cfg: Optional[dict] = None):
+    """``DCNDATv1.inference(x0, x1, t)`` -- models/archive/DCNDAT.py:231-251; the rgb mean is added at the end but the
+    inputs are NOT shifted by it (line 233 is commented out upstream)."""
+    cfg = cfg or dcndat_config()
+    nf = cfg["nf"]
+    p = _P(sd)
+    mean_ = torch.cat((x0, x1), dim=2).mean(1, keepdim=True).mean(2, keepdim=True).mean(3, keepdim=True)
+    f0 = _encoder(p.sub("cnn_encoder"), x0, cfg["enc_res_blocks"])
+    f1 = _encoder(p.sub("cnn_encoder"), x1, cfg["enc_res_blocks"])
+    # DCNInterFeatBuilderwithT with ONE shared DeformableConv2d (lines 81-110)
+    qb = p.sub("dcn_feat_t_builder")
+    _, _, fh, fw = f0[3].shape
+    tt = t.repeat(1, 1, fh, fw)
+    cb = qb.sub("convblock")
+
+    def motion(a, b_, plane):
+        return _prelu(cb, "3", _conv(cb, "2", _prelu(cb, "1", _conv(cb, "0", torch.cat((a, b_, plane), 1)))))
+
+    from0, ft0_4 = dcn_block(qb.sub("dcn"), f0[3], motion(f0[3], f1[3], tt))
+    from1, ft1_4 = dcn_block(qb.sub("dcn"), f1[3], motion(f1[3], f0[3], 1 - tt))
+    bb = qb.sub("blendblock")
+    q4 = _conv(bb, "2", _prelu(bb, "1", _conv(bb, "0", torch.cat((from0, from1), 1))))
+    s3 = _deconv(p, "query_builder3", torch.cat((q4, ft0_4, ft1_4), dim=1))
+    q3, ft0_3, ft1_3 = s3[:, :nf], s3[:, nf:nf + 2], s3[:, nf + 2:nf + 4]
+    a3, ft0_2, ft1_2 = dcndat_block(p.sub("dat_scale3"), q3, f0[2], f1[2], ft0_3, ft1_3, **cfg["levels"]["scale3"])
+    a2, ft0_1, ft1_1 = dcndat_block(p.sub("dat_scale2"), _deconv(p, "query_builder2", a3), f0[1], f1[1], ft0_2, ft1_2,
+                                    **cfg["levels"]["scale2"])
+    a1 = dcndat_block(p.sub("dat_scale1"), _deconv(p, "query_builder1", a2), f0[0], f1[0], ft0_1, ft1_1,
+                      pred_res_flow=False, **cfg["levels"]["scale1"])
+    return _generator(p.sub("generator"), a1, mean_, cfg["dec_res_blocks"])
 
 
 def input_pad(x, divisor: int = 16) -> Tuple[torch.Tensor, Tuple[int, int, int, int]]:

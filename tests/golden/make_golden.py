@@ -4,7 +4,7 @@ Runs only in the build container (needs the read-only checkout at /root/referenc
 torchvision 0.26.0 CPU ops).  Fixtures hold reference OUTPUTS; inputs and weights are rebuilt at test
 time from ``tests/_det.py``, which is shared with this script (``cases.py`` lists the cases).
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py [fixture names...]
 """
 from __future__ import annotations
 
@@ -25,7 +25,12 @@ import golden_cases as gc  # noqa: E402
 OUT = Path(__file__).resolve().parent
 
 
+ONLY = set(sys.argv[1:])     # e.g. `make_golden.py dcndat_model` rewrites just that fixture
+
+
 def save(name, **arrays):
+    if ONLY and name not in ONLY:
+        return
     np.savez_compressed(OUT / f"{name}.npz", **{k: np.ascontiguousarray(v.detach().numpy() if torch.is_tensor(v) else v)
                                                 for k, v in arrays.items()})
     print("wrote", name, {k: tuple(v.shape) for k, v in arrays.items()})
@@ -135,6 +140,52 @@ def main():
     names = np.array(sorted(net.state_dict().keys()))
     save("dat_model_full", pred=pred, n_params=np.array(sum(p.numel() for p in net.parameters())), names=names,
          shapes=np.array([str(tuple(net.state_dict()[k].shape)) for k in names]))
+
+    # ---- DCNDATv1 (models/archive/DCNDAT.py), repaired per SURVEY.md Note B ----------------------
+    RepairedDCNDATv1 = import_repaired_dcndat()
+    args = NS(gc.DCNDAT_SMALL_ARGS)
+    net = RepairedDCNDATv1(args).eval()
+    gc.fill(net.state_dict(), seed=3)
+    x0, x1, t = gc.dat_model_inputs(H=64, W=96, seed=3)
+    pred_small = net.inference(x0, x1, t)
+    args = NS(dict(nf=64, enc_res_blocks=5, dec_res_blocks=10, mlp_ratio=2, geo_lambda=0.01, distill_lambda=0.01))
+    net = RepairedDCNDATv1(args).eval()
+    gc.fill(net.state_dict(), seed=4)
+    x0, x1, t = gc.dat_model_inputs(H=64, W=64, seed=4)
+    names = np.array(sorted(net.state_dict().keys()))
+    save("dcndat_model", pred_small=pred_small, pred_full=net.inference(x0, x1, t),
+         n_params=np.array(sum(p.numel() for p in net.parameters())), names=names,
+         shapes=np.array([str(tuple(net.state_dict()[k].shape)) for k in names]))
+
+
+def import_repaired_dcndat():
+    """models/archive/DCNDAT.py names six symbols that no longer exist (SURVEY.md Note B).  Bind each to what it was
+    renamed to, import the file UNMODIFIED, and give the class the `generate_rgb_frame` body of
+    models/archive/DCNTrans.py:118-123 (= modules/generator.py BasicResPixelShuffleGenerator) as `self.generator`."""
+    import importlib
+    import models.BaseModel as rbase
+    import models.DAT as rdatm
+    import modules.deformable_attn as rdat
+    import modules.basic_blocks as rbb
+    import modules.generator as rgen
+    import utils as rutils
+    rdat.DeformAttn = rdat.Attn
+    base = types.ModuleType("models.base")
+    base.Basemodel = rbase.BaseModel
+    sys.modules["models.base"] = base
+    rdatm.Mlp = lambda in_features, hidden_features, out_features: rbb.FeadForward(in_features, int(hidden_features), out_features)
+    rutils.resize = rbase.BaseModel.resize
+    mod = importlib.import_module("models.archive.DCNDAT")
+    mod.make_layer = lambda nf, n_layers: rbb.make_residual_layers(nf=nf, n_layers=n_layers)
+
+    class RepairedDCNDATv1(mod.DCNDATv1):
+        def __init__(self, args):
+            super().__init__(args)
+            self.generator = rgen.BasicResPixelShuffleGenerator(args.nf, args.dec_res_blocks)
+
+        def generate_rgb_frame(self, feat, mean_):
+            return self.generator(feat, mean_)
+    return RepairedDCNDATv1
 
 
 if __name__ == "__main__":

@@ -142,6 +142,7 @@ def madat_inputs(B=2, H=8, W=10):
 
 # ---- whole model ------------------------------------------------------------------------------
 DAT_SMALL_ARGS = dict(nf=16, enc_res_blocks=1, dec_res_blocks=1, mlp_ratio=2, distill_lambda=0.01)
+DCNDAT_SMALL_ARGS = dict(nf=32, enc_res_blocks=1, dec_res_blocks=1, mlp_ratio=2, geo_lambda=0.01, distill_lambda=0.01)
 
 
 def dat_model_inputs(B=1, H=64, W=96, seed=0):

@@ -1,0 +1,98 @@
+"""DCNDATv1 (BASELINE configs[3]; models/archive/DCNDAT.py read as repaired by SURVEY.md Note B).
+
+CPU: the product module's parameter table and the oracle restatement against outputs of the reference's own class
+(tests/golden/dcndat_model.npz, written by tests/golden/make_golden.py::import_repaired_dcndat).
+GPU: the CUDA path (vfi_bwarp_f32, vfi_dcn_f32 with offset groups != weight groups, vfi_dattn_f32 on final
+coordinates, vfi_conv3x3_f32) against the same fixtures and against the oracle at a larger frame.
+"""
+import pytest
+import torch
+
+import golden_cases as gc
+import oracle
+from _util import assert_close
+
+N_PARAMS = 3677845
+
+
+def _cfg(args: dict):
+    return oracle.dcndat_config(**{k: v for k, v in args.items() if k not in ("geo_lambda", "distill_lambda")})
+
+
+def test_dcndat_param_table(golden):
+    import videoframeinterpolation_b200 as vfi
+    g = golden("dcndat_model")
+    sd = vfi.DCNDATv1(vfi.dcndat_default_args()).state_dict()
+    names = [str(n) for n in g["names"]]
+    assert sorted(sd) == names
+    for n, shp in zip(names, g["shapes"]):
+        assert str(tuple(sd[n].shape)) == str(shp), n
+    assert sum(v.numel() for v in sd.values()) == int(g["n_params"]) == N_PARAMS
+
+
+def test_dcndat_oracle_matches_reference(golden):
+    import videoframeinterpolation_b200 as vfi
+    g = golden("dcndat_model")
+    sd = gc.fill(vfi.DCNDATv1(vfi.dcndat_default_args(**gc.DCNDAT_SMALL_ARGS)).state_dict(), seed=3)
+    x0, x1, t = gc.dat_model_inputs(H=64, W=96, seed=3)
+    assert_close(oracle.dcndat_forward(sd, x0, x1, t, _cfg(gc.DCNDAT_SMALL_ARGS)), g["pred_small"], 2e-5, "dcndat small")
+    sd = gc.fill(vfi.DCNDATv1(vfi.dcndat_default_args()).state_dict(), seed=4)
+    x0, x1, t = gc.dat_model_inputs(H=64, W=64, seed=4)
+    with oracle.library_ops():
+        assert_close(oracle.dcndat_forward(sd, x0, x1, t), g["pred_full"], 2e-5, "dcndat nf=64")
+
+
+@pytest.fixture()
+def vfi_fp32():
+    import videoframeinterpolation_b200 as v
+    old = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False          # dense convs in fp32 for model-level parity
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield v
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def _load(net, sd):
+    net.load_state_dict({k: v.clone() for k, v in sd.items()}, strict=True)
+    return net.cuda().eval()
+
+
+@pytest.mark.gpu
+def test_dcndat_golden(vfi_fp32, golden):
+    vfi = vfi_fp32
+    g = golden("dcndat_model")
+    net = vfi.DCNDATv1(vfi.dcndat_default_args(**gc.DCNDAT_SMALL_ARGS))
+    net = _load(net, gc.fill(net.state_dict(), seed=3))
+    x0, x1, t = gc.dat_model_inputs(H=64, W=96, seed=3)
+    assert_close(net.inference(x0.cuda(), x1.cuda(), t.cuda()), g["pred_small"], 5e-5, "DCNDATv1 nf=32 vs reference")
+    net = vfi.DCNDATv1(vfi.dcndat_default_args())
+    net = _load(net, gc.fill(net.state_dict(), seed=4))
+    x0, x1, t = gc.dat_model_inputs(H=64, W=64, seed=4)
+    assert_close(net.inference(x0.cuda(), x1.cuda(), t.cuda()), g["pred_full"], 5e-5, "DCNDATv1 nf=64 vs reference")
+
+
+@pytest.mark.gpu
+def test_dcndat_vs_oracle_larger_frame_and_batch(vfi_fp32):
+    vfi = vfi_fp32
+    net = vfi.DCNDATv1(vfi.dcndat_default_args())
+    sd = gc.fill(net.state_dict(), seed=5)
+    net = _load(net, sd)
+    x0, x1, t = gc.dat_model_inputs(B=2, H=128, W=192, seed=5)
+    t = torch.tensor([0.5, 0.25]).view(2, 1, 1, 1)
+    with oracle.library_ops():
+        ref = oracle.dcndat_forward({k: v.cpu() for k, v in sd.items()}, x0, x1, t)
+    out = net.inference(x0.cuda(), x1.cuda(), t.cuda())
+    assert_close(out, ref, 5e-5, "DCNDATv1 2x128x192 vs oracle")
+    # frame pairs are independent: the batch equals its pairs run one by one
+    one = net.inference(x0[1:].cuda(), x1[1:].cuda(), t[1:].cuda())
+    assert_close(out[1:], one, 1e-5, "pair 1 alone")
+
+
+@pytest.mark.gpu
+def test_dcndat_graph_replay(vfi_fp32):
+    vfi = vfi_fp32
+    net = vfi.DCNDATv1(vfi.dcndat_default_args()).cuda().eval()
+    x0, x1, t = (v.cuda() for v in gc.dat_model_inputs(H=96, W=128, seed=6))
+    eager = net.inference(x0, x1, t).clone()
+    g = vfi.GraphedInference(net, x0, x1, t)
+    assert torch.equal(g(x0, x1, t), eager)

@@ -9,6 +9,7 @@ from .dcnv2 import deform_conv2d, DeformableConv2d, DeformableConv2dGivenOffset
 from .deformable_attn import Attn, CrossDeformableAttentionBlockwFlow
 from .madat import DeformAttnwMotion, DATwithMotionEstimation
 from .dat import DATwConstantnCv1, DCNInterFeatBuilderwithT, InputPadder, default_args
+from .dcndat import DCNDATv1, dcndat_default_args
 from .graph import GraphedInference
 from .checkpoint import load_reference_checkpoint, save_reference_checkpoint, strip_ddp_prefix
 
