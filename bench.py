@@ -219,6 +219,38 @@ def torch_cuda_baseline(args, dev, H, W):
             "sample": "oracle port of DATwConstantnCv1.inference with library ops on cuda:0, median of 3 after 1 warm-up"}
 
 
+def dcndat_1080p(args, dev, H, W):
+    """BASELINE configs[3] read literally: the DCNDATv1 archive model (models/archive/DCNDAT.py, repaired per SURVEY.md
+    Note B) on one padded frame pair resident in HBM -- this repo's CUDA-graph replay next to the same composition on
+    the PyTorch-CUDA library ops (oracle port with ATen grid_sample / torchvision deform_conv2d / cuDNN)."""
+    import oracle
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.workloads import init_dat_weights, seed_for
+    torch.manual_seed(0)
+    net = init_dat_weights(v.DCNDATv1(v.dcndat_default_args())).to(dev).eval().to(memory_format=torch.channels_last)
+    g = torch.Generator().manual_seed(seed_for(4, 1))
+    ph, pw = -(-H // 16) * 16, -(-W // 16) * 16
+    x0, x1 = (torch.rand(1, 3, ph, pw, generator=g).to(dev).contiguous(memory_format=torch.channels_last) for _ in range(2))
+    t = torch.full((1, 1, 1, 1), 0.5, device=dev)
+    out = {"model": "DCNDATv1 (configs/archive/DCNDAT.yaml, nf=64)", "frame": f"{pw}x{ph}", "pairs": 1, "unit": UNIT}
+    try:
+        with torch.no_grad():
+            graphed = v.GraphedInference(net, x0, x1, t)
+            ms = time_op(graphed.replay, max(args.steps, 5), None)
+            out.update({"value": 1e3 / ms, "ms_per_step": ms, "api": "DCNDATv1.inference replayed from a CUDA graph"})
+            del graphed
+            sd = {k: w.detach().clone() for k, w in net.state_dict().items()}
+            xa, xb = x0.contiguous(), x1.contiguous()
+            with oracle.library_ops():
+                ms_lib = time_op(lambda: oracle.dcndat_forward(sd, xa, xb, t), 3, None)
+            out["torch_cuda_baseline"] = {"value": 1e3 / ms_lib, "ms_per_step": ms_lib, "speedup_of_this_repo": ms_lib / ms,
+                                          "ops": "ATen grid_sampler_2d, torchvision deform_conv2d, cuDNN convs (tf32=%d), eager PyTorch" % args.tf32}
+    except torch.OutOfMemoryError as e:
+        out["unavailable"] = f"out of memory: {str(e)[:120]}"
+    torch.cuda.empty_cache()
+    return out
+
+
 def workload_name(args):
     ph, pw = -(-args.height // 16) * 16, -(-args.width // 16) * 16
     return (f"DAT (configs/DAT.yaml, nf=72) inference on synthetic {args.width}x{args.height} frame pairs replicate-padded to "
@@ -498,6 +530,7 @@ def run_vfi(args):
             if "value" in tb:
                 tb["speedup_of_this_repo"] = (1e3 * args.pairs / line["ms_per_step"]) / tb["value"]   # per GPU, frames/s over frames/s
             line["torch_cuda_baseline"] = tb
+            line["dcndat_1080p"] = dcndat_1080p(args, dev, H, W)
         if not args.no_cpu and world == 1:
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
