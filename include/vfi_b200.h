@@ -231,6 +231,17 @@ int vfi_frame_prep(const void* x0, const void* x1, int is_u8, float* out0, float
 int vfi_frame_finish(const float* y, const int64_t y_strides[4], const float* mean, void* out, int out_is_u8, int B, int H,
                      int W, int Hp, int Wp, int pad_top, int pad_left, void* stream);
 
+/* On-device validators.  Replaces: evaluate.py:15-26 (gaussian / create_window_3d),
+ * evaluate.py:29-79 (calculate_ssim: 11x11x11 Gaussian window over (channel, y, x), replicate padding 5, five
+ * conv3d calls) and evaluate.py:82-84 (calculate_psnr).
+ * img1, img2 (B,C,H,W) contiguous fp32; val_range = L of evaluate.py:30-42 (1 for frames in [0,1]).
+ * out (B,3) fp64 per sample: [0] sum of squared differences, [1] sum of the SSIM map, [2] sum of v1/v2 (the
+ *   contrast-structure term): the means of the reference are these sums / (C*H*W), psnr = -10 log10(sse / n).
+ * Deterministic (fixed summation order).  H, W >= 11, C <= 32.  workspace: vfi_frame_metrics_workspace_bytes. */
+size_t vfi_frame_metrics_workspace_bytes(int B, int C, int H, int W);
+int vfi_frame_metrics_f32(const float* img1, const float* img2, double* out, int B, int C, int H, int W, float val_range,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vfi_launch_count(void);

@@ -27,7 +27,7 @@ __all__ = [
     "library_ops", "grid_sample_bilinear", "bwarp", "splat_sum", "fwarp", "softsplat",
     "fwarp_using_two_frames", "fwarp_mframes", "deform_conv2d", "dcn_block", "dcn_given_offset",
     "ref_coords", "dsample", "attn", "dat_block", "madat_ref_feats", "madat_attn",
-    "layer_norm_c", "conv3x3_tf32", "tf32_truncate", "tf32_round", "dat_forward", "dcndat_forward", "dcndat_config", "dcndat_block", "dat_config", "dat_param_shapes", "input_pad", "input_unpad", "count_params",
+    "layer_norm_c", "conv3x3_tf32", "tf32_truncate", "tf32_round", "calculate_ssim", "calculate_psnr", "dat_forward", "dcndat_forward", "dcndat_config", "dcndat_block", "dat_config", "dat_param_shapes", "input_pad", "input_unpad", "count_params",
 ]
 
 _USE_LIBRARY = False
@@ -623,6 +623,47 @@ def dcndat_forward(sd: Dict[str, torch.Tensor], x0, x1, t, cfg: Optional[dict] =
     a1 = dcndat_block(p.sub("dat_scale1"), _deconv(p, "query_builder1", a2), f0[0], f1[0], ft0_1, ft1_1,
                       pred_res_flow=False, **cfg["levels"]["scale1"])
     return _generator(p.sub("generator"), a1, mean_, cfg["dec_res_blocks"])
+
+
+# ----------------------------------------------------------------------------------------------
+# validators (evaluate.py:15-84)
+# ----------------------------------------------------------------------------------------------
+
+def _gaussian(window_size: int, sigma: float) -> torch.Tensor:
+    """evaluate.py:15-17."""
+    import math
+    g = torch.Tensor([math.exp(-(x - window_size // 2) ** 2 / float(2 * sigma ** 2)) for x in range(window_size)])
+    return g / g.sum()
+
+
+def calculate_ssim(img1, img2, window_size: int = 11, val_range: Optional[float] = None, full: bool = False):
+    """``calculate_ssim`` -- evaluate.py:29-79 (3-D window of evaluate.py:20-26 without the ``.cuda()``)."""
+    if val_range is None:
+        L = (255 if torch.max(img1) > 128 else 1) - (-1 if torch.min(img1) < -0.5 else 0)
+    else:
+        L = val_range
+    _, _, height, width = img1.size()
+    real = min(window_size, height, width)
+    w1 = _gaussian(real, 1.5).unsqueeze(1)
+    w2 = w1.mm(w1.t())
+    window = (w2.unsqueeze(2) @ w1.t()).expand(1, 1, real, real, real).contiguous().to(img1)
+    a, b = img1.unsqueeze(1), img2.unsqueeze(1)
+
+    def blur(x):
+        return F.conv3d(F.pad(x, (5, 5, 5, 5, 5, 5), mode="replicate"), window, padding=0, groups=1)
+
+    mu1, mu2 = blur(a), blur(b)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1, s2, s12 = blur(a * a) - mu1_sq, blur(b * b) - mu2_sq, blur(a * b) - mu1_mu2
+    c1, c2 = (0.01 * L) ** 2, (0.03 * L) ** 2
+    v1, v2 = 2.0 * s12 + c2, s1 + s2 + c2
+    ssim = (((2 * mu1_mu2 + c1) * v1) / ((mu1_sq + mu2_sq + c1) * v2)).mean()
+    return (ssim, torch.mean(v1 / v2)) if full else ssim
+
+
+def calculate_psnr(img1, img2):
+    """``calculate_psnr`` -- evaluate.py:82-84."""
+    return -10 * torch.log10(((img1 - img2) * (img1 - img2)).mean())
 
 
 def input_pad(x, divisor: int = 16) -> Tuple[torch.Tensor, Tuple[int, int, int, int]]:

@@ -157,6 +157,16 @@ def main():
          n_params=np.array(sum(p.numel() for p in net.parameters())), names=names,
          shapes=np.array([str(tuple(net.state_dict()[k].shape)) for k in names]))
 
+    # ---- validators: evaluate.py:29-84 (its window is created with .cuda(); identity here) --------
+    sys.modules.setdefault("imageio", types.SimpleNamespace(imread=None))
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    import evaluate as rev
+    out = {}
+    for key, (a, b, L) in gc.metrics_cases().items():
+        ssim, cs = rev.calculate_ssim(a, b, full=True, val_range=L)
+        out[key] = torch.stack((rev.calculate_psnr(a, b), ssim, cs))
+    save("metrics", **out)
+
 
 def import_repaired_dcndat():
     """models/archive/DCNDAT.py names six symbols that no longer exist (SURVEY.md Note B).  Bind each to what it was

@@ -148,3 +148,20 @@ DCNDAT_SMALL_ARGS = dict(nf=32, enc_res_blocks=1, dec_res_blocks=1, mlp_ratio=2,
 def dat_model_inputs(B=1, H=64, W=96, seed=0):
     return (det.uniform("dm.x0", (B, 3, H, W), seed), det.uniform("dm.x1", (B, 3, H, W), seed),
             torch.full((B, 1, 1, 1), 0.5))
+
+
+# ---- validators (evaluate.py:29-84) ------------------------------------------------------------
+def metrics_cases():
+    """name -> (img1, img2, val_range or None).  Frames in [0,1], in [0,255], a ragged size, one channel, six channels."""
+    out = {}
+    a = det.uniform("mt.a", (2, 3, 40, 50))
+    out["unit"] = (a, (a + 0.05 * det.normal("mt.n", (2, 3, 40, 50))).clamp(0, 1), None)
+    a = det.uniform("mt.b", (1, 3, 67, 45)) * 255.0
+    out["bytes"] = (a, (a + 4.0 * det.normal("mt.m", (1, 3, 67, 45))).clamp(0, 255), None)
+    a = det.uniform("mt.c", (1, 1, 33, 64))
+    out["gray"] = (a, det.uniform("mt.d", (1, 1, 33, 64)), 1.0)
+    a = det.uniform("mt.e", (1, 6, 32, 32))
+    out["six"] = (a, (a * 0.9 + 0.03), None)
+    a = det.uniform("mt.f", (1, 3, 11, 11))
+    out["tiny"] = (a, (a + 0.1 * det.normal("mt.g", (1, 3, 11, 11))).clamp(0, 1), None)
+    return out

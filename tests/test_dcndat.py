@@ -85,7 +85,7 @@ def test_dcndat_vs_oracle_larger_frame_and_batch(vfi_fp32):
     assert_close(out, ref, 5e-5, "DCNDATv1 2x128x192 vs oracle")
     # frame pairs are independent: the batch equals its pairs run one by one
     one = net.inference(x0[1:].cuda(), x1[1:].cuda(), t[1:].cuda())
-    assert_close(out[1:], one, 1e-5, "pair 1 alone")
+    assert_close(out[1:], one, 5e-5, "pair 1 alone")     # cuDNN picks other fp32 algorithms for the other batch size
 
 
 @pytest.mark.gpu
@@ -95,4 +95,6 @@ def test_dcndat_graph_replay(vfi_fp32):
     x0, x1, t = (v.cuda() for v in gc.dat_model_inputs(H=96, W=128, seed=6))
     eager = net.inference(x0, x1, t).clone()
     g = vfi.GraphedInference(net, x0, x1, t)
-    assert torch.equal(g(x0, x1, t), eager)
+    first = g(x0, x1, t).clone()
+    assert_close(first, eager, 1e-5, "graph replay vs eager")
+    assert_close(g.replay(), first, 1e-6, "replay vs replay")   # not bitwise: the library convs around the path may split-K with atomics

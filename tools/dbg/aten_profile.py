@@ -7,7 +7,10 @@ from videoframeinterpolation_b200.workloads import init_dat_weights
 from torch.profiler import profile, ProfilerActivity
 dev = torch.device("cuda")
 torch.manual_seed(0)
-net = init_dat_weights(v.DATwConstantnCv1(v.default_args())).to(dev).eval().to(memory_format=torch.channels_last)
+if len(sys.argv) > 1 and sys.argv[1] == "dcndat":
+    net = init_dat_weights(v.DCNDATv1(v.dcndat_default_args())).to(dev).eval().to(memory_format=torch.channels_last)
+else:
+    net = init_dat_weights(v.DATwConstantnCv1(v.default_args())).to(dev).eval().to(memory_format=torch.channels_last)
 x0, x1 = (torch.rand(1, 3, 1088, 1920, device=dev).contiguous(memory_format=torch.channels_last) for _ in range(2))
 t = torch.full((1, 1, 1, 1), 0.5, device=dev)
 for _ in range(3):
@@ -16,6 +19,13 @@ torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True, with_stack=False) as prof:
     net.inference(x0, x1, t)
     torch.cuda.synchronize()
+print("==== kernels ====")
+kern = {}
+for e in prof.events():
+    if e.device_type == torch.autograd.DeviceType.CUDA:
+        k = kern.setdefault(e.name[:90], [0, 0.0]); k[0] += 1; k[1] += e.device_time
+for name, (n, us) in sorted(kern.items(), key=lambda kv: -kv[1][1])[:30]:
+    print(f"{us:10.1f} us  n={n:4d}  {name}")
 print(prof.key_averages(group_by_input_shape=True).table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=40, max_shapes_column_width=70))
 print("==== ATen ops that launch kernels, by shape ====")
 rows = [e for e in prof.key_averages(group_by_input_shape=True) if e.key.startswith("aten::") and e.device_time_total > 0

@@ -11,6 +11,7 @@ from .madat import DeformAttnwMotion, DATwithMotionEstimation
 from .dat import DATwConstantnCv1, DCNInterFeatBuilderwithT, InputPadder, default_args
 from .dcndat import DCNDATv1, dcndat_default_args
 from .graph import GraphedInference
+from .metrics import calculate_psnr, calculate_ssim, frame_metrics
 from .checkpoint import load_reference_checkpoint, save_reference_checkpoint, strip_ddp_prefix
 
 FunctionSoftsplat = softsplat   # name used by BASELINE.json's north_star for the same four-argument call

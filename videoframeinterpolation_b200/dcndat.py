@@ -28,7 +28,7 @@ from . import conv as _conv
 from .blocks import (BasicResPixelShuffleGenerator, FeadForward, HalfChannelConv5ResBlock, SameChannelResEncoder,
                      conv_bias_act, conv_prelu, resize, run_conv_chain)
 from .dcnv2 import DeformableConv2d, DeformableConv2dGivenOffset
-from .deformable_attn import Attn, fused_deformable_attention, grouped_sample
+from .deformable_attn import Attn, fused_deformable_attention, fused_supported, grouped_sample
 from .warp import bwarp
 
 __all__ = ["DCNDATv1", "dcndat_default_args"]
@@ -105,7 +105,7 @@ class DCNCrossDeformableAttentionBlockwFlow(nn.Module):
         q = self.query_blender(torch.cat((self.query_enhancer_dcn(feat0, c0, m0), feat_t,
                                           self.query_enhancer_dcn(feat1, c1, m1)), dim=1))
         b, _, fh, fw = feat_t.shape
-        if self.n_groups == self.n_heads:
+        if fused_supported(self.in_c, self.n_groups, self.n_heads):
             attended = fused_deformable_attention(q, feat0, feat1, c0.reshape(b, -1, fh, fw), c1.reshape(b, -1, fh, fw), None, None,
                                                   *self.attn._weights(), n_groups=self.n_groups, n_samples=self.n_samples,
                                                   n_heads=self.n_heads, offset_scale=1.0, coords_final=True)

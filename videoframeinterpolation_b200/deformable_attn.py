@@ -91,6 +91,15 @@ def attention_over_samples(q, kv, wq, bq, wk, bk, wv, bv, n_heads: int, want_sco
     return (out, s0, s1) if want_scores else out
 
 
+# (C / nG, nG) pairs vfi_dattn_f32 is instantiated for (csrc/dattn.cu, VFI_DATTN_CASE); other shapes take the
+# materialising kernels (vfi_dsample_f32 + vfi_attn_f32)
+_FUSED_INSTANCES = {(9, 8), (18, 4), (8, 8), (16, 4), (4, 4), (2, 8), (8, 4), (3, 8), (6, 4)}
+
+
+def fused_supported(channels: int, n_groups: int, n_heads: int) -> bool:
+    return n_groups == n_heads and channels % n_groups == 0 and (channels // n_groups, n_groups) in _FUSED_INSTANCES
+
+
 def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torch.Tensor], ft1: Optional[torch.Tensor],
                                wq, bq, wk, bk, wv, bv, n_groups: int, n_samples: int, n_heads: int, offset_scale: float,
                                coords_final: bool = False, want_scores: bool = False, offs_bias=None):
@@ -261,7 +270,7 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
         else:
             mv0 = self._get_movement_feats(feat_t, feat0, ft0)
             mv1 = self._get_movement_feats(feat_t, feat1, ft1)
-        if self.n_groups == self.n_heads:
+        if fused_supported(self.in_c, self.n_groups, self.n_heads):
             # bias-free conv: the fused kernel adds conv_res_offset.bias itself (same fp32 order: conv + bias, then tanh)
             co = self.conv_res_offset
             if _conv.eligible(co, mv0) and _conv.eligible(co, mv1):
