@@ -231,6 +231,13 @@ int vfi_frame_prep(const void* x0, const void* x1, int is_u8, float* out0, float
 int vfi_frame_finish(const float* y, const int64_t y_strides[4], const float* mean, void* out, int out_is_u8, int B, int H,
                      int W, int Hp, int Wp, int pad_top, int pad_left, void* stream);
 
+/* Glue of the DCNDAT block in one pass.  Replaces: models/archive/DCNDAT.py:150-157 (_get_ref_coords_mask: chunk,
+ * 2*tanh, view, + flow) and :69-70 (offset.permute(0,2,1,3,4).flip(1).contiguous().view, sigmoid(mask)).
+ * raw (B,3n,H,W) with element strides raw_strides, n = nG*nS; ft (B,2,H,W) with element strides ft_strides.
+ * coords (B,n,2,H,W), dcn_offset (B,2n,H,W) [all y then all x, the order line 69 produces], mask (B,n,H,W): contiguous. */
+int vfi_dcndat_coords_f32(const float* raw, const int64_t raw_strides[4], const float* ft, const int64_t ft_strides[4],
+                          float* coords, float* dcn_offset, float* mask, int B, int n, int H, int W, void* stream);
+
 /* On-device validators.  Replaces: evaluate.py:15-26 (gaussian / create_window_3d),
  * evaluate.py:29-79 (calculate_ssim: 11x11x11 Gaussian window over (channel, y, x), replicate padding 5, five
  * conv3d calls) and evaluate.py:82-84 (calculate_psnr).

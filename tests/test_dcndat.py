@@ -98,3 +98,31 @@ def test_dcndat_graph_replay(vfi_fp32):
     first = g(x0, x1, t).clone()
     assert_close(first, eager, 1e-5, "graph replay vs eager")
     assert_close(g.replay(), first, 1e-6, "replay vs replay")   # not bitwise: the library convs around the path may split-K with atomics
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("channels_last", [False, True])
+def test_dcndat_coords_kernel_matches_the_composition(vfi_fp32, channels_last):
+    """vfi_dcndat_coords_f32 against DCNDAT.py:150-157 + 69-70 written out in torch ops (same rounding sequence)."""
+    import _det as det
+    vfi = vfi_fp32
+    b, nG, nS, h, w = 2, 4, 9, 37, 53
+    n = nG * nS
+    blk = vfi.dcndat.DCNCrossDeformableAttentionBlockwFlow(64, 64, n_samples=nS, n_groups=nG, n_heads=nG, mlp_ratio=2).cuda().eval()
+    raw = det.normal("dcg.raw", (b, 3 * n, h, w), std=1.5).cuda()
+    if channels_last:
+        raw = raw.contiguous(memory_format=torch.channels_last)
+    ft = det.normal("dcg.ft", (b, 6, h, w), std=3.0).cuda()[:, 2:4]          # a channel slice, as in the model
+    blk.conv_res_offset_mask = torch.nn.Identity()                             # feed raw straight through
+    import videoframeinterpolation_b200.dcndat as dd
+    old = dd.conv_bias_act
+    dd.conv_bias_act = lambda conv, x: x
+    try:
+        coords, off, mask = blk._coords_offsets_mask(ft, raw)
+    finally:
+        dd.conv_bias_act = old
+    o1, o2, m = torch.chunk(raw, 3, dim=1)
+    ref = (2.0 * torch.tanh(torch.cat((o1, o2), dim=1))).reshape(b, n, 2, h, w) + ft.unsqueeze(1)
+    assert_close(coords, ref, 1e-6, "coords")
+    assert_close(off, ref.permute(0, 2, 1, 3, 4).flip(1).contiguous().view(b, -1, h, w), 1e-6, "dcn offsets")
+    assert_close(mask, torch.sigmoid(m), 1e-6, "mask")

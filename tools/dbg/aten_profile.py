@@ -32,3 +32,8 @@ rows = [e for e in prof.key_averages(group_by_input_shape=True) if e.key.startsw
         and not any(k in e.key for k in ("conv", "addmm", "gelu", "cudnn"))]
 for e in sorted(rows, key=lambda e: -e.device_time_total)[:60]:
     print(f"{e.key:28s} n={e.count:3d} cuda_us={e.device_time_total:9.1f} shapes={str(e.input_shapes)[:110]}")
+print("==== elementwise_kernel launches by op ====")
+for e in sorted([e for e in prof.key_averages(group_by_input_shape=True) if e.device_time_total > 0 and e.key.startswith("aten::")
+                 and any(k in e.key for k in ("copy_", "fill_", "add", "mul", "sub", "cat", "contiguous", "tanh", "sigmoid", "clone"))],
+                key=lambda e: -e.device_time_total)[:25]:
+    print(f"{e.key:24s} n={e.count:3d} cuda_us={e.device_time_total:9.1f} shapes={str(e.input_shapes)[:120]}")

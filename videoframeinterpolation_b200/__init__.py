@@ -9,6 +9,7 @@ from .dcnv2 import deform_conv2d, DeformableConv2d, DeformableConv2dGivenOffset
 from .deformable_attn import Attn, CrossDeformableAttentionBlockwFlow
 from .madat import DeformAttnwMotion, DATwithMotionEstimation
 from .dat import DATwConstantnCv1, DCNInterFeatBuilderwithT, InputPadder, default_args
+from . import dcndat
 from .dcndat import DCNDATv1, dcndat_default_args
 from .graph import GraphedInference
 from .metrics import calculate_psnr, calculate_ssim, frame_metrics

@@ -49,6 +49,7 @@ SIGNATURES = {
     "vfi_frame_finish": (c_int, [c_void_p] * 4 + [c_int] * 8 + [c_void_p]),
     "vfi_dcn_im2col_f32": (c_int, [c_void_p] * 4 + [c_int] * 10 + [c_void_p]),
     "vfi_dcn_col2im_f32": (c_int, [c_void_p] * 7 + [c_int] * 10 + [c_void_p]),
+    "vfi_dcndat_coords_f32": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
     "vfi_frame_metrics_workspace_bytes": (c_size_t, [c_int] * 4),
     "vfi_frame_metrics_f32": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_float, c_void_p, c_size_t, c_void_p]),
     "vfi_launch_count": (c_int64, []),

@@ -83,7 +83,7 @@ def deform_conv2d(input: torch.Tensor, offset: torch.Tensor, weight: torch.Tenso
     if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in (input, offset, weight, bias, mask)):
         return _DeformConvFn.apply(input, offset, weight, bias, mask, _pair(stride), _pair(padding), _pair(dilation), algo)
     dev = _lib.require_cuda(input, offset, weight, bias, mask)
-    x, offset, weight = _lib.f32c(input), _lib.f32c(offset), _lib.f32c(weight)
+    x, offset, weight = _lib.planar(input), _lib.f32c(offset), _lib.f32c(weight)   # channels-last input: one transpose kernel
     bias, mask = _lib.f32c(bias), _lib.f32c(mask)
     B, Cin, H, W = x.shape
     Cout, cin_g, kh, kw = weight.shape

@@ -186,6 +186,37 @@ class Attn(nn.Module):
         return torch.einsum("bsd,bcsd->bcd", w, v).reshape(b, self.out_c, fh, fw)
 
 
+def movement_feats_pair(me, feat_t, feat0, feat1, ft0, ft1):
+    """Both movement features with the first two convs split over their input channels (a convolution is linear
+    in them), all passes on the tensor-core kernel:
+        conv0(cat(feat_t, warped, flow)) = conv0_a(feat_t) + conv0_b(cat(warped, flow))
+    The feat_t term is shared by the two frames, the concat (and cuDNN's channel padding of its 146 channels)
+    disappears, and conv1 (144 -> 72) runs as two 72-channel passes.  Same sums up to fp32 addition order."""
+    c0, p0, c1, p1 = me[0][0], me[0][1], me[1][0], me[1][1]
+    C = feat_t.shape[1]
+    b, _, fh, fw = feat_t.shape
+    shared = _conv.conv3x3(c0, feat_t, in_slice=(0, C, 0))                       # + bias, no activation
+    outs = []
+    for feat_x, ftx in ((feat0, ft0), (feat1, ft1)):
+        wf = torch.empty((b, fh, fw, C + 4), dtype=torch.float32, device=feat_t.device).permute(0, 3, 1, 2)
+        _bwarp_forward(feat_x, ftx, out=wf[:, :C])
+        wf[:, C:C + 2] = ftx
+        wf[:, C + 2:] = 0.0
+        y = _conv.conv3x3(c0, wf, p0.weight, residual=shared, use_bias=False, in_slice=(C, 2 * C + 2, 2))
+        r = _conv.conv3x3(c1, y[:, :C], in_slice=(0, C, 0))
+        z = _conv.conv3x3(c1, y[:, C:], p1.weight, residual=r, use_bias=False, in_slice=(C, 2 * C, 0))
+        outs.append(me[2](z))
+    return outs
+
+
+def movement_split_ok(me, feat_t, feat0):
+    C = feat_t.shape[1]
+    return (C % 4 == 0 and _conv.part_eligible(me[0][0], feat_t) and _conv.part_eligible(me[1][0], feat_t)
+            and feat0.is_cuda and feat0.dtype == torch.float32
+            and bool(_lib.lib().vfi_conv3x3_supported(C + 4, C + 4, me[0][0].out_channels, 1))
+            and bool(_lib.lib().vfi_conv3x3_supported(C, 2 * C, me[1][0].out_channels, 1)))
+
+
 class CrossDeformableAttentionBlockwFlow(nn.Module):
     def __init__(self, in_c, out_c, n_samples=9, n_groups=12, n_heads=12, mlp_ratio=2.0, offset_scale=2.0,
                  pred_res_flow=True):
@@ -217,35 +248,10 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
         return grouped_sample(feat, flow, self.n_groups, self.n_samples)        # b, c, nS, fh*fw
 
     def _movement_feats_pair(self, feat_t, feat0, feat1, ft0, ft1):
-        """Both movement features with the first two convs split over their input channels (a convolution is linear
-        in them), all passes on the tensor-core kernel:
-            conv0(cat(feat_t, warped, flow)) = conv0_a(feat_t) + conv0_b(cat(warped, flow))
-        The feat_t term is shared by the two frames, the concat (and cuDNN's channel padding of its 146 channels)
-        disappears, and conv1 (144 -> 72) runs as two 72-channel passes.  Same sums up to fp32 addition order."""
-        me = self.movement_extractor
-        c0, p0, c1, p1 = me[0][0], me[0][1], me[1][0], me[1][1]
-        C = feat_t.shape[1]
-        b, _, fh, fw = feat_t.shape
-        shared = _conv.conv3x3(c0, feat_t, in_slice=(0, C, 0))                       # + bias, no activation
-        outs = []
-        for feat_x, ftx in ((feat0, ft0), (feat1, ft1)):
-            wf = torch.empty((b, fh, fw, C + 4), dtype=torch.float32, device=feat_t.device).permute(0, 3, 1, 2)
-            _bwarp_forward(feat_x, ftx, out=wf[:, :C])
-            wf[:, C:C + 2] = ftx
-            wf[:, C + 2:] = 0.0
-            y = _conv.conv3x3(c0, wf, p0.weight, residual=shared, use_bias=False, in_slice=(C, 2 * C + 2, 2))
-            r = _conv.conv3x3(c1, y[:, :C], in_slice=(0, C, 0))
-            z = _conv.conv3x3(c1, y[:, C:], p1.weight, residual=r, use_bias=False, in_slice=(C, 2 * C, 0))
-            outs.append(me[2](z))
-        return outs
+        return movement_feats_pair(self.movement_extractor, feat_t, feat0, feat1, ft0, ft1)
 
     def _split_ok(self, feat_t, feat0):
-        me = self.movement_extractor
-        C = feat_t.shape[1]
-        return (C % 4 == 0 and _conv.part_eligible(me[0][0], feat_t) and _conv.part_eligible(me[1][0], feat_t)
-                and feat0.is_cuda and feat0.dtype == torch.float32
-                and bool(_lib.lib().vfi_conv3x3_supported(C + 4, C + 4, me[0][0].out_channels, 1))
-                and bool(_lib.lib().vfi_conv3x3_supported(C, 2 * C, me[1][0].out_channels, 1)))
+        return movement_split_ok(self.movement_extractor, feat_t, feat0)
 
     # -- fused forward ------------------------------------------------------------------------------
     def _forward_autograd(self, feat_t, feat0, feat1, ft0, ft1):
