@@ -114,6 +114,26 @@ class DCNCrossDeformableAttentionBlockwFlow(nn.Module):
                   coords.data_ptr(), off.data_ptr(), mask.data_ptr(), b, n, fh, fw, _lib.stream_ptr(dev))
         return coords, off, mask
 
+    def _blend_query(self, parts):
+        """``query_blender(cat(parts))`` (DCNDAT.py:182): the 1x1 conv as three planar GEMMs W_i @ part_i accumulated in
+        place -- no 192-channel concat and no transpose of it to the conv's layout (1.1 ms at 544x960; concatenating
+        straight into a channels-last buffer was measured slower still).  Same math mode as the cuDNN convs around it."""
+        qb = self.query_blender
+        x0 = parts[0]
+        if not (x0.is_cuda and x0.dtype == torch.float32 and not torch.is_grad_enabled() and qb.bias is not None):
+            return qb(torch.cat(parts, dim=1))
+        b, c, fh, fw = x0.shape
+        w = qb.weight.reshape(qb.out_channels, 3, c)
+        out = qb.bias.view(1, -1, 1).expand(b, qb.out_channels, fh * fw).contiguous()
+        prev = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = bool(torch.backends.cudnn.allow_tf32)
+        try:
+            for i, part in enumerate(parts):
+                out.baddbmm_(w[:, i].unsqueeze(0).expand(b, -1, -1), _lib.planar(part).view(b, c, fh * fw))
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = prev
+        return out.view(b, qb.out_channels, fh, fw)
+
     def forward(self, feat_t, feat0, feat1, ft0, ft1):
         if movement_split_ok(self.conv_res_feat, feat_t, feat0):
             mv0, mv1 = movement_feats_pair(self.conv_res_feat, feat_t, feat0, feat1, ft0, ft1)
@@ -127,8 +147,7 @@ class DCNCrossDeformableAttentionBlockwFlow(nn.Module):
         b, c, fh, fw = feat_t.shape
         parts = (deform_conv2d(feat0, off0, rc.weight, rc.bias, padding=1, mask=m0), feat_t,
                  deform_conv2d(feat1, off1, rc.weight, rc.bias, padding=1, mask=m1))
-        qin = torch.cat(parts, dim=1)     # (cat straight into a channels-last buffer was measured slower: 19.9 vs 18.4 ms / step)
-        q = self.query_blender(qin)
+        q = self._blend_query(parts)
         if fused_supported(self.in_c, self.n_groups, self.n_heads):
             attended = fused_deformable_attention(q, feat0, feat1, c0.reshape(b, -1, fh, fw), c1.reshape(b, -1, fh, fw), None, None,
                                                   *self.attn._weights(), n_groups=self.n_groups, n_samples=self.n_samples,
