@@ -76,12 +76,16 @@ int vfi_bwarp_f32(const float* img, const float* flow, const float* lin_x, const
  * Non-finite targets are skipped and corners are bounds-tested one by one, as the reference kernel does
  * (modules/softsplat.py:306-307, 325-339).  All tensors contiguous NCHW here; the Python wrapper makes
  * non-contiguous views contiguous (the reference bakes strides into its NVRTC source instead).
+ * workspace == NULL: scatter form (fp32 atomics).  A 16-byte aligned workspace of vfi_splat_workspace_bytes selects
+ * the gather form of vfi_splat_fused_f32 below with the sums left un-normalised: a link pass, then one owner thread
+ * per target pixel stores (accumulate == 0) or adds (accumulate != 0) this source's sums to num / den -- no
+ * floating-point atomics and no zero fill; used by the two-frame / multi-branch callers from 8 channels up.
  */
 int vfi_splat_f32(const float* in, const float* flow, const float* metric, const float* t,
                   float* num, float* den, int B, int C, int H, int W,
                   int weight_mode, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
 /* Bytes of scratch vfi_splat_fused_f32 needs for this shape (68 B per source pixel: 4 claim slots + 4 slot weights
- * + list head + 4 overflow nodes; independent of C).  vfi_splat_f32 itself needs none (workspace may be NULL). */
+ * + list head + 4 overflow nodes; independent of C).  vfi_splat_f32's scatter form needs none (workspace may be NULL). */
 size_t vfi_splat_workspace_bytes(int B, int C, int H, int W);
 
 /* out = num / f(den) per eps_mode; blank_mask (B,1,H,W) uint8, optional: f(den) < blank_threshold

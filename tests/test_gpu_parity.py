@@ -90,6 +90,42 @@ def test_splat_golden(vfi, golden):
         assert (m.cpu().to(torch.uint8) != g[key + "_mask"]).float().mean() < 0.01
 
 
+@pytest.mark.parametrize("algo", ["scatter", "gather"])
+def test_two_frame_and_mframes_both_routes(vfi, golden, algo, monkeypatch):
+    """a4 / a5 through the scatter kernel (fp32 atomics) and through the gather route of vfi_splat_f32 (a workspace is
+    passed: link pass + one owner thread per target pixel adds each direction / branch, no fp atomics): the golden
+    cases (C = 3) forced down each route, then C = 16 and C = 64 with folding flows against the oracle."""
+    monkeypatch.setenv("VFI_SPLAT_ALGO", algo)
+    g = golden("splat")
+    for key, args in gc.two_frame_cases().items():
+        o, m = vfi.fwarp_using_two_frames(*cu(*args))
+        assert_close(o, g[key + "_out"], TOL_SPLAT, f"{key} ({algo})")
+        assert (m.cpu().to(torch.uint8) != g[key + "_mask"]).float().mean() < 0.01
+    for key, args in gc.mframes_cases().items():
+        o, m = vfi.fwarp_mframes(*cu(*args))
+        assert_close(o, g[key + "_out"], TOL_SPLAT, f"{key} ({algo})")
+        assert (m.cpu().to(torch.uint8) != g[key + "_mask"]).float().mean() < 0.01
+    for (B, C, H, W) in ((2, 16, 67, 121), (1, 64, 136, 240)):
+        tag = f"tfr.{B}.{C}"
+        in1, in2 = det.normal(tag + ".a", (B, C, H, W)), det.normal(tag + ".b", (B, C, H, W))
+        f1 = det.flow_field(tag + ".f1", B, H, W, sigma=4.0, nonfinite_frac=0.001)
+        f2 = det.flow_field(tag + ".f2", B, H, W, sigma=4.0)
+        t1 = det.uniform(tag + ".t", (B, 1, 1, 1), lo=0.1, hi=0.9)
+        m1, m2 = det.normal(tag + ".m1", (B, 1, H, W), std=2.0), det.normal(tag + ".m2", (B, 1, H, W), std=2.0)
+        ref, ref_mask = oracle.fwarp_using_two_frames(in1, f1, t1, in2, f2, 1 - t1, m1, m2)
+        o, m = vfi.fwarp_using_two_frames(*cu(in1, f1, t1, in2, f2, 1 - t1, m1, m2))
+        assert_close(o, ref, TOL_SPLAT, f"two-frame {C} ch ({algo})")
+        assert (m.cpu() != ref_mask).float().mean() < 0.01
+        nb = 3
+        fb1 = torch.stack([det.flow_field(f"{tag}.g1.{i}", B, H, W, sigma=3.0) for i in range(nb)])
+        fb2 = torch.stack([det.flow_field(f"{tag}.g2.{i}", B, H, W, sigma=3.0) for i in range(nb)])
+        tb = det.uniform(tag + ".tb", (nb, B, 1, 1, 1), lo=0.1, hi=0.9)
+        ref, ref_mask = oracle.fwarp_mframes(in1, fb1, tb, in2, fb2, 1 - tb, m1, m2)
+        o, m = vfi.fwarp_mframes(*cu(in1, fb1, tb, in2, fb2, 1 - tb, m1, m2))
+        assert_close(o, ref, TOL_SPLAT, f"mframes {C} ch ({algo})")
+        assert (m.cpu() != ref_mask).float().mean() < 0.01
+
+
 @pytest.mark.parametrize("mode", ["sum", "avg", "linear", "soft", "soft-zeroeps", "linear-clipeps"])
 @pytest.mark.parametrize("shape", [(1, 3, 135, 240), (2, 16, 67, 121)])
 def test_splat_vs_oracle(vfi, mode, shape):

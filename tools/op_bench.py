@@ -111,6 +111,21 @@ def run_splat(a, dev, flush):
            wl.bytes_splat(B, C, H, W, a.mode))
 
 
+def run_twoframe(a, dev, flush):
+    """fwarp_using_two_frames (a4): SURVEY.md 8d traffic 4*(2(C+3)+C+1) B/px."""
+    H, W = 1080 >> a.level, 1920 >> a.level
+    C, B = a.C or 64, a.pairs
+    g = torch.Generator().manual_seed(wl.seed_for(2, 500 + a.level * 10 + C))
+    in1, in2 = torch.rand(B, C, H, W, generator=g).to(dev), torch.rand(B, C, H, W, generator=g).to(dev)
+    m1, m2 = torch.randn(B, 1, H, W, generator=g).to(dev), torch.randn(B, 1, H, W, generator=g).to(dev)
+    f1 = wl.make_flow(B, H, W, 8.0 / (1 << a.level), g, kind=a.flow, device=dev)
+    f2 = wl.make_flow(B, H, W, 8.0 / (1 << a.level), g, kind=a.flow, device=dev)
+    t = torch.full((B, 1, 1, 1), 0.5, device=dev)
+    ms, best = timeit(lambda: v.fwarp_using_two_frames(in1, f1, t, in2, f2, 1 - t, m1, m2), a.iters, flush)
+    report("twoframe", dict(level=a.level, B=B, C=C, H=H, W=W, flow=a.flow, algo=os.environ.get("VFI_SPLAT_ALGO", "auto")), ms, best,
+           4 * (2 * (C + 3) + C + 1) * B * H * W)
+
+
 def run_dcn(a, dev, flush):
     B, C, H, W = a.pairs if a.pairs > 1 else 32, a.C or 64, 256, 256
     OG = WG = 8
@@ -131,7 +146,7 @@ def run_dcn(a, dev, flush):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--op", default="all", choices=["dattn", "bwarp", "splat", "dcn", "all"])
+    ap.add_argument("--op", default="all", choices=["dattn", "bwarp", "splat", "twoframe", "dcn", "all"])
     ap.add_argument("--level", type=int, default=None)
     ap.add_argument("--C", type=int, default=None)
     ap.add_argument("--pairs", type=int, default=1)
@@ -159,6 +174,8 @@ def main():
                 a.level, a.C = lv0, C
                 run_splat(a, dev, flush)
             a.C = None
+        if a.op == "twoframe":
+            run_twoframe(a, dev, flush)
         if a.op in ("dcn", "all"):
             run_dcn(a, dev, flush)
 

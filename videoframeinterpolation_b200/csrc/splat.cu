@@ -102,14 +102,17 @@ __global__ void __launch_bounds__(256) splat_normalize_kernel(const float* __res
     }
 }
 
+int launch_splat_gather(const float* in, const float* flow, const float* metric, const float* t, float* out, float* den_io, int B, int C,
+                        int H, int W, int weight_mode, int normalize, int eps_mode, float eps_value, int acc_mode, void* workspace,
+                        cudaStream_t st);
+bool splat_gather_applicable(int B, int C, int H, int W, const void* workspace, size_t workspace_bytes);
+
 }  // namespace vfi
 
 extern "C" int vfi_splat_f32(const float* in, const float* flow, const float* metric, const float* t, float* num,
                              float* den, int B, int C, int H, int W, int weight_mode, int accumulate, void* workspace,
                              size_t workspace_bytes, void* stream) {
     using namespace vfi;
-    (void)workspace;
-    (void)workspace_bytes;
     if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(in && flow && num, "vfi_splat_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 0 && H >= 1 && W >= 1, "vfi_splat_f32: bad shape");
@@ -121,6 +124,11 @@ extern "C" int vfi_splat_f32(const float* in, const float* flow, const float* me
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (B == 0) return VFI_OK;
     const int64_t HW = (int64_t)H * W;
+    // a workspace selects the gather form (csrc/splat_fused.cu): link pass + one owner thread per target pixel that
+    // stores / adds this source's sums -- no floating-point atomics, no zero fill
+    if (splat_gather_applicable(B, C, H, W, workspace, workspace_bytes))
+        return launch_splat_gather(in, flow, metric, t, num, weight_mode == VFI_SPLAT_W_NONE ? nullptr : den, B, C, H, W, weight_mode, 0,
+                                   VFI_EPS_ADD, 0.0f, accumulate ? 1 : 0, workspace, st);
     if (!accumulate) {
         if (C > 0) VFI_CUDA(cudaMemsetAsync(num, 0, sizeof(float) * (size_t)B * C * HW, st));
         if (den) VFI_CUDA(cudaMemsetAsync(den, 0, sizeof(float) * (size_t)B * HW, st));

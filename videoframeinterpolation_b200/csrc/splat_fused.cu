@@ -50,17 +50,19 @@ __device__ __forceinline__ SplatCornersF splat_corners_f(int x, int y, float flo
     return c;
 }
 
-__device__ __forceinline__ float splat_weight_f(int mode, const float* __restrict__ metric, int64_t idx) {
+__device__ __forceinline__ float splat_weight_f(int mode, const float* __restrict__ metric, const float* __restrict__ t, int b,
+                                                int64_t idx) {
     switch (mode) {
         case VFI_SPLAT_W_LINEAR: return ld_stream(metric + idx);
         case VFI_SPLAT_W_SOFT: return expf(ld_stream(metric + idx));
+        case VFI_SPLAT_W_SOFT_CLIP_T: return t[b] * expf(fminf(fmaxf(ld_stream(metric + idx), -20.0f), 20.0f));   // as splat.cu
         default: return 1.0f;
     }
 }
 
 // K1: one thread per source pixel
 __global__ void __launch_bounds__(256) splat_link_kernel(const float* __restrict__ flow, const float* __restrict__ metric,
-                                                         int* __restrict__ slot_src, float* __restrict__ slot_w,
+                                                         const float* __restrict__ t, int* __restrict__ slot_src, float* __restrict__ slot_w,
                                                          int* __restrict__ head, SplatNode* __restrict__ nodes, int B, int H,
                                                          int W, int mode) {
     const int64_t HW = (int64_t)H * W, total = (int64_t)B * HW;
@@ -71,7 +73,7 @@ __global__ void __launch_bounds__(256) splat_link_kernel(const float* __restrict
         const float* fp = flow + (int64_t)b * 2 * HW + pix;
         const SplatCornersF c = splat_corners_f(x, y, ld_stream(fp), ld_stream(fp + HW), H, W);
         if (!c.valid) continue;
-        const float wm = splat_weight_f(mode, metric, idx);
+        const float wm = splat_weight_f(mode, metric, t, b, idx);
         const bool in_x0 = c.x0 >= 0, in_x1 = c.x0 + 1 < W, in_y0 = c.y0 >= 0, in_y1 = c.y0 + 1 < H;
         const int64_t q = (int64_t)b * HW + (int64_t)c.y0 * W + c.x0;     // output pixel of the north-west corner
         const int node0 = (int)(idx * 4);
@@ -106,7 +108,7 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
                                                            const float* __restrict__ slot_w, const int* __restrict__ head,
                                                            const SplatNode* __restrict__ nodes, float* __restrict__ out, int C,
                                                            int H, int W, int c_chunk, int n_chunks, int normalize, int eps_mode,
-                                                           float eps, int lockstep) {
+                                                           float eps, int lockstep, float* __restrict__ den_io, int acc_mode) {
     const int x = blockIdx.x * 32 + threadIdx.x;
     const int y = blockIdx.y * 8 + threadIdx.y;
     const int b = blockIdx.z / n_chunks;
@@ -159,6 +161,10 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
     // one reciprocal per pixel instead of an IEEE division per (pixel, channel): <= 1.5 ulp from the reference's
     // divide, far inside the 1e-4 splat tolerance (the summation order already differs from the atomics')
     const float rdiv = normalize ? __frcp_rn(splat_divisor_f(den, eps_mode, eps)) : 1.0f;
+    // accumulate form (two-frame / multi-branch splat, modules/warp.py:68-114): this source's un-normalised sums are
+    // stored (acc_mode 0) or added (acc_mode 1) to out / den_io.  Every (pixel, plane) has exactly one owner thread,
+    // so the read-modify-write needs no atomic; den_io belongs to the first channel chunk.
+    if (den_io != nullptr && c_begin == 0 && live) den_io[q] = acc_mode ? den_io[q] + den : den;
 
     // byte offsets of the source pixels inside a plane (32-bit: H*W*4 < 2^32); plane bases are block-uniform, so a
     // tap is one IMAD.WIDE.U32 + one predicated LDG + one predicated FFMA
@@ -215,7 +221,10 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
         }
 #pragma unroll
         for (int u = 0; u < kChUnroll; ++u)
-            if (live) st_stream(reinterpret_cast<float*>(obase + (int64_t)(c + u) * plane_bytes + oo), acc[u] * rdiv);
+            if (live) {
+                float* op = reinterpret_cast<float*>(obase + (int64_t)(c + u) * plane_bytes + oo);
+                st_stream(op, acc_mode ? *op + acc[u] * rdiv : acc[u] * rdiv);
+            }
     }
     for (; c < n_c; ++c) {
         const char* pl = ibase + (int64_t)c * plane_bytes;
@@ -228,7 +237,10 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
             acc = fmaf(tap(pl, (unsigned)(((int64_t)nd - base4) >> 2)), __int_as_float(e.y), acc);
             nd = e.x;
         }
-        if (live) st_stream(reinterpret_cast<float*>(obase + (int64_t)c * plane_bytes + oo), acc * rdiv);
+        if (live) {
+            float* op = reinterpret_cast<float*>(obase + (int64_t)c * plane_bytes + oo);
+            st_stream(op, acc_mode ? *op + acc * rdiv : acc * rdiv);
+        }
     }
 }
 
@@ -240,6 +252,50 @@ extern "C" size_t vfi_splat_workspace_bytes(int B, int C, int H, int W) {
     const size_t px = (size_t)B * H * W;
     return px * 4 * (sizeof(int) + sizeof(float)) + px * sizeof(int) + px * 4 * sizeof(vfi::SplatNode) + 256;
 }
+
+namespace vfi {
+
+// link + gather for one source; shared by vfi_splat_fused_f32 (normalised, one source) and vfi_splat_f32's gather route
+// (un-normalised sums stored or accumulated into num / den)
+int launch_splat_gather(const float* in, const float* flow, const float* metric, const float* t, float* out, float* den_io, int B, int C,
+                        int H, int W, int weight_mode, int normalize, int eps_mode, float eps_value, int acc_mode, void* workspace,
+                        cudaStream_t st) {
+    const int64_t px = (int64_t)B * H * W;
+    // layout: slot_src[4 px] | head[px] (one memset of 0xFF covers both) | slot_w[4 px] | nodes[4 px]
+    int* slot_src = reinterpret_cast<int*>(workspace);
+    int* head = slot_src + px * 4;
+    float* slot_w = reinterpret_cast<float*>(head + ((px + 3) & ~3ll));
+    SplatNode* nodes = reinterpret_cast<SplatNode*>(slot_w + px * 4);
+    VFI_CUDA(cudaMemsetAsync(slot_src, 0xFF, (size_t)px * 5 * sizeof(int), st));
+    {
+        const int blocks = (int)min64(ceil_div(px, 256), (int64_t)kNumSMs * 16);
+        splat_link_kernel<<<blocks, 256, 0, st>>>(flow, metric, t, slot_src, slot_w, head, nodes, B, H, W, weight_mode);
+        VFI_CHECK_LAUNCH("splat_link_kernel");
+    }
+    const int64_t tiles = ceil_div(W, 32) * ceil_div(H, 8) * B;
+    int n_chunks = 1;
+    while (tiles * n_chunks < (int64_t)kNumSMs * 16 && ceil_div(C, n_chunks * 2) >= 16) n_chunks *= 2;
+    int c_chunk = (int)ceil_div(C, n_chunks);
+    c_chunk = (int)ceil_div(c_chunk, kChUnroll) * kChUnroll;
+    n_chunks = (int)ceil_div(C, c_chunk);
+    VFI_REQUIRE((int64_t)B * n_chunks <= 65535 && ceil_div(H, 8) <= 65535, "splat (gather form): grid too large");
+    dim3 grid((unsigned)ceil_div(W, 32), (unsigned)ceil_div(H, 8), (unsigned)(B * n_chunks));
+    int lockstep = 1;
+    if (const char* e = getenv("VFI_SPLAT_LOCKSTEP")) lockstep = atoi(e);
+    splat_gather_kernel<<<grid, dim3(32, 8), 0, st>>>(in, slot_src, slot_w, head, nodes, out, C, H, W, c_chunk, n_chunks, normalize,
+                                                      eps_mode, eps_value, lockstep, den_io, acc_mode);
+    VFI_CHECK_LAUNCH("splat_gather_kernel");
+    return VFI_OK;
+}
+
+// gather route of vfi_splat_f32: 0 = not applicable (caller scatters), else done / error
+bool splat_gather_applicable(int B, int C, int H, int W, const void* workspace, size_t workspace_bytes) {
+    const int64_t px = (int64_t)B * H * W;
+    return workspace != nullptr && C >= 1 && px * 4 < (1ll << 31) && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0 &&
+           workspace_bytes >= vfi_splat_workspace_bytes(B, C, H, W);
+}
+
+}  // namespace vfi
 
 extern "C" int vfi_splat_fused_f32(const float* in, const float* flow, const float* metric, float* out, int B, int C, int H, int W,
                                    int weight_mode, int eps_mode, float eps_value, void* workspace, size_t workspace_bytes,
@@ -258,30 +314,6 @@ extern "C" int vfi_splat_fused_f32(const float* in, const float* flow, const flo
     VFI_REQUIRE(workspace && workspace_bytes >= vfi_splat_workspace_bytes(B, C, H, W), "vfi_splat_fused_f32: workspace of %zu B needed",
                 vfi_splat_workspace_bytes(B, C, H, W));
     VFI_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "vfi_splat_fused_f32: workspace must be 16-byte aligned");
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    // layout: slot_src[4 px] | head[px] (one memset of 0xFF covers both) | slot_w[4 px] | nodes[4 px]
-    int* slot_src = reinterpret_cast<int*>(workspace);
-    int* head = slot_src + px * 4;
-    float* slot_w = reinterpret_cast<float*>(head + ((px + 3) & ~3ll));
-    SplatNode* nodes = reinterpret_cast<SplatNode*>(slot_w + px * 4);
-    VFI_CUDA(cudaMemsetAsync(slot_src, 0xFF, (size_t)px * 5 * sizeof(int), st));
-    {
-        const int blocks = (int)min64(ceil_div(px, 256), (int64_t)kNumSMs * 16);
-        splat_link_kernel<<<blocks, 256, 0, st>>>(flow, metric, slot_src, slot_w, head, nodes, B, H, W, weight_mode);
-        VFI_CHECK_LAUNCH("splat_link_kernel");
-    }
-    const int64_t tiles = ceil_div(W, 32) * ceil_div(H, 8) * B;
-    int n_chunks = 1;
-    while (tiles * n_chunks < (int64_t)kNumSMs * 16 && ceil_div(C, n_chunks * 2) >= 16) n_chunks *= 2;
-    int c_chunk = (int)ceil_div(C, n_chunks);
-    c_chunk = (int)ceil_div(c_chunk, kChUnroll) * kChUnroll;
-    n_chunks = (int)ceil_div(C, c_chunk);
-    VFI_REQUIRE((int64_t)B * n_chunks <= 65535 && ceil_div(H, 8) <= 65535, "vfi_splat_fused_f32: grid too large");
-    dim3 grid((unsigned)ceil_div(W, 32), (unsigned)ceil_div(H, 8), (unsigned)(B * n_chunks));
-    int lockstep = 1;
-    if (const char* e = getenv("VFI_SPLAT_LOCKSTEP")) lockstep = atoi(e);
-    splat_gather_kernel<<<grid, dim3(32, 8), 0, st>>>(in, slot_src, slot_w, head, nodes, out, C, H, W, c_chunk, n_chunks,
-                                                      weight_mode == VFI_SPLAT_W_NONE ? 0 : 1, eps_mode, eps_value, lockstep);
-    VFI_CHECK_LAUNCH("splat_gather_kernel");
-    return VFI_OK;
+    return launch_splat_gather(in, flow, metric, nullptr, out, nullptr, B, C, H, W, weight_mode, weight_mode == VFI_SPLAT_W_NONE ? 0 : 1,
+                               eps_mode, eps_value, 0, workspace, static_cast<cudaStream_t>(stream));
 }

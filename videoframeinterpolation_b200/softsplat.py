@@ -31,9 +31,12 @@ def splat_accumulate(tenIn, tenFlow, tenMetric, t, num, den, weight: str, accumu
     assert tuple(tenFlow.shape) == (B, 2, H, W), "flow must be (B,2,H,W)"
     assert tenMetric is None or tuple(tenMetric.shape) == (B, 1, H, W), "metric must be (B,1,H,W)"
     assert num.is_contiguous() and (den is None or den.is_contiguous())
+    # a workspace selects the gather form (no floating-point atomics); below ~8 channels the scatter kernel is cheaper
+    ws = _workspace(dev, int(_lib.lib().vfi_splat_workspace_bytes(B, C, H, W))) if _fused_ok(B, C, H, W) else None
     _lib.call("vfi_splat_f32", dev, tenIn.data_ptr(), tenFlow.data_ptr(), _lib.ptr(tenMetric), _lib.ptr(t),
                                         num.data_ptr(), _lib.ptr(den), B, C, H, W, _WEIGHT_MODES[weight],
-                                        1 if accumulate else 0, None, 0, _lib.stream_ptr(dev))
+                                        1 if accumulate else 0, _lib.ptr(ws), ws.numel() if ws is not None else 0,
+                                        _lib.stream_ptr(dev))
 
 
 def splat_normalize(num, den, eps_mode: str, eps_value: float, want_mask: bool = False,
