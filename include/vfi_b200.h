@@ -94,6 +94,14 @@ int vfi_splat_normalize_f32(const float* num, const float* den, float* out, uint
                             int B, int C, int H, int W, int eps_mode, float eps_value, float blank_threshold,
                             void* stream);
 
+/* Last source of an accumulate sequence, gather route only (modules/warp.py:76-83, 106-114 in one pass less):
+ *   num_out = (num_out + splat(in * w)) / f(den + splat(w)),  blank_mask = f(.) < blank_threshold (optional)
+ * den (the sum of the earlier sources' weights) is read, not updated.  Needs the workspace of vfi_splat_workspace_bytes;
+ * VFI_UNSUPPORTED otherwise (callers then use vfi_splat_f32(accumulate) + vfi_splat_normalize_f32). */
+int vfi_splat_last_f32(const float* in, const float* flow, const float* metric, const float* t, float* num_out, const float* den,
+                       uint8_t* blank_mask, int B, int C, int H, int W, int weight_mode, int eps_mode, float eps_value,
+                       float blank_threshold, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Fused single-call form of softsplat(tenIn, tenFlow, tenMetric, strMode) for sum/avg/linear/soft in GATHER form:
  * a link pass records, per target pixel, which source pixels hit it (integer CAS / exchange only), then one thread
  * per target pixel sums its sources for every plane and divides in the same pass -- no floating-point atomics,

@@ -29,6 +29,7 @@ SIGNATURES = {
     "vfi_splat_f32": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "vfi_splat_workspace_bytes": (c_size_t, [c_int] * 4),
     "vfi_splat_normalize_f32": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_int, c_float, c_float, c_void_p]),
+    "vfi_splat_last_f32": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_int, c_int, c_float, c_float, c_void_p, c_size_t, c_void_p]),
     "vfi_splat_fused_f32": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_int, c_int, c_float, c_void_p, c_size_t, c_void_p]),
     "vfi_dsample_f32": (c_int, [c_void_p] * 6 + [c_int] * 6 + [c_void_p]),
     "vfi_attn_f32": (c_int, [c_void_p] * 11 + [c_int] * 6 + [c_void_p]),

@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(256) splat_normalize_kernel(const float* __res
 
 int launch_splat_gather(const float* in, const float* flow, const float* metric, const float* t, float* out, float* den_io, int B, int C,
                         int H, int W, int weight_mode, int normalize, int eps_mode, float eps_value, int acc_mode, void* workspace,
-                        cudaStream_t st);
+                        cudaStream_t st, uint8_t* blank, float blank_thr);
 bool splat_gather_applicable(int B, int C, int H, int W, const void* workspace, size_t workspace_bytes);
 
 }  // namespace vfi
@@ -128,7 +128,7 @@ extern "C" int vfi_splat_f32(const float* in, const float* flow, const float* me
     // stores / adds this source's sums -- no floating-point atomics, no zero fill
     if (splat_gather_applicable(B, C, H, W, workspace, workspace_bytes))
         return launch_splat_gather(in, flow, metric, t, num, weight_mode == VFI_SPLAT_W_NONE ? nullptr : den, B, C, H, W, weight_mode, 0,
-                                   VFI_EPS_ADD, 0.0f, accumulate ? 1 : 0, workspace, st);
+                                   VFI_EPS_ADD, 0.0f, accumulate ? 1 : 0, workspace, st, nullptr, 0.0f);
     if (!accumulate) {
         if (C > 0) VFI_CUDA(cudaMemsetAsync(num, 0, sizeof(float) * (size_t)B * C * HW, st));
         if (den) VFI_CUDA(cudaMemsetAsync(den, 0, sizeof(float) * (size_t)B * HW, st));

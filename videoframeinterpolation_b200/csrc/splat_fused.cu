@@ -108,7 +108,8 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
                                                            const float* __restrict__ slot_w, const int* __restrict__ head,
                                                            const SplatNode* __restrict__ nodes, float* __restrict__ out, int C,
                                                            int H, int W, int c_chunk, int n_chunks, int normalize, int eps_mode,
-                                                           float eps, int lockstep, float* __restrict__ den_io, int acc_mode) {
+                                                           float eps, int lockstep, float* __restrict__ den_io, int acc_mode,
+                                                           uint8_t* __restrict__ blank, float blank_thr) {
     const int x = blockIdx.x * 32 + threadIdx.x;
     const int y = blockIdx.y * 8 + threadIdx.y;
     const int b = blockIdx.z / n_chunks;
@@ -160,11 +161,15 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
     }
     // one reciprocal per pixel instead of an IEEE division per (pixel, channel): <= 1.5 ulp from the reference's
     // divide, far inside the 1e-4 splat tolerance (the summation order already differs from the atomics')
-    const float rdiv = normalize ? __frcp_rn(splat_divisor_f(den, eps_mode, eps)) : 1.0f;
     // accumulate form (two-frame / multi-branch splat, modules/warp.py:68-114): this source's un-normalised sums are
-    // stored (acc_mode 0) or added (acc_mode 1) to out / den_io.  Every (pixel, plane) has exactly one owner thread,
-    // so the read-modify-write needs no atomic; den_io belongs to the first channel chunk.
-    if (den_io != nullptr && c_begin == 0 && live) den_io[q] = acc_mode ? den_io[q] + den : den;
+    // stored (acc_mode 0) or added (acc_mode 1) to out / den_io; acc_mode 2 = last source: added, then divided by the
+    // total weight in the same pass (den_io is only read).  Every (pixel, plane) has exactly one owner thread, so the
+    // read-modify-write needs no atomic; den_io and the blank mask belong to the first channel chunk.
+    const float den_fin = acc_mode == 2 ? den_io[q] + den : den;
+    const float dv = splat_divisor_f(den_fin, eps_mode, eps);
+    const float rdiv = normalize ? __frcp_rn(dv) : 1.0f;
+    if (den_io != nullptr && c_begin == 0 && live && acc_mode != 2) den_io[q] = acc_mode ? den_io[q] + den : den;
+    if (blank != nullptr && c_begin == 0 && live) blank[q] = dv < blank_thr ? 1 : 0;
 
     // byte offsets of the source pixels inside a plane (32-bit: H*W*4 < 2^32); plane bases are block-uniform, so a
     // tap is one IMAD.WIDE.U32 + one predicated LDG + one predicated FFMA
@@ -223,7 +228,7 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
         for (int u = 0; u < kChUnroll; ++u)
             if (live) {
                 float* op = reinterpret_cast<float*>(obase + (int64_t)(c + u) * plane_bytes + oo);
-                st_stream(op, acc_mode ? *op + acc[u] * rdiv : acc[u] * rdiv);
+                st_stream(op, acc_mode == 2 ? (*op + acc[u]) * rdiv : (acc_mode ? *op + acc[u] * rdiv : acc[u] * rdiv));
             }
     }
     for (; c < n_c; ++c) {
@@ -239,7 +244,7 @@ __global__ void __launch_bounds__(256) splat_gather_kernel(const float* __restri
         }
         if (live) {
             float* op = reinterpret_cast<float*>(obase + (int64_t)c * plane_bytes + oo);
-            st_stream(op, acc_mode ? *op + acc * rdiv : acc * rdiv);
+            st_stream(op, acc_mode == 2 ? (*op + acc) * rdiv : (acc_mode ? *op + acc * rdiv : acc * rdiv));
         }
     }
 }
@@ -259,7 +264,7 @@ namespace vfi {
 // (un-normalised sums stored or accumulated into num / den)
 int launch_splat_gather(const float* in, const float* flow, const float* metric, const float* t, float* out, float* den_io, int B, int C,
                         int H, int W, int weight_mode, int normalize, int eps_mode, float eps_value, int acc_mode, void* workspace,
-                        cudaStream_t st) {
+                        cudaStream_t st, uint8_t* blank, float blank_thr) {
     const int64_t px = (int64_t)B * H * W;
     // layout: slot_src[4 px] | head[px] (one memset of 0xFF covers both) | slot_w[4 px] | nodes[4 px]
     int* slot_src = reinterpret_cast<int*>(workspace);
@@ -283,7 +288,7 @@ int launch_splat_gather(const float* in, const float* flow, const float* metric,
     int lockstep = 1;
     if (const char* e = getenv("VFI_SPLAT_LOCKSTEP")) lockstep = atoi(e);
     splat_gather_kernel<<<grid, dim3(32, 8), 0, st>>>(in, slot_src, slot_w, head, nodes, out, C, H, W, c_chunk, n_chunks, normalize,
-                                                      eps_mode, eps_value, lockstep, den_io, acc_mode);
+                                                      eps_mode, eps_value, lockstep, den_io, acc_mode, blank, blank_thr);
     VFI_CHECK_LAUNCH("splat_gather_kernel");
     return VFI_OK;
 }
@@ -315,5 +320,23 @@ extern "C" int vfi_splat_fused_f32(const float* in, const float* flow, const flo
                 vfi_splat_workspace_bytes(B, C, H, W));
     VFI_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "vfi_splat_fused_f32: workspace must be 16-byte aligned");
     return launch_splat_gather(in, flow, metric, nullptr, out, nullptr, B, C, H, W, weight_mode, weight_mode == VFI_SPLAT_W_NONE ? 0 : 1,
-                               eps_mode, eps_value, 0, workspace, static_cast<cudaStream_t>(stream));
+                               eps_mode, eps_value, 0, workspace, static_cast<cudaStream_t>(stream), nullptr, 0.0f);
+}
+
+extern "C" int vfi_splat_last_f32(const float* in, const float* flow, const float* metric, const float* t, float* num_out, const float* den,
+                                  uint8_t* blank_mask, int B, int C, int H, int W, int weight_mode, int eps_mode, float eps_value,
+                                  float blank_threshold, void* workspace, size_t workspace_bytes, void* stream) {
+    using namespace vfi;
+    if (B == 0) return VFI_OK;
+    VFI_REQUIRE(in && flow && num_out && den, "vfi_splat_last_f32: null pointer");
+    VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1, "vfi_splat_last_f32: bad shape");
+    VFI_REQUIRE(weight_mode >= VFI_SPLAT_W_ONES && weight_mode <= VFI_SPLAT_W_SOFT_CLIP_T, "vfi_splat_last_f32: bad weight_mode %d", weight_mode);
+    VFI_REQUIRE(eps_mode >= VFI_EPS_ADD && eps_mode <= VFI_EPS_CLIP, "vfi_splat_last_f32: bad eps_mode %d", eps_mode);
+    if (weight_mode >= VFI_SPLAT_W_LINEAR) VFI_REQUIRE(metric != nullptr, "vfi_splat_last_f32: weight mode %d needs a metric", weight_mode);
+    if (weight_mode == VFI_SPLAT_W_SOFT_CLIP_T) VFI_REQUIRE(t != nullptr, "vfi_splat_last_f32: SOFT_CLIP_T needs t");
+    if (!splat_gather_applicable(B, C, H, W, workspace, workspace_bytes))
+        VFI_UNSUPPORTED("vfi_splat_last_f32: needs a 16-byte aligned workspace of %zu B and B*H*W < 2^29 (else vfi_splat_f32 + vfi_splat_normalize_f32)",
+                        vfi_splat_workspace_bytes(B, C, H, W));
+    return launch_splat_gather(in, flow, metric, t, num_out, const_cast<float*>(den), B, C, H, W, weight_mode, 1, eps_mode, eps_value, 2,
+                               workspace, static_cast<cudaStream_t>(stream), blank_mask, blank_threshold);
 }

@@ -33,7 +33,7 @@ def splat_accumulate(tenIn, tenFlow, tenMetric, t, num, den, weight: str, accumu
     assert num.is_contiguous() and (den is None or den.is_contiguous())
     # a workspace selects the gather form (no floating-point atomics).  Its sums are read-modify-written once per
     # source, so the crossover is higher than for the one-call splat: measured at 1080p, two sources: C = 16 0.62 vs
-    # 0.60 ms (scatter), C = 64 1.51 vs 2.28 ms
+    # 0.60 ms (scatter), C = 64 1.24 vs 2.27 ms
     ws = _workspace(dev, int(_lib.lib().vfi_splat_workspace_bytes(B, C, H, W))) if _fused_ok(B, C, H, W, min_c=32) else None
     _lib.call("vfi_splat_f32", dev, tenIn.data_ptr(), tenFlow.data_ptr(), _lib.ptr(tenMetric), _lib.ptr(t),
                                         num.data_ptr(), _lib.ptr(den), B, C, H, W, _WEIGHT_MODES[weight],
@@ -53,6 +53,23 @@ def splat_normalize(num, den, eps_mode: str, eps_value: float, want_mask: bool =
     if want_mask:
         return num, mask.view(torch.bool)
     return num
+
+
+def splat_last(tenIn, tenFlow, tenMetric, t, num, den, weight: str, eps_mode: str, eps_value: float, blank_threshold: float):
+    """Last source of an accumulate sequence on the gather route (vfi_splat_last_f32): adds this source and divides by
+    the total weight in the same pass.  Returns (num normalised in place, bool mask), or None when the gather route does
+    not apply to this shape (the caller then accumulates and calls ``splat_normalize``)."""
+    B, C, H, W = tenIn.shape
+    if not _fused_ok(B, C, H, W, min_c=32):
+        return None
+    dev = _lib.require_cuda(tenIn, tenFlow, tenMetric, num, den)
+    tenIn, tenFlow, tenMetric, t = _lib.f32c(tenIn), _lib.f32c(tenFlow), _lib.f32c(tenMetric), _lib.f32c(t)
+    ws = _workspace(dev, int(_lib.lib().vfi_splat_workspace_bytes(B, C, H, W)))
+    mask = torch.empty((B, 1, H, W), dtype=torch.uint8, device=dev)
+    _lib.call("vfi_splat_last_f32", dev, tenIn.data_ptr(), tenFlow.data_ptr(), _lib.ptr(tenMetric), _lib.ptr(t), num.data_ptr(),
+              den.data_ptr(), mask.data_ptr(), B, C, H, W, _WEIGHT_MODES[weight], _EPS_MODES[eps_mode], eps_value, blank_threshold,
+              ws.data_ptr(), ws.numel(), _lib.stream_ptr(dev))
+    return num, mask.view(torch.bool)
 
 
 _ws_cache = {}

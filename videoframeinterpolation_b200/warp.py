@@ -12,7 +12,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from .softsplat import softsplat, splat_accumulate, splat_normalize
+from .softsplat import softsplat, splat_accumulate, splat_last, splat_normalize
 
 __all__ = ["bwarp", "fwarp", "fwarp_using_two_frames", "fwarp_mframes"]
 
@@ -78,10 +78,18 @@ def fwarp(tenIn: torch.Tensor, tenFlow: torch.Tensor, tenMetric: torch.Tensor, s
     return softsplat(tenIn, tenFlow, tenMetric, strMode)
 
 
-def _two_directions(num, den, tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2, first: bool):
+def _two_directions(num, den, tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2, first: bool, last_eps=None):
+    """Both directions of one branch into num / den.  ``last_eps``: this is the final branch -- the second direction
+    also divides by the total weight + last_eps (vfi_splat_last_f32) and (out, mask) is returned when the gather route
+    applies; None otherwise (the caller normalises)."""
     B = tenIn1.shape[0]
     splat_accumulate(tenIn1, tenFlow1, tenMetric1, t1.reshape(B), num, den, "soft_clip_t", accumulate=not first)
+    if last_eps is not None:
+        done = splat_last(tenIn2, tenFlow2, tenMetric2, t2.reshape(B), num, den, "soft_clip_t", "add", last_eps, 0.00001)
+        if done is not None:
+            return done
     splat_accumulate(tenIn2, tenFlow2, tenMetric2, t2.reshape(B), num, den, "soft_clip_t", accumulate=True)
+    return None
 
 
 def fwarp_using_two_frames(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1=None, tenMetric2=None):
@@ -96,7 +104,10 @@ def fwarp_using_two_frames(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric
     B, C, H, W = tenIn1.shape
     num = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
     den = torch.empty((B, 1, H, W), dtype=torch.float32, device=dev)
-    _two_directions(num, den, tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2, first=True)
+    done = _two_directions(num, den, tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2, first=True,
+                           last_eps=2 * 0.0000001)
+    if done is not None:
+        return done
     return splat_normalize(num, den, "add", 2 * 0.0000001, want_mask=True, blank_threshold=0.00001)
 
 
@@ -108,6 +119,8 @@ def fwarp_mframes(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMet
     num = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
     den = torch.empty((B, 1, H, W), dtype=torch.float32, device=dev)
     for idx in range(n_branch):
-        _two_directions(num, den, tenIn1, tenFlow1[idx], t1[idx], tenIn2, tenFlow2[idx], t2[idx], tenMetric1, tenMetric2,
-                        first=idx == 0)
+        done = _two_directions(num, den, tenIn1, tenFlow1[idx], t1[idx], tenIn2, tenFlow2[idx], t2[idx], tenMetric1, tenMetric2,
+                               first=idx == 0, last_eps=2 * n_branch * 0.0000001 if idx == n_branch - 1 else None)
+        if done is not None:
+            return done
     return splat_normalize(num, den, "add", 2 * n_branch * 0.0000001, want_mask=True, blank_threshold=0.00001)
