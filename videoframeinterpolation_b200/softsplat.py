@@ -32,9 +32,9 @@ def splat_accumulate(tenIn, tenFlow, tenMetric, t, num, den, weight: str, accumu
     assert tenMetric is None or tuple(tenMetric.shape) == (B, 1, H, W), "metric must be (B,1,H,W)"
     assert num.is_contiguous() and (den is None or den.is_contiguous())
     # a workspace selects the gather form (no floating-point atomics).  Its sums are read-modify-written once per
-    # source, so the crossover is higher than for the one-call splat: measured at 1080p, two sources: C = 16 0.62 vs
-    # 0.60 ms (scatter), C = 64 1.24 vs 2.27 ms
-    ws = _workspace(dev, int(_lib.lib().vfi_splat_workspace_bytes(B, C, H, W))) if _fused_ok(B, C, H, W, min_c=32) else None
+    # source, so the crossover is higher than for the one-call splat: measured at 1080p, two sources
+    # (profiles/r2d_op_bench.txt): C = 16 0.55 vs 0.59 ms (scatter), C = 64 1.22 vs 2.23 ms
+    ws = _workspace(dev, int(_lib.lib().vfi_splat_workspace_bytes(B, C, H, W))) if _fused_ok(B, C, H, W, min_c=16) else None
     _lib.call("vfi_splat_f32", dev, tenIn.data_ptr(), tenFlow.data_ptr(), _lib.ptr(tenMetric), _lib.ptr(t),
                                         num.data_ptr(), _lib.ptr(den), B, C, H, W, _WEIGHT_MODES[weight],
                                         1 if accumulate else 0, _lib.ptr(ws), ws.numel() if ws is not None else 0,
@@ -60,7 +60,7 @@ def splat_last(tenIn, tenFlow, tenMetric, t, num, den, weight: str, eps_mode: st
     the total weight in the same pass.  Returns (num normalised in place, bool mask), or None when the gather route does
     not apply to this shape (the caller then accumulates and calls ``splat_normalize``)."""
     B, C, H, W = tenIn.shape
-    if not _fused_ok(B, C, H, W, min_c=32):
+    if not _fused_ok(B, C, H, W, min_c=16):
         return None
     dev = _lib.require_cuda(tenIn, tenFlow, tenMetric, num, den)
     tenIn, tenFlow, tenMetric, t = _lib.f32c(tenIn), _lib.f32c(tenFlow), _lib.f32c(tenMetric), _lib.f32c(t)
