@@ -151,7 +151,11 @@ class DCNCrossDeformableAttentionBlockwFlow(nn.Module):
         if fused_supported(self.in_c, self.n_groups, self.n_heads):
             attended = fused_deformable_attention(q, feat0, feat1, c0.reshape(b, -1, fh, fw), c1.reshape(b, -1, fh, fw), None, None,
                                                   *self.attn._weights(), n_groups=self.n_groups, n_samples=self.n_samples,
-                                                  n_heads=self.n_heads, offset_scale=1.0, coords_final=True)
+                                                  n_heads=self.n_heads, offset_scale=1.0, coords_final=True,
+                                                  # q is planar (GEMMs over planar DCN outputs); the conv stacks and the
+                                                  # MLP GEMMs downstream run channels-last when the features do
+                                                  out_channels_last=feat_t.is_contiguous(memory_format=torch.channels_last)
+                                                  and not feat_t.is_contiguous())
         else:
             attended = self.attn(q, torch.cat((self._get_ref_feats(feat0, c0), self._get_ref_feats(feat1, c1)), dim=2))
         out = self.mlp.forward_residual(attended)

@@ -102,7 +102,8 @@ def fused_supported(channels: int, n_groups: int, n_heads: int) -> bool:
 
 def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torch.Tensor], ft1: Optional[torch.Tensor],
                                wq, bq, wk, bk, wv, bv, n_groups: int, n_samples: int, n_heads: int, offset_scale: float,
-                               coords_final: bool = False, want_scores: bool = False, offs_bias=None):
+                               coords_final: bool = False, want_scores: bool = False, offs_bias=None,
+                               out_channels_last: Optional[bool] = None):
     """Sampler + attention over both frames in one kernel (vfi_dattn_f32).
 
     offs* (b, nG*nS*2, h, w): raw conv_res_offset outputs (``coords_final=False``: the kernel applies
@@ -132,7 +133,8 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
         ft_strides = _lib.strides4(ft0)
     else:
         ft_strides = None
-    if q_cl:
+    out_cl = q_cl if out_channels_last is None else bool(out_channels_last)   # the kernel writes either layout
+    if out_cl:
         out = torch.empty((b, fh, fw, c), dtype=torch.float32, device=dev).permute(0, 3, 1, 2)
     else:
         out = torch.empty((b, c, fh, fw), dtype=torch.float32, device=dev)
@@ -147,7 +149,7 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
                                         _lib.linspace_m11(fw, dev).data_ptr(), _lib.linspace_m11(fh, dev).data_ptr(),
                                         out.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), b, c, fh, fw, n_groups, n_samples, n_heads,
                                         float(offset_scale), 1 if coords_final else 0, _lib.ptr(offs_bias), 1 if offs_cl else 0,
-                                        1 if q_cl else 0, 1 if q_cl else 0, _lib.stream_ptr(dev))
+                                        1 if q_cl else 0, 1 if out_cl else 0, _lib.stream_ptr(dev))
     return (out, s0, s1) if want_scores else out
 
 
