@@ -12,7 +12,15 @@
  *   - all data pointers are DEVICE pointers to fp32 unless said otherwise; strides are in ELEMENTS;
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
  *   - scratch memory is supplied by the caller (`workspace`), sized by the matching *_workspace_bytes;
- *   - safe to capture in a CUDA graph.
+ *   - safe to capture in a CUDA graph;
+ *   - `frame_ext` (vfi_bwarp_f32, vfi_dsample_f32, vfi_dattn_f32, vfi_resize2x_f32): NULL when the
+ *     tensors are whole frames.  For one tile of a spatially split frame (BASELINE configs[4]) it points to four HOST
+ *     ints {Wg, Hg, x0, y0}: the frame is Wg x Hg pixels at this tensor's resolution and the (H, W) tensors are the
+ *     crop whose top-left pixel is (x0, y0).  lin_x / lin_y are then the slices [x0, x0+W) / [y0, y0+H) of the frame's
+ *     linspace vectors, and normalisation, border clamp and zero padding are the FRAME's: a crop samples exactly where
+ *     the whole frame would (modules/warp.py:9-14, modules/deformable_attn.py:91-99 on the whole frame).  Taps the
+ *     crop does not hold are clamped to the crop (bwarp) or read as zero (samplers): the caller's halo must cover them.
+ *     vfi_dcn_f32 needs no such argument: torchvision's offsets are absolute pixels, nothing is normalised by the frame.
  */
 #ifndef VFI_B200_H_
 #define VFI_B200_H_
@@ -24,7 +32,7 @@
 extern "C" {
 #endif
 
-#define VFI_B200_VERSION 100 /* major*10000 + minor*100 + patch */
+#define VFI_B200_VERSION 200 /* major*10000 + minor*100 + patch */
 
 typedef enum vfi_status {
     VFI_OK = 0,
@@ -66,7 +74,7 @@ int vfi_device_supported(void);
 int vfi_bwarp_f32(const float* img, const float* flow, const float* lin_x, const float* lin_y, float* out,
                   int B, int C, int H, int W,
                   const int64_t img_strides[4], const int64_t flow_strides[4], const int64_t out_strides[4],
-                  void* stream);
+                  const int* frame_ext, void* stream);
 
 /* ---- a2-a5: forward splatting -- modules/softsplat.py:237-360, modules/warp.py:18-114 -------------
  * One call = pre-scale (weight mode) + summation splat of `in` (B,C,H,W) and of the weight channel.
@@ -118,7 +126,8 @@ int vfi_splat_fused_f32(const float* in, const float* flow, const float* metric,
  * gy = lin_y[y] + dy / ((H-1)/2), F.grid_sample(align_corners=True, padding_mode='zeros').
  */
 int vfi_dsample_f32(const float* feat, const float* coords, const float* lin_x, const float* lin_y,
-                    float* out, float* grid_out, int B, int C, int H, int W, int nG, int nS, void* stream);
+                    float* out, float* grid_out, int B, int C, int H, int W, int nG, int nS, const int* frame_ext,
+                    void* stream);
 
 /* ---- a9 / a11: Attn.forward(q, kv) on a materialised kv -- modules/deformable_attn.py:26-40, madat.py:86-115
  * q (B,C,H,W) un-projected; kv (B,C,S,H*W); weights (C,C) row-major [out][in], biases (C).
@@ -134,17 +143,23 @@ int vfi_attn_f32(const float* q, const float* kv, const float* Wq, const float* 
  * are already absolute displacements and ft0/ft1 are ignored.  ft0/ft1 (B,2,H,W) with strides ft_strides.
  * offs_bias (nG*nS*2 floats or NULL) is added to the raw offsets first (the bias of conv_res_offset, so the conv can
  * run bias-free); offs_channels_last != 0: offs0/offs1 are laid out (B, H, W, nG*nS*2) as a channels-last conv writes them.
- * q_channels_last / out_channels_last != 0: q is read / out is written as (B, H, W, C) (feat0/feat1 stay planar: they
- * are gathered).
+ * q_channels_last / out_channels_last != 0: q is read / out is written as (B, H, W, C).
+ * feat_channels_last == 0: feat0 / feat1 are planar (B,C,H,W) and every tap is gathered from global memory (csrc/dattn.cu).
+ * feat_channels_last != 0: feat0 / feat1 are (B, H, W, C) as the encoder convolutions write them and the kernel stages,
+ *   per 8x4 pixel tile and frame, the window all samples fall into in shared memory with one TMA box load
+ *   (csrc/dattn_win.cu; the reach of the residual offsets is bounded by offset_scale); covered shapes:
+ *   vfi_dattn_win_covers (C = 72, nG = 8, raw channels-last offsets, nS % 4 == 0, offset_scale <= 16) -- others return
+ *   VFI_ERR_UNSUPPORTED and the caller passes planar features.
  * Requires nG == nH (true for every block the reference instantiates; madat.py:121 asserts it).
  */
+int vfi_dattn_win_covers(int C, int nG, int nS, float offset_scale, int coords_final, int offs_channels_last);
 int vfi_dattn_f32(const float* q, const float* feat0, const float* feat1, const float* offs0, const float* offs1,
                   const float* ft0, const float* ft1, const int64_t ft_strides[4],
                   const float* Wq, const float* bq, const float* Wk, const float* bk, const float* Wv,
                   const float* bv, const float* lin_x, const float* lin_y, float* out, float* score0,
                   float* score1, int B, int C, int H, int W, int nG, int nS, int nH, float offset_scale,
                   int coords_final, const float* offs_bias, int offs_channels_last, int q_channels_last,
-                  int out_channels_last, void* stream);
+                  int out_channels_last, int feat_channels_last, const int* frame_ext, void* stream);
 
 /* ---- a6 / a7: modulated deformable convolution -- torchvision.ops.deform_conv2d semantics
  * (call sites modules/dcnv2.py:60-66, models/archive/DCNDAT.py:71-77).
@@ -242,6 +257,14 @@ int vfi_frame_prep(const void* x0, const void* x1, int is_u8, float* out0, float
                    int Hp, int Wp, int pad_top, int pad_left, void* workspace, size_t workspace_bytes, void* stream);
 int vfi_frame_finish(const float* y, const int64_t y_strides[4], const float* mean, void* out, int out_is_u8, int B, int H,
                      int W, int Hp, int Wp, int pad_top, int pad_left, void* stream);
+
+/* ---- flow upsampling between pyramid levels: out (B,C,2H,2W) contiguous = res + mul * resize(x, 2)
+ * Replaces: BaseModel.resize (models/BaseModel.py:19-22, F.interpolate bilinear / align_corners=True) followed by
+ * `* 2.0` and `conv_res_flow(..) +` at modules/deformable_attn.py:127-131 -- three elementwise passes in one, ATen's
+ * upsample_bilinear2d arithmetic.  x (B,C,H,W) / res (B,C,2H,2W, optional) with element strides.  frame_ext refers
+ * to x's level: align_corners=True makes the source position depend on the frame size (see the conventions above). */
+int vfi_resize2x_f32(const float* x, const int64_t x_strides[4], const float* res, const int64_t res_strides[4], float mul,
+                     float* out, int B, int C, int H, int W, const int* frame_ext, void* stream);
 
 /* Glue of the DCNDAT block in one pass.  Replaces: models/archive/DCNDAT.py:150-157 (_get_ref_coords_mask: chunk,
  * 2*tanh, view, + flow) and :69-70 (offset.permute(0,2,1,3,4).flip(1).contiguous().view, sigmoid(mask)).

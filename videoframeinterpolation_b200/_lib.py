@@ -25,15 +25,16 @@ SIGNATURES = {
     "vfi_version": (c_int, []),
     "vfi_last_error_string": (ctypes.c_char_p, []),
     "vfi_device_supported": (c_int, []),
-    "vfi_bwarp_f32": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p] * 3 + [c_void_p]),
+    "vfi_bwarp_f32": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p] * 3 + [c_void_p, c_void_p]),
     "vfi_splat_f32": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "vfi_splat_workspace_bytes": (c_size_t, [c_int] * 4),
     "vfi_splat_normalize_f32": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_int, c_float, c_float, c_void_p]),
     "vfi_splat_last_f32": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_int, c_int, c_float, c_float, c_void_p, c_size_t, c_void_p]),
     "vfi_splat_fused_f32": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_int, c_int, c_float, c_void_p, c_size_t, c_void_p]),
-    "vfi_dsample_f32": (c_int, [c_void_p] * 6 + [c_int] * 6 + [c_void_p]),
+    "vfi_dsample_f32": (c_int, [c_void_p] * 6 + [c_int] * 6 + [c_void_p, c_void_p]),
     "vfi_attn_f32": (c_int, [c_void_p] * 11 + [c_int] * 6 + [c_void_p]),
-    "vfi_dattn_f32": (c_int, [c_void_p] * 19 + [c_int] * 7 + [c_float, c_int, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "vfi_dattn_f32": (c_int, [c_void_p] * 19 + [c_int] * 7 + [c_float, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "vfi_dattn_win_covers": (c_int, [c_int, c_int, c_int, c_float, c_int, c_int]),
     "vfi_dcn_f32": (c_int, [c_void_p] * 6 + [c_int] * 13 + [c_void_p, c_size_t, c_void_p]),
     "vfi_dcn_workspace_bytes": (c_size_t, [c_int] * 10),
     "vfi_bias_act_f32": (c_int, [c_void_p] * 5 + [c_int] * 6 + [c_void_p]),
@@ -53,6 +54,7 @@ SIGNATURES = {
     "vfi_dcndat_coords_f32": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
     "vfi_frame_metrics_workspace_bytes": (c_size_t, [c_int] * 4),
     "vfi_frame_metrics_f32": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_float, c_void_p, c_size_t, c_void_p]),
+    "vfi_resize2x_f32": (c_int, [c_void_p] * 4 + [c_float, c_void_p] + [c_int] * 4 + [c_void_p, c_void_p]),
     "vfi_launch_count": (c_int64, []),
     "vfi_launch_count_reset": (None, []),
 }
@@ -149,6 +151,46 @@ def linspace_m11(n: int, dev: torch.device) -> torch.Tensor:
         t = torch.linspace(-1.0, 1.0, n).to(dev)
         _lin_cache[key] = t
     return t
+
+
+# ---- tiles of a larger frame (BASELINE configs[4]) ---------------------------------------------------
+# While a crop context is active, every frame-normalised op (bwarp, the samplers, the flow resize) is told the extent
+# of the WHOLE frame and where its tensors sit in it, so a tile samples exactly where the whole frame would.
+_crop: Optional[Tuple[int, int, int, int, int, int]] = None     # (Hg, Wg, y0, x0, Hc, Wc) at full resolution
+_I32x4 = c_int * 4
+
+
+class crop_context:
+    """``with crop_context(Hg, Wg, y0, x0, Hc, Wc): net._generate_frame(crop0, crop1, t, mean_=...)`` -- the tensors of
+    the forward are the (Hc, Wc) crop at (y0, x0) of an (Hg, Wg) frame (all multiples of 16: every pyramid level then
+    has integer extents)."""
+
+    def __init__(self, Hg, Wg, y0, x0, Hc, Wc):
+        for v in (Hg, Wg, y0, x0, Hc, Wc):
+            assert v % 16 == 0, "crop contexts need frame, origin and crop sizes that are multiples of 16"
+        assert 0 <= y0 and y0 + Hc <= Hg and 0 <= x0 and x0 + Wc <= Wg, "crop outside the frame"
+        self.ctx = (Hg, Wg, y0, x0, Hc, Wc)
+
+    def __enter__(self):
+        global _crop
+        self._prev, _crop = _crop, self.ctx
+        return self
+
+    def __exit__(self, *exc):
+        global _crop
+        _crop = self._prev
+        return False
+
+
+def frame_ext(H: int, W: int, dev: torch.device):
+    """-> (frame_ext argument of the C ABI or None, lin_x, lin_y) for an (H, W) tensor of the current forward."""
+    if _crop is None:
+        return None, linspace_m11(W, dev), linspace_m11(H, dev)
+    Hg, Wg, y0, x0, Hc, Wc = _crop
+    s = Hc // H
+    assert s >= 1 and H * s == Hc and W * s == Wc and s in (1, 2, 4, 8, 16), f"({H}, {W}) is not a level of the ({Hc}, {Wc}) crop"
+    ext = _I32x4(Wg // s, Hg // s, x0 // s, y0 // s)
+    return ext, linspace_m11(Wg // s, dev)[x0 // s:x0 // s + W], linspace_m11(Hg // s, dev)[y0 // s:y0 // s + H]
 
 
 def launch_count() -> int:

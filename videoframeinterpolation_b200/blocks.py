@@ -248,3 +248,18 @@ class BasicResPixelShuffleGenerator(nn.Module):
 def resize(x, scale_factor):
     """``BaseModel.resize`` (models/BaseModel.py:19-22)."""
     return F.interpolate(x, scale_factor=scale_factor, recompute_scale_factor=False, mode="bilinear", align_corners=True)
+
+
+def flow_up2_add(res: torch.Tensor, ft: torch.Tensor, mul: float = 2.0) -> torch.Tensor:
+    """``res + mul * resize(ft, scale_factor=2.0)`` (modules/deformable_attn.py:127-131) in one pass (vfi_resize2x_f32);
+    frame-extent aware, so a tile of a larger frame upsamples exactly as the whole frame would."""
+    if not (ft.is_cuda and ft.dtype == torch.float32 and res.dtype == torch.float32 and not torch.is_grad_enabled()):
+        return res + mul * resize(ft, scale_factor=2.0)
+    B, C, H, W = ft.shape
+    assert tuple(res.shape) == (B, C, 2 * H, 2 * W), "flow_up2_add: res must be (B, C, 2H, 2W)"
+    dev = ft.device
+    out = torch.empty((B, C, 2 * H, 2 * W), dtype=torch.float32, device=dev)
+    ext, _, _ = _lib.frame_ext(H, W, dev)
+    _lib.call("vfi_resize2x_f32", dev, ft.data_ptr(), _lib.strides4(ft), res.data_ptr(), _lib.strides4(res), float(mul),
+              out.data_ptr(), B, C, H, W, ext, _lib.stream_ptr(dev))
+    return out

@@ -23,10 +23,14 @@ struct BwarpGeom {
     float w_nw, w_ne, w_sw, w_se;
 };
 
-__device__ __forceinline__ BwarpGeom bwarp_geom(float fx, float fy, float lin_x, float lin_y, int H, int W,
-                                                float half_w, float half_h) {
+// The tensor may be a crop (H x W at fe.x0, fe.y0) of a frame of fe.Wg x fe.Hg pixels (4K tiles): the
+// normalisation and the border clamp are the FRAME's (lin_x / lin_y are slices of the frame's linspace vectors), so a
+// crop samples exactly where the whole frame would; taps the crop does not hold clamp to the crop's edge (the
+// caller's halo has to cover them).
+__device__ __forceinline__ BwarpGeom bwarp_geom(float fx, float fy, float lin_x, float lin_y, int H, int W, const FrameExt& fe) {
     // reference op order: flow / ((W-1)/2) is a true fp32 division (torch CPU), then grid + flow_
-    const float wm1 = (float)(W - 1), hm1 = (float)(H - 1);
+    const float wm1 = (float)(fe.Wg - 1), hm1 = (float)(fe.Hg - 1);
+    const float half_w = (float)((fe.Wg - 1.0) / 2.0), half_h = (float)((fe.Hg - 1.0) / 2.0);
     float ix = replay_coord(lin_x, __fdiv_rn(fx, half_w), wm1);
     float iy = replay_coord(lin_y, __fdiv_rn(fy, half_h), hm1);
     ix = fminf(fmaxf(ix, 0.0f), wm1);  // padding_mode='border'
@@ -35,10 +39,13 @@ __device__ __forceinline__ BwarpGeom bwarp_geom(float fx, float fy, float lin_x,
     const float tx = ix - xf, ty = iy - yf;
     const float ex = 1.0f - tx, ey = 1.0f - ty;
     BwarpGeom g;
-    g.x0 = (int)xf;
-    g.y0 = (int)yf;
-    g.x1 = min(g.x0 + 1, W - 1);  // weight is exactly 0 whenever this clamps
-    g.y1 = min(g.y0 + 1, H - 1);
+    const int x0 = (int)xf, y0 = (int)yf;
+    const int x1 = min(x0 + 1, fe.Wg - 1);  // weight is exactly 0 whenever this clamps
+    const int y1 = min(y0 + 1, fe.Hg - 1);
+    g.x0 = min(max(x0 - fe.x0, 0), W - 1);   // crop coordinates (no-ops on a whole frame)
+    g.x1 = min(max(x1 - fe.x0, 0), W - 1);
+    g.y0 = min(max(y0 - fe.y0, 0), H - 1);
+    g.y1 = min(max(y1 - fe.y0, 0), H - 1);
     g.w_nw = ey * ex;
     g.w_ne = ey * tx;
     g.w_sw = ty * ex;
@@ -56,7 +63,7 @@ __global__ void __launch_bounds__(256) bwarp_planar_kernel(const float* __restri
                                                            const float* __restrict__ lin_x,
                                                            const float* __restrict__ lin_y, float* __restrict__ out,
                                                            int C, int H, int W, int c_chunk, int n_chunks, Str4 si,
-                                                           Str4 sf, Str4 so) {
+                                                           Str4 sf, Str4 so, FrameExt fe) {
     const int x = blockIdx.x * 32 + threadIdx.x;
     const int y = blockIdx.y * 8 + threadIdx.y;
     const int b = blockIdx.z / n_chunks;
@@ -70,8 +77,7 @@ __global__ void __launch_bounds__(256) bwarp_planar_kernel(const float* __restri
 
     const float* fp = flow + b * sf.n + yc * sf.h + xc * sf.w;
     const float fx = ld_stream(fp), fy = ld_stream(fp + sf.c);
-    const float half_w = (float)((W - 1.0) / 2.0), half_h = (float)((H - 1.0) / 2.0);
-    const BwarpGeom g = bwarp_geom(fx, fy, lin_x[xc], lin_y[yc], H, W, half_w, half_h);
+    const BwarpGeom g = bwarp_geom(fx, fy, lin_x[xc], lin_y[yc], H, W, fe);
 
     const int64_t o_nw = g.y0 * si.h + g.x0 * si.w, o_ne = g.y0 * si.h + g.x1 * si.w;
     const int64_t o_sw = g.y1 * si.h + g.x0 * si.w, o_se = g.y1 * si.h + g.x1 * si.w;
@@ -112,10 +118,9 @@ __global__ void __launch_bounds__(256) bwarp_planar_kernel(const float* __restri
 __global__ void __launch_bounds__(256) bwarp_cl_kernel(const float* __restrict__ img, const float* __restrict__ flow,
                                                        const float* __restrict__ lin_x, const float* __restrict__ lin_y,
                                                        float* __restrict__ out, int B, int C, int H, int W, Str4 si,
-                                                       Str4 sf, Str4 so) {
+                                                       Str4 sf, Str4 so, FrameExt fe) {
     const int cv = C >> 2;
     const int64_t total = (int64_t)B * H * W * cv;
-    const float half_w = (float)((W - 1.0) / 2.0), half_h = (float)((H - 1.0) / 2.0);
     for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
         const int c4 = (int)(idx % cv) * 4;
         int64_t p = idx / cv;
@@ -124,7 +129,7 @@ __global__ void __launch_bounds__(256) bwarp_cl_kernel(const float* __restrict__
         const int y = (int)(p % H);
         const int b = (int)(p / H);
         const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
-        const BwarpGeom g = bwarp_geom(__ldg(fp), __ldg(fp + sf.c), lin_x[x], lin_y[y], H, W, half_w, half_h);
+        const BwarpGeom g = bwarp_geom(__ldg(fp), __ldg(fp + sf.c), lin_x[x], lin_y[y], H, W, fe);
         const float* ip = img + b * si.n + c4;
         const float4 a = __ldg(reinterpret_cast<const float4*>(ip + g.y0 * si.h + g.x0 * si.w));
         const float4 bq = __ldg(reinterpret_cast<const float4*>(ip + g.y0 * si.h + g.x1 * si.w));
@@ -185,7 +190,7 @@ __global__ void __launch_bounds__(kTileThreads) bwarp_tile_kernel(const __grid_c
                                                                   const float* __restrict__ img, const float* __restrict__ flow,
                                                                   const float* __restrict__ lin_x, const float* __restrict__ lin_y,
                                                                   float* __restrict__ out, int C, int H, int W, Str4 sf,
-                                                                  int tiles_x, int tiles_y, int n_tiles_all, int c_chunk) {
+                                                                  int tiles_x, int tiles_y, int n_tiles_all, int c_chunk, FrameExt fe) {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     uint8_t* smem_al = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);   // TMA destinations need 128 B alignment
     float* stage = reinterpret_cast<float*>(smem_al);
@@ -251,14 +256,13 @@ __global__ void __launch_bounds__(kTileThreads) bwarp_tile_kernel(const __grid_c
 
     // ---- consumers: geometry of my 4 pixels (x = lane, lane+32; y = warp, warp+8) ----
     TilePix px[4];
-    const float half_w = (float)((W - 1.0) / 2.0), half_h = (float)((H - 1.0) / 2.0);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const int xr = x_t0 + lane + 32 * (k & 1), yr = y_t0 + warp + 8 * (k >> 1);
         const bool valid = xr < W && yr < H;
         const int x = min(xr, W - 1), y = min(yr, H - 1);
         const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
-        const BwarpGeom g = bwarp_geom(ld_stream(fp), ld_stream(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, half_w, half_h);
+        const BwarpGeom g = bwarp_geom(ld_stream(fp), ld_stream(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, fe);
         const int lx0 = g.x0 - rx0, ly0 = g.y0 - ry0, lx1 = g.x1 - rx0, ly1 = g.y1 - ry0;
         const bool inside = lx0 >= 0 && lx1 < kRW && ly0 >= 0 && ly1 < kRH;
         if (valid && !inside) s_outlist[atomicAdd(&s_nout, 1)] = (unsigned short)((yr - y_t0) * kTW + (xr - x_t0));
@@ -300,7 +304,7 @@ __global__ void __launch_bounds__(kTileThreads) bwarp_tile_kernel(const __grid_c
         const int pid = s_outlist[item / n_chunks], c0 = c_begin + (item % n_chunks) * kCh;
         const int x = x_t0 + pid % kTW, y = y_t0 + pid / kTW;
         const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
-        const BwarpGeom g = bwarp_geom(__ldg(fp), __ldg(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, half_w, half_h);
+        const BwarpGeom g = bwarp_geom(__ldg(fp), __ldg(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, fe);
         const int o_nw = g.y0 * W + g.x0, o_ne = g.y0 * W + g.x1, o_sw = g.y1 * W + g.x0, o_se = g.y1 * W + g.x1;
         const float* ip = img + ((int64_t)b * C + c0) * HW;
         float* op = out + ((int64_t)b * C + c0) * HW + (int64_t)y * W + x;
@@ -353,7 +357,7 @@ static int get_img_tmap(const float* img, int BC, int H, int W, const CUtensorMa
 
 extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* lin_x, const float* lin_y, float* out,
                              int B, int C, int H, int W, const int64_t img_strides[4], const int64_t flow_strides[4],
-                             const int64_t out_strides[4], void* stream) {
+                             const int64_t out_strides[4], const int* frame_ext, void* stream) {
     using namespace vfi;
     if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(img && flow && lin_x && lin_y && out, "vfi_bwarp_f32: null pointer");
@@ -364,6 +368,8 @@ extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* l
     const Str4 sf{flow_strides[0], flow_strides[1], flow_strides[2], flow_strides[3]};
     const Str4 so{out_strides[0], out_strides[1], out_strides[2], out_strides[3]};
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const FrameExt fe = frame_ext_of(frame_ext, H, W);
+    VFI_REQUIRE(frame_ext_ok(fe, H, W), "vfi_bwarp_f32: the crop does not lie inside the frame");
 
     auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
     const bool channels_last = si.c == 1 && so.c == 1 && C % 4 == 0 && C > 1 && aligned16(img) && aligned16(out) &&
@@ -372,7 +378,7 @@ extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* l
     if (channels_last) {
         const int64_t total = (int64_t)B * H * W * (C / 4);
         const int blocks = (int)min64(ceil_div(total, 256), (int64_t)kNumSMs * 32);
-        bwarp_cl_kernel<<<blocks, 256, 0, st>>>(img, flow, lin_x, lin_y, out, B, C, H, W, si, sf, so);
+        bwarp_cl_kernel<<<blocks, 256, 0, st>>>(img, flow, lin_x, lin_y, out, B, C, H, W, si, sf, so, fe);
         VFI_CHECK_LAUNCH("bwarp_cl_kernel");
         return VFI_OK;
     }
@@ -393,7 +399,7 @@ extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* l
         if (const char* e = getenv("VFI_BWARP_CCHUNK")) c_chunk = atoi(e) > 0 ? atoi(e) : c_chunk;
         const int n_tiles_all = tiles_x * tiles_y * B, n_cchunks = (int)ceil_div(C, c_chunk);
         bwarp_tile_kernel<<<(unsigned)(n_tiles_all * n_cchunks), kTileThreads, smem, st>>>(*tm, img, flow, lin_x, lin_y, out, C, H, W, sf,
-                                                                                          tiles_x, tiles_y, n_tiles_all, c_chunk);
+                                                                                          tiles_x, tiles_y, n_tiles_all, c_chunk, fe);
         VFI_CHECK_LAUNCH("bwarp_tile_kernel");
         return VFI_OK;
     }
@@ -407,7 +413,7 @@ extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* l
     VFI_REQUIRE((int64_t)B * n_chunks <= 65535, "vfi_bwarp_f32: B*chunks=%lld exceeds grid.z", (long long)B * n_chunks);
     VFI_REQUIRE(ceil_div(H, 8) <= 65535, "vfi_bwarp_f32: H too large");
     dim3 grid((unsigned)ceil_div(W, 32), (unsigned)ceil_div(H, 8), (unsigned)(B * n_chunks));
-    bwarp_planar_kernel<<<grid, dim3(32, 8), 0, st>>>(img, flow, lin_x, lin_y, out, C, H, W, c_chunk, n_chunks, si, sf, so);
+    bwarp_planar_kernel<<<grid, dim3(32, 8), 0, st>>>(img, flow, lin_x, lin_y, out, C, H, W, c_chunk, n_chunks, si, sf, so, fe);
     VFI_CHECK_LAUNCH("bwarp_planar_kernel");
     return VFI_OK;
 }

@@ -11,7 +11,7 @@ namespace vfi {
 __global__ void __launch_bounds__(256) dsample_kernel(const float* __restrict__ feat, const float* __restrict__ coords,
                                                       const float* __restrict__ lin_x, const float* __restrict__ lin_y,
                                                       float* __restrict__ out, float* __restrict__ grid_out, int C, int H, int W,
-                                                      int nG, int nS) {
+                                                      int nG, int nS, FrameExt fe) {
     const int64_t HW = (int64_t)H * W;
     const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= HW) return;
@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(256) dsample_kernel(const float* __restrict__ 
     const int y = (int)(pix / W), x = (int)(pix - (int64_t)y * W);
     const int gc = C / nG;
     const float* cp = coords + (((int64_t)b * nG * nS + gs) * 2) * HW + pix;
-    const TapGeom tg = sampler_geom(ld_stream(cp), ld_stream(cp + HW), lin_x[x], lin_y[y], H, W);
+    const TapGeom tg = sampler_geom(ld_stream(cp), ld_stream(cp + HW), lin_x[x], lin_y[y], H, W, fe);
     if (grid_out != nullptr) {
         float2* gp = reinterpret_cast<float2*>(grid_out) + ((int64_t)b * nG * nS + gs) * HW + pix;
         *gp = make_float2(tg.gx, tg.gy);
@@ -38,17 +38,18 @@ __global__ void __launch_bounds__(256) dsample_kernel(const float* __restrict__ 
 }  // namespace vfi
 
 extern "C" int vfi_dsample_f32(const float* feat, const float* coords, const float* lin_x, const float* lin_y, float* out,
-                               float* grid_out, int B, int C, int H, int W, int nG, int nS, void* stream) {
+                               float* grid_out, int B, int C, int H, int W, int nG, int nS, const int* frame_ext, void* stream) {
     using namespace vfi;
     if (B == 0) return VFI_OK;   // empty batch: nothing to do (an empty torch tensor has a NULL data pointer)
     VFI_REQUIRE(feat && coords && lin_x && lin_y && out, "vfi_dsample_f32: null pointer");
     VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && nG >= 1 && nS >= 1, "vfi_dsample_f32: bad shape");
     VFI_REQUIRE(C % nG == 0, "vfi_dsample_f32: C=%d not divisible by nG=%d", C, nG);
     VFI_REQUIRE((int64_t)nG * nS <= 65535 && B <= 65535, "vfi_dsample_f32: nG*nS or B exceeds grid limits");
-    if (B == 0) return VFI_OK;
+    const FrameExt fe = frame_ext_of(frame_ext, H, W);
+    VFI_REQUIRE(frame_ext_ok(fe, H, W), "vfi_dsample_f32: the crop does not lie inside the frame");
     const int64_t HW = (int64_t)H * W;
     dim3 grid((unsigned)ceil_div(HW, 256), (unsigned)(nG * nS), (unsigned)B);
-    dsample_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(feat, coords, lin_x, lin_y, out, grid_out, C, H, W, nG, nS);
+    dsample_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(feat, coords, lin_x, lin_y, out, grid_out, C, H, W, nG, nS, fe);
     VFI_CHECK_LAUNCH("dsample_kernel");
     return VFI_OK;
 }

@@ -14,22 +14,26 @@ struct TapGeom {
 // F.grid_sample(bilinear, padding_mode='zeros', align_corners=True) on the reference's grid:
 //   gx = lin_x[x] + (dx / (W-1)) / 2    (sic: modules/deformable_attn.py:94)
 //   gy = lin_y[y] + dy / ((H-1)/2)
-__device__ __forceinline__ TapGeom sampler_geom(float dx, float dy, float lin_x, float lin_y, int H, int W) {
+// The tensor may be a crop (H x W at origin fe.x0, fe.y0) of a frame of fe.Wg x fe.Hg pixels: the grid is the
+// FRAME's (lin_x / lin_y are slices of the frame's linspace vectors), so a crop samples exactly where the whole
+// frame would; taps outside the crop read as zero (inside the frame they are data the crop does not hold: the
+// caller's halo has to cover them).
+__device__ __forceinline__ TapGeom sampler_geom(float dx, float dy, float lin_x, float lin_y, int H, int W, const FrameExt& fe) {
     TapGeom g;
-    const float wm1 = (float)(W - 1), hm1 = (float)(H - 1);
-    const float half_h = (float)((H - 1.0) / 2.0);
+    const float wm1 = (float)(fe.Wg - 1), hm1 = (float)(fe.Hg - 1);
+    const float half_h = (float)((fe.Hg - 1.0) / 2.0);
     g.gx = __fadd_rn(lin_x, __fmul_rn(__fdiv_rn(dx, wm1), 0.5f));
     g.gy = __fadd_rn(lin_y, __fdiv_rn(dy, half_h));
     float ix = __fmul_rn(__fmul_rn(__fadd_rn(g.gx, 1.0f), 0.5f), wm1);
     float iy = __fmul_rn(__fmul_rn(__fadd_rn(g.gy, 1.0f), 0.5f), hm1);
     // anything beyond one pixel outside has no in-bounds corner; clamp so the int conversion is defined
     const bool finite = isfinite(ix) && isfinite(iy);
-    ix = fminf(fmaxf(finite ? ix : -2.0f, -2.0f), (float)W + 1.0f);
-    iy = fminf(fmaxf(finite ? iy : -2.0f, -2.0f), (float)H + 1.0f);
+    ix = fminf(fmaxf(finite ? ix : -2.0f, -2.0f), (float)fe.Wg + 1.0f);
+    iy = fminf(fmaxf(finite ? iy : -2.0f, -2.0f), (float)fe.Hg + 1.0f);
     const float xf = floorf(ix), yf = floorf(iy);
     const float tx = ix - xf, ty = iy - yf;
     const float ex = 1.0f - tx, ey = 1.0f - ty;
-    const int x0 = (int)xf, y0 = (int)yf;
+    const int x0 = (int)xf - fe.x0, y0 = (int)yf - fe.y0;      // crop coordinates
     const bool in_x0 = x0 >= 0 && x0 < W, in_x1 = x0 + 1 >= 0 && x0 + 1 < W;
     const bool in_y0 = y0 >= 0 && y0 < H, in_y1 = y0 + 1 >= 0 && y0 + 1 < H;
     g.k_nw = in_x0 && in_y0;

@@ -48,6 +48,21 @@ void note_launch();
         }                                                                                \
     } while (0)
 
+// A tensor that is a crop of a larger frame (4K tiles): frame extent and the crop's origin in it.
+struct FrameExt {
+    int Wg, Hg, x0, y0;
+};
+// frame_ext = {Wg, Hg, x0, y0} (host ints) or NULL: the tensor is the whole frame
+static inline FrameExt frame_ext_of(const int* frame_ext, int H, int W) {
+    FrameExt fe;
+    if (frame_ext) { fe.Wg = frame_ext[0]; fe.Hg = frame_ext[1]; fe.x0 = frame_ext[2]; fe.y0 = frame_ext[3]; }
+    else { fe.Wg = W; fe.Hg = H; fe.x0 = 0; fe.y0 = 0; }
+    return fe;
+}
+static inline bool frame_ext_ok(const FrameExt& fe, int H, int W) {
+    return fe.x0 >= 0 && fe.y0 >= 0 && fe.Wg >= 1 && fe.Hg >= 1 && (int64_t)fe.x0 + W <= fe.Wg && (int64_t)fe.y0 + H <= fe.Hg;
+}
+
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline int64_t min64(int64_t a, int64_t b) { return a < b ? a : b; }
 

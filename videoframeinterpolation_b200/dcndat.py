@@ -27,7 +27,7 @@ import torch.nn as nn
 from . import _lib
 from . import conv as _conv
 from .blocks import (BasicResPixelShuffleGenerator, FeadForward, HalfChannelConv5ResBlock, SameChannelResEncoder,
-                     conv_bias_act, conv_prelu, resize, run_conv_chain)
+                     conv_bias_act, conv_prelu, flow_up2_add, resize, run_conv_chain)
 from .dcnv2 import DeformableConv2d, DeformableConv2dGivenOffset, deform_conv2d
 from .deformable_attn import (Attn, fused_deformable_attention, fused_supported, grouped_sample, movement_feats_pair,
                               movement_split_ok)
@@ -161,8 +161,8 @@ class DCNCrossDeformableAttentionBlockwFlow(nn.Module):
         out = self.mlp.forward_residual(attended)
         if not self.pred_res_flow:
             return out
-        up_ft0 = _conv.conv_transpose_up2(self.conv_res_flow, mv0, out_channels_last=False) + 2.0 * resize(ft0, scale_factor=2.0)
-        up_ft1 = _conv.conv_transpose_up2(self.conv_res_flow, mv1, out_channels_last=False) + 2.0 * resize(ft1, scale_factor=2.0)
+        up_ft0 = flow_up2_add(_conv.conv_transpose_up2(self.conv_res_flow, mv0, out_channels_last=False), ft0)
+        up_ft1 = flow_up2_add(_conv.conv_transpose_up2(self.conv_res_flow, mv1, out_channels_last=False), ft1)
         return out, up_ft0, up_ft1
 
 

@@ -11,6 +11,7 @@ kernels (csrc/dsample.cu, csrc/attn.cu).
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -19,7 +20,7 @@ import torch.nn.functional as F
 
 from . import _lib
 from . import conv as _conv
-from .blocks import FeadForward, HalfChannelConv5ResBlock, conv_bias_act, conv_prelu, resize
+from .blocks import FeadForward, HalfChannelConv5ResBlock, conv_bias_act, conv_prelu, flow_up2_add, resize
 from .warp import bwarp, _bwarp_forward
 
 __all__ = ["Attn", "CrossDeformableAttentionBlockwFlow", "grouped_sample", "attention_over_samples", "fused_deformable_attention"]
@@ -62,10 +63,18 @@ def grouped_sample(feat: torch.Tensor, flow: torch.Tensor, n_groups: int, n_samp
     assert tuple(flow.shape) == (b, n_groups * n_samples, 2, fh, fw), f"flow shape {tuple(flow.shape)}"
     out = torch.empty((b, c, n_samples, fh * fw), dtype=torch.float32, device=dev)
     grid = torch.empty((b, n_groups * n_samples, fh * fw, 2), dtype=torch.float32, device=dev) if want_grid else None
-    _lib.call("vfi_dsample_f32", dev, feat.data_ptr(), flow.data_ptr(), _lib.linspace_m11(fw, dev).data_ptr(),
-                                          _lib.linspace_m11(fh, dev).data_ptr(), out.data_ptr(), _lib.ptr(grid), b, c, fh, fw,
-                                          n_groups, n_samples, _lib.stream_ptr(dev))
+    ext, lin_x, lin_y = _lib.frame_ext(fh, fw, dev)
+    _lib.call("vfi_dsample_f32", dev, feat.data_ptr(), flow.data_ptr(), lin_x.data_ptr(), lin_y.data_ptr(), out.data_ptr(),
+              _lib.ptr(grid), b, c, fh, fw, n_groups, n_samples, ext, _lib.stream_ptr(dev))
     return (out, grid) if want_grid else out
+
+
+def _dense_nhwc(t: torch.Tensor) -> bool:
+    """(B,C,H,W) fp32 view of a dense (B,H,W,C) buffer, 16-byte aligned."""
+    if not (t.dim() == 4 and t.dtype == torch.float32 and t.shape[1] > 1 and t.data_ptr() % 16 == 0):
+        return False
+    B, C, H, W = t.shape
+    return tuple(t.stride()) == (H * W * C, 1, W * C, C)
 
 
 def _w2d(w: torch.Tensor) -> torch.Tensor:
@@ -116,7 +125,6 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
             and q.is_contiguous(memory_format=torch.channels_last))
     if not q_cl:
         q = _lib.f32c(q)
-    feat0, feat1 = _lib.planar(feat0), _lib.planar(feat1)
     # offsets are read in the layout the conv wrote them: channels-last (B,H,W,nG*nS*2) needs no transpose
     offs_cl = (offs0.dim() == 4 and offs0.dtype == torch.float32 and not offs0.is_contiguous()
                and offs0.is_contiguous(memory_format=torch.channels_last)
@@ -126,6 +134,14 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
         offs0, offs1 = _lib.f32c(offs0), _lib.f32c(offs1)
     offs_bias = _lib.f32c(offs_bias)
     b, c, fh, fw = q.shape
+    # features: dense channels-last maps (what the encoder convolutions write) go to the shared-memory window kernel
+    # as they are when it covers the shape; everything else is gathered from planar maps
+    feat_cl = (_dense_nhwc(feat0) and _dense_nhwc(feat1) and not want_scores
+               and os.environ.get("VFI_DATTN_ALGO", "win") != "gather"
+               and bool(_lib.lib().vfi_dattn_win_covers(c, n_groups, n_samples, float(offset_scale), 1 if coords_final else 0,
+                                                        1 if offs_cl else 0)))
+    if not feat_cl:
+        feat0, feat1 = _lib.planar(feat0), _lib.planar(feat1)
     assert offs0.numel() == b * n_groups * n_samples * 2 * fh * fw and offs1.numel() == offs0.numel(), "offset shape"
     if not coords_final:
         ft0, ft1 = _lib.f32(ft0), _lib.f32(ft1)
@@ -142,14 +158,13 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
     if want_scores:
         s0 = torch.empty((b * n_heads, n_samples, fh * fw), dtype=torch.float32, device=dev)
         s1 = torch.empty_like(s0)
+    ext, lin_x, lin_y = _lib.frame_ext(fh, fw, dev)
     _lib.call("vfi_dattn_f32", dev, q.data_ptr(), feat0.data_ptr(), feat1.data_ptr(), offs0.data_ptr(), offs1.data_ptr(),
-                                        _lib.ptr(ft0) if not coords_final else None, _lib.ptr(ft1) if not coords_final else None,
-                                        ft_strides, _w2d(wq).data_ptr(), _lib.f32c(bq).data_ptr(), _w2d(wk).data_ptr(),
-                                        _lib.f32c(bk).data_ptr(), _w2d(wv).data_ptr(), _lib.f32c(bv).data_ptr(),
-                                        _lib.linspace_m11(fw, dev).data_ptr(), _lib.linspace_m11(fh, dev).data_ptr(),
-                                        out.data_ptr(), _lib.ptr(s0), _lib.ptr(s1), b, c, fh, fw, n_groups, n_samples, n_heads,
-                                        float(offset_scale), 1 if coords_final else 0, _lib.ptr(offs_bias), 1 if offs_cl else 0,
-                                        1 if q_cl else 0, 1 if out_cl else 0, _lib.stream_ptr(dev))
+              _lib.ptr(ft0) if not coords_final else None, _lib.ptr(ft1) if not coords_final else None, ft_strides,
+              _w2d(wq).data_ptr(), _lib.f32c(bq).data_ptr(), _w2d(wk).data_ptr(), _lib.f32c(bk).data_ptr(), _w2d(wv).data_ptr(),
+              _lib.f32c(bv).data_ptr(), lin_x.data_ptr(), lin_y.data_ptr(), out.data_ptr(), _lib.ptr(s0), _lib.ptr(s1),
+              b, c, fh, fw, n_groups, n_samples, n_heads, float(offset_scale), 1 if coords_final else 0, _lib.ptr(offs_bias),
+              1 if offs_cl else 0, 1 if q_cl else 0, 1 if out_cl else 0, 1 if feat_cl else 0, ext, _lib.stream_ptr(dev))
     return (out, s0, s1) if want_scores else out
 
 
@@ -300,6 +315,6 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
         out = self.mlp.forward_residual(attended)
         if not self.pred_res_flow:
             return out
-        up_ft0 = _conv.conv_transpose_up2(self.conv_res_flow, mv0, out_channels_last=False) + 2.0 * resize(ft0, scale_factor=2.0)
-        up_ft1 = _conv.conv_transpose_up2(self.conv_res_flow, mv1, out_channels_last=False) + 2.0 * resize(ft1, scale_factor=2.0)
+        up_ft0 = flow_up2_add(_conv.conv_transpose_up2(self.conv_res_flow, mv0, out_channels_last=False), ft0)
+        up_ft1 = flow_up2_add(_conv.conv_transpose_up2(self.conv_res_flow, mv1, out_channels_last=False), ft1)
         return out, up_ft0, up_ft1

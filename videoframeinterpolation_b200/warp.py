@@ -66,10 +66,9 @@ def _bwarp_forward(img: torch.Tensor, flow: torch.Tensor, out: torch.Tensor = No
         out = torch.empty_like(img, memory_format=torch.channels_last)
     else:
         out = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
-    _lib.call("vfi_bwarp_f32", dev, img.data_ptr(), flow.data_ptr(), _lib.linspace_m11(W, dev).data_ptr(),
-                                        _lib.linspace_m11(H, dev).data_ptr(), out.data_ptr(), B, C, H, W,
-                                        _lib.strides4(img), _lib.strides4(flow), _lib.strides4(out),
-                                        _lib.stream_ptr(dev))
+    ext, lin_x, lin_y = _lib.frame_ext(H, W, dev)
+    _lib.call("vfi_bwarp_f32", dev, img.data_ptr(), flow.data_ptr(), lin_x.data_ptr(), lin_y.data_ptr(), out.data_ptr(), B, C, H, W,
+              _lib.strides4(img), _lib.strides4(flow), _lib.strides4(out), ext, _lib.stream_ptr(dev))
     return out
 
 
