@@ -27,7 +27,7 @@ __all__ = [
     "library_ops", "grid_sample_bilinear", "bwarp", "splat_sum", "fwarp", "softsplat",
     "fwarp_using_two_frames", "fwarp_mframes", "deform_conv2d", "dcn_block", "dcn_given_offset",
     "ref_coords", "dsample", "attn", "dat_block", "madat_ref_feats", "madat_attn",
-    "layer_norm_c", "conv3x3_tf32", "tf32_truncate", "tf32_round", "calculate_ssim", "calculate_psnr", "dat_forward", "dcndat_forward", "dcndat_config", "dcndat_block", "dat_config", "dat_param_shapes", "input_pad", "input_unpad", "count_params",
+    "layer_norm_c", "conv3x3_tf32", "tf32_truncate", "tf32_round", "calculate_ssim", "calculate_psnr", "dat_forward", "dcndat_forward", "dcndat_config", "dcndat_block", "dat_config", "dat_param_shapes", "input_pad", "input_unpad", "count_params", "resize",
 ]
 
 _USE_LIBRARY = False
@@ -389,8 +389,13 @@ def _res5(p: _P, x, side: int):
     return _prelu(p, "prelu", x + _conv(p, "conv5", out))
 
 
+def resize(x, scale_factor):
+    """BaseModel.resize (models/BaseModel.py:19-22)."""
+    return F.interpolate(x, scale_factor=scale_factor, recompute_scale_factor=False, mode="bilinear", align_corners=True)
+
+
 def _resize2(x):
-    return F.interpolate(x, scale_factor=2.0, recompute_scale_factor=False, mode="bilinear", align_corners=True)
+    return resize(x, 2.0)
 
 
 def dat_block(p: _P, feat_t, feat0, feat1, ft0, ft1, n_samples, n_groups, n_heads, offset_scale,

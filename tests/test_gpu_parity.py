@@ -72,6 +72,97 @@ def test_bwarp_identity_and_idempotence_1080p(vfi):
     assert_close(out[:, :2], lin, TOL, "bwarp 1080p vs oracle (2 channels)")
 
 
+@pytest.mark.parametrize("algo", ["tile", "gather"])
+@pytest.mark.parametrize("C", [8, 16, 64])
+@pytest.mark.parametrize("kind", ["smooth", "gentle", "iid", "edge"])
+def test_bwarp_tile_and_gather_kernels_vs_oracle(vfi, monkeypatch, algo, C, kind):
+    """Both NCHW kernels of vfi_bwarp_f32 forced by VFI_BWARP_ALGO at a size that really dispatches the TMA tile kernel
+    (H*W >= 64K, W % 4 == 0, C >= 8; the 64x16 tiles are ragged in both directions at 270x480), on the bench's flow
+    kinds WITH their 2 % outliers (taps outside the 96x32 window -> the tile kernel's global-gather tail pass), and on
+    an 'edge' flow whose median shift pushes the window past each frame border (the window origin clamps + the
+    16-byte rounding of the TMA x origin).  Reference: modules/warp.py:7-15 through the oracle."""
+    from videoframeinterpolation_b200.workloads import make_flow
+    monkeypatch.setenv("VFI_BWARP_ALGO", algo)
+    B, H, W = 1, 270, 480
+    gen = torch.Generator().manual_seed(100 + C)
+    img = torch.randn(B, C, H, W, generator=gen)
+    if kind == "edge":
+        flow = make_flow(B, H, W, 1.0, gen, kind="smooth", outlier_frac=0.01)
+        flow[:, 0, :, : W // 2] -= 300.0       # left half samples far left of the frame, right half far right
+        flow[:, 0, :, W // 2:] += 300.0
+        flow[:, 1, : H // 2] -= 200.0          # top half above, bottom half below
+        flow[:, 1, H // 2:] += 200.0
+        flow[:, :, 100:140, 200:280] = make_flow(B, 40, 80, 6.0, gen, kind="iid", outlier_frac=0.0)   # an interior patch
+    else:
+        flow = make_flow(B, H, W, 8.0, gen, kind=kind)
+    if algo == "tile" and kind != "edge":
+        # the out-of-window tail is provably hit: some pixel's displacement differs from every probe of its tile by
+        # more than the window margin (2 % of the pixels have flows uniform in [-W, W])
+        assert float((flow.abs() > 64).float().mean()) > 0.005
+    assert_close(vfi.bwarp(*cu(img, flow)), oracle.bwarp(img, flow), TOL, f"bwarp {algo} kernel C={C} {kind}")
+
+
+@pytest.mark.parametrize("layout", ["nchw_tile", "nchw_gather", "channels_last"])
+def test_bwarp_on_a_crop_samples_like_the_whole_frame(vfi, monkeypatch, layout):
+    """frame_ext (Wg, Hg, x0, y0): bwarp of a crop, told the frame's extent and the crop's origin, equals
+    the crop of bwarp of the whole frame wherever the taps stay inside the crop -- normalisation (modules/warp.py:9-12)
+    and border clamp are the frame's.  Without frame_ext the same call differs (the crop's own W-1 / H-1)."""
+    from videoframeinterpolation_b200 import _lib
+    monkeypatch.setenv("VFI_BWARP_ALGO", "tile" if layout == "nchw_tile" else "gather")
+    Hg, Wg, C = 544, 960, 16
+    y0, x0, Hc, Wc = 128, 320, 288, 512
+    img = det.normal("crop.img", (1, C, Hg, Wg))
+    flow = det.flow_field("crop.flow", 1, Hg, Wg, sigma=5.0, outlier_frac=0.0)
+    whole = oracle.bwarp(img, flow)[:, :, y0:y0 + Hc, x0:x0 + Wc]
+    ci, cf = img[:, :, y0:y0 + Hc, x0:x0 + Wc].contiguous().cuda(), flow[:, :, y0:y0 + Hc, x0:x0 + Wc].contiguous().cuda()
+    if layout == "channels_last":
+        ci = ci.contiguous(memory_format=torch.channels_last)
+    with _lib.crop_context(Hg, Wg, y0, x0, Hc, Wc):
+        out = vfi.bwarp(ci, cf)
+    m = 32       # |flow| < 6 sigma = 30 px: taps of interior pixels stay inside the crop
+    assert_close(out[:, :, m:-m, m:-m], whole[:, :, m:-m, m:-m], TOL, f"bwarp crop vs whole ({layout})")
+    plain = vfi.bwarp(ci, cf)
+    assert rel_err(plain[:, :, m:-m, m:-m], whole[:, :, m:-m, m:-m]) > 1e-4, "the crop's own extent gives a different warp"
+
+
+def test_sampler_on_a_crop_samples_like_the_whole_frame(vfi):
+    """frame_ext for the grouped sampler (modules/deformable_attn.py:88-101 on the whole frame vs on a crop)."""
+    from videoframeinterpolation_b200 import _lib
+    from videoframeinterpolation_b200.deformable_attn import grouped_sample
+    Hg, Wg, C, nG, nS = 96, 160, 16, 4, 3
+    y0, x0, Hc, Wc = 32, 48, 48, 80
+    feat = det.normal("cs.feat", (1, C, Hg, Wg))
+    coords = det.normal("cs.coords", (1, nG * nS, 2, Hg, Wg), std=3.0)
+    with oracle.library_ops():
+        whole = oracle.dsample(feat, coords, nG, nS).view(1, C, nS, Hg, Wg)[..., y0:y0 + Hc, x0:x0 + Wc]
+    with _lib.crop_context(Hg, Wg, y0, x0, Hc, Wc):
+        out = grouped_sample(feat[..., y0:y0 + Hc, x0:x0 + Wc].contiguous().cuda(),
+                             coords[..., y0:y0 + Hc, x0:x0 + Wc].contiguous().cuda(), nG, nS).view(1, C, nS, Hc, Wc)
+    m = 20
+    assert_close(out[..., m:-m, m:-m], whole[..., m:-m, m:-m], TOL, "dsample crop vs whole")
+
+
+def test_flow_resize_matches_interpolate_and_crops(vfi):
+    """vfi_resize2x_f32 = res + 2 * BaseModel.resize(ft, 2) (models/BaseModel.py:19-22, modules/deformable_attn.py:127-131),
+    on a whole frame and on a crop with frame_ext."""
+    from videoframeinterpolation_b200 import _lib
+    from videoframeinterpolation_b200.blocks import flow_up2_add
+    Hg, Wg = 64, 112
+    ft = det.normal("rs.ft", (2, 2, Hg, Wg), std=4.0)
+    res = det.normal("rs.res", (2, 2, 2 * Hg, 2 * Wg))
+    ref = res + 2.0 * oracle.resize(ft, 2.0)
+    with torch.no_grad():
+        assert_close(flow_up2_add(res.cuda(), ft.cuda()), ref, 1e-6, "flow_up2_add")
+        packed = torch.cat((det.normal("rs.pad", (2, 3, Hg, Wg)), ft), 1).cuda()          # ft as a channel slice
+        assert_close(flow_up2_add(res.cuda(), packed[:, 3:5]), ref, 1e-6, "flow_up2_add, strided input")
+        y0, x0, Hc, Wc = 16, 32, 32, 64
+        with _lib.crop_context(16 * Hg, 16 * Wg, 16 * y0, 16 * x0, 16 * Hc, 16 * Wc):     # these tensors are the 1/16 level
+            out = flow_up2_add(res[..., 2 * y0:2 * (y0 + Hc), 2 * x0:2 * (x0 + Wc)].contiguous().cuda(),
+                               ft[..., y0:y0 + Hc, x0:x0 + Wc].contiguous().cuda())
+    crop_ref = ref[..., 2 * y0:2 * (y0 + Hc), 2 * x0:2 * (x0 + Wc)]
+    assert_close(out[..., 2:-2, 2:-2], crop_ref[..., 2:-2, 2:-2], 1e-6, "flow_up2_add on a crop")
+
+
 # ---- splat -------------------------------------------------------------------------------------
 def test_splat_golden(vfi, golden):
     g = golden("splat")

@@ -80,11 +80,14 @@ def run_dattn(a, dev, flush):
     ft1 = wl.make_flow(B, H, W, 8.0 / (1 << lv), g, device=dev)
     ws = [torch.randn(C, C, generator=g).to(dev) * C ** -0.5 if i % 2 == 0 else torch.randn(C, generator=g).to(dev) * 0.1
           for i in range(6)]
+    if a.layout == "cl":     # what the model hands the kernel: channels-last q / features / offsets (window kernel where covered)
+        q, f0, f1, raw0, raw1 = (t.contiguous(memory_format=torch.channels_last) for t in (q, f0, f1, raw0, raw1))
     fn = lambda: fused_deformable_attention(q, f0, f1, raw0, raw1, ft0, ft1, *ws, n_groups=nG, n_samples=nS, n_heads=nG,
                                             offset_scale=scale)
     ms, best = timeit(fn, a.iters, flush)
     flops = 2.0 * B * H * W * (2 * C * C + C * C + 2 * (2 * nS) * nG * (C // nG) * nG + 4 * C * 2 * nS)
-    report("dattn", dict(level=lv, B=B, C=C, H=H, W=W, nG=nG, nS=nS, offsets=a.flow), ms, best, wl.bytes_dattn(B, C, H, W, nG, nS),
+    report("dattn", dict(level=lv, B=B, C=C, H=H, W=W, nG=nG, nS=nS, offsets=a.flow, layout=a.layout,
+                         algo=os.environ.get("VFI_DATTN_ALGO", "win")), ms, best, wl.bytes_dattn(B, C, H, W, nG, nS),
            {"tflops_fp32": round(flops / ms / 1e9, 2)})
 
 
@@ -153,6 +156,7 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--mode", default="soft")
     ap.add_argument("--flow", default="smooth", choices=["smooth", "gentle", "iid"])
+    ap.add_argument("--layout", default="cl", choices=["cl", "planar"], help="dattn: channels-last (model) or planar tensors")
     ap.add_argument("--no-flush", action="store_true")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)

@@ -133,8 +133,12 @@ class DATwConstantnCv1(nn.Module):
     @torch.no_grad()
     def inference_tiled(self, x0, x1, t, grid=(2, 4), halo=64, rank: int = 0, world: int = 1, out=None):
         """Spatially tiled inference (BASELINE configs[4]): every tile+halo crop runs the whole forward with the
-        global rgb mean; interiors are written into ``out``.  ``rank``/``world`` select this process's tiles
-        (no collective: each rank fills its own interiors; gather them however the caller likes)."""
+        global rgb mean and, through ``_lib.crop_context``, the FRAME's extent in every frame-normalised op (bwarp, the
+        samplers, the flow resize: SURVEY.md H5), so a crop samples exactly where the whole frame would and what is
+        left of the tile-vs-whole difference is the receptive field of the conv stacks cut by the halo.  Interiors are
+        written into ``out``.  ``rank``/``world`` select this process's tiles (no collective: each rank fills its own
+        interiors; gather them however the caller likes)."""
+        from . import _lib
         from .shard import tile_plan, tiles_of_rank
         B, _, H, W = x0.shape
         mean_ = torch.cat((x0, x1), dim=2).mean(1, keepdim=True).mean(2, keepdim=True).mean(3, keepdim=True)
@@ -142,7 +146,8 @@ class DATwConstantnCv1(nn.Module):
             out = torch.zeros((B, 3, H, W), dtype=x0.dtype, device=x0.device)
         for tl in tiles_of_rank(tile_plan(H, W, grid, halo), rank, world):
             ys, xs = tl.crop
-            pred = self._generate_frame(x0[:, :, ys, xs].contiguous(), x1[:, :, ys, xs].contiguous(), t, mean_=mean_)
+            with _lib.crop_context(H, W, ys.start, xs.start, ys.stop - ys.start, xs.stop - xs.start):
+                pred = self._generate_frame(x0[:, :, ys, xs].contiguous(), x1[:, :, ys, xs].contiguous(), t, mean_=mean_)
             iy, ix = tl.interior_in_crop
             oy, ox = tl.interior
             out[:, :, oy, ox] = pred[:, :, iy, ix]
