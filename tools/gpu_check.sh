@@ -2,8 +2,8 @@
 # first GPU check of round 2: new parity tests, op timings of the two attention kernels, full suite, bench
 set -u
 mkdir -p gpurun_out
-T=r3a
-timeout -s KILL 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_parity_dat.py -q -m gpu -s > gpurun_out/${T}_newtests.log 2>&1; echo "new tests rc=$?"; tail -25 gpurun_out/${T}_newtests.log
+T=${1:-r3b}
+timeout -s KILL 600 python -m pytest tests/test_gpu_parity_dat.py -q -m gpu -s -k "dattn or dat_block or tiled or full_width" > gpurun_out/${T}_newtests.log 2>&1; echo "new tests rc=$?"; tail -25 gpurun_out/${T}_newtests.log
 for lv in 1 2; do
   timeout -s KILL 200 python tools/op_bench.py --op dattn --level $lv --layout cl >> gpurun_out/${T}_op.log 2>&1
   VFI_DATTN_ALGO=gather timeout -s KILL 200 python tools/op_bench.py --op dattn --level $lv --layout cl >> gpurun_out/${T}_op.log 2>&1
