@@ -34,7 +34,29 @@ struct WinGeom {
     int mx, my;      // window origin = tile origin + floor(median displacement) - (mx, my)
     int row_bytes;   // Ww * REC * 4
     uint32_t box_bytes;
+    float r_wm1, r_half_h;   // RN(1 / (Wg - 1)), RN(1 / ((Hg - 1) / 2)): see div_rn
 };
+
+// x / d, correctly rounded, from r = RN(1 / d): q = RN(x r); e = x - q d (exact in one FMA); RN(q + e r).  Bit-identical to
+// the IEEE division the reference's coordinate arithmetic performs (modules/deformable_attn.py:94-95) -- checked against
+// numpy's float32 division on 2.9e8 operands for the divisors of every pyramid level (and for infinities / NaN the
+// result is non-finite either way, which is all the sampler looks at) -- in 3 instructions instead of ~10 + a branch.
+__device__ __forceinline__ float div_rn(float x, float d, float r) {
+    const float q = __fmul_rn(x, r);
+    const float e = __fmaf_rn(-q, d, x);
+    return __fmaf_rn(e, r, q);
+}
+
+// tanh(x) = 1 - 2 / (exp(2x) + 1) on the SFU (ex2.approx, rcp.approx): absolute error <= 3e-7 (both approximations are
+// good to 2 ulp and the formula is only ill-conditioned where tanh is small), i.e. <= 2.4e-6 px after offset_scale = 8:
+// below what the 1e-5 output tolerance can see.  libdevice's tanhf is the same formula above |x| = 0.55 plus a
+// polynomial branch below it, ~4x the instructions.
+__device__ __forceinline__ float tanh_sfu(float x) {
+    float t, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(x * 2.885390081777927f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(t + 1.0f));
+    return fmaf(-2.0f, r, 1.0f);
+}
 
 constexpr int kWinTW = 8, kWinTH = 4;   // pixel tile of a CTA (lane = pixel)
 
@@ -285,16 +307,22 @@ dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant_
             const int ox = f == 0 ? org[0] : org_f1x, oy = f == 0 ? org[1] : org_f1y;
             const float* offcl = a.offs[f] + ((int64_t)b * HW + pix) * (NG * nS * 2) + (int64_t)g * nS * 2;
             const float* featg = a.feat[f] + (int64_t)b * HW * C + gbase;      // channels-last, my group's aligned base
-            // raw offsets of my group, 2 slots per 128-bit streaming load, two loads in flight (4 slots ahead)
+            // raw offsets of my group: 4 slots (32 B, one sector) per load group, loaded one group (two iterations of the
+            // pair loop) ahead of their use
             float4 od_a = ld_stream4(offcl), od_b = ld_stream4(offcl + 4);
             mbar_wait(wbar, wphase);       // window (tile, f) has landed
             wphase ^= 1;
+            float4 oc_a = od_a, oc_b = od_b;
             for (int s0 = 0; s0 < nS; s0 += 2) {
-                const float4 oc = (s0 & 2) ? od_b : od_a;
-                if (s0 + 4 < nS) {
-                    if (s0 & 2) od_b = ld_stream4(offcl + 2 * (s0 + 4));
-                    else od_a = ld_stream4(offcl + 2 * (s0 + 4));
+                if ((s0 & 2) == 0) {
+                    oc_a = od_a;
+                    oc_b = od_b;
+                    if (s0 + 4 < nS) {
+                        od_a = ld_stream4(offcl + 2 * (s0 + 4));
+                        od_b = ld_stream4(offcl + 2 * (s0 + 4) + 4);
+                    }
                 }
+                const float4 oc = (s0 & 2) ? oc_b : oc_a;
                 float xs[2][GC];
                 float lg[2];
 #pragma unroll
@@ -302,11 +330,11 @@ dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant_
                     // ---- sample my group's channels at slot s0 + si ----
                     const float2 ob = *reinterpret_cast<const float2*>(ob_s + ((s0 + si) * NG + g) * 2);
                     float dx = __fadd_rn(si == 0 ? oc.x : oc.z, ob.x), dy = __fadd_rn(si == 0 ? oc.y : oc.w, ob.y);
-                    dx = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dx)), ftx);
-                    dy = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dy)), fty);
+                    dx = __fadd_rn(__fmul_rn(a.offset_scale, tanh_sfu(dx)), ftx);
+                    dy = __fadd_rn(__fmul_rn(a.offset_scale, tanh_sfu(dy)), fty);
                     // coordinate replay of sampler_geom (sampler.cuh), frame coordinates
-                    const float gx = __fadd_rn(lxv, __fmul_rn(__fdiv_rn(dx, wm1), 0.5f));
-                    const float gy = __fadd_rn(lyv, __fdiv_rn(dy, half_h));
+                    const float gx = __fadd_rn(lxv, __fmul_rn(div_rn(dx, wm1, w.r_wm1), 0.5f));
+                    const float gy = __fadd_rn(lyv, div_rn(dy, half_h, w.r_half_h));
                     float ix = __fmul_rn(__fmul_rn(__fadd_rn(gx, 1.0f), 0.5f), wm1);
                     float iy = __fmul_rn(__fmul_rn(__fadd_rn(gy, 1.0f), 0.5f), hm1);
                     const bool finite = isfinite(ix) && isfinite(iy);
@@ -516,6 +544,8 @@ static int launch_win(const DattnArgs& a_in, cudaStream_t st) {
     w.my = RY + 1 + sy;
     w.row_bytes = w.Ww * Cfg::REC * 4;
     w.box_bytes = (uint32_t)((size_t)w.Ww * w.Hw * Cfg::REC * 4);
+    w.r_wm1 = (float)(1.0 / (double)(float)(a.fe.Wg - 1));
+    w.r_half_h = (float)(1.0 / (double)(float)((a.fe.Hg - 1.0) / 2.0));
     const size_t smem = fixed + w.box_bytes;
     const CUtensorMap *tm0 = nullptr, *tm1 = nullptr;
     int rc = get_win_tmap(a.feat[0], a.B, a.H, a.W, Cfg::C, Cfg::REC, w.Ww, w.Hw, &tm0);
@@ -547,6 +577,7 @@ int launch_dattn_win(const DattnArgs& a, int C, int nG, cudaStream_t st) {
     if ((reinterpret_cast<uintptr_t>(a.feat[0]) | reinterpret_cast<uintptr_t>(a.feat[1]) | reinterpret_cast<uintptr_t>(a.offs[0]) |
          reinterpret_cast<uintptr_t>(a.offs[1])) & 15)
         return VFI_ERR_UNSUPPORTED;
+    if (a.fe.Wg < 2 || a.fe.Hg < 2) return VFI_ERR_UNSUPPORTED;      // degenerate normalisation: the gather kernel handles it
     if (C == 72 && nG == 8) return launch_win<9>(a, st);
     return VFI_ERR_UNSUPPORTED;
 }
