@@ -48,6 +48,8 @@ __device__ __forceinline__ float div_rn(float x, float d, float r) {
     return __fmaf_rn(e, r, q);
 }
 
+constexpr int kWinTW = 8, kWinTH = 4;   // pixel tile of a CTA (8 warps x 4 horizontally adjacent pixels)
+
 // Shared-memory plan (floats).  Row / block strides are padded so that the 8 lanes of a pixel (one per group, reading 8
 // different rows / blocks with LDS.128) fall into 8 different bank quads.
 template <int GC>
