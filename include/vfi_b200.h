@@ -284,6 +284,18 @@ size_t vfi_frame_metrics_workspace_bytes(int B, int C, int H, int W);
 int vfi_frame_metrics_f32(const float* img1, const float* img2, double* out, int B, int C, int H, int W, float val_range,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* Allocation-free variant of vfi_frame_metrics_f32.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same inputs, outputs and results, but the partial sums live in a 1 MiB file-scope
+ * device array (vfi_frame_metrics_static_max_bytes) that every GPU loading the library holds until exit; the call itself
+ * allocates and frees nothing.  Shapes whose vfi_frame_metrics_workspace_bytes exceed the array (e.g. more than 7
+ * 1080p RGB frame pairs per call) are refused with VFI_ERR_UNSUPPORTED.  All calls on a device share the array: calls
+ * that overlap on the GPU (different streams / host threads) race; calls on one stream are safe.  Nothing needs clearing
+ * between calls (every partial read is written first). */
+size_t vfi_frame_metrics_static_max_bytes(void);
+int vfi_frame_metrics_static_f32(const float* img1, const float* img2, double* out, int B, int C, int H, int W,
+                                 float val_range, void* stream);
+
 /* Number of kernel launches issued by this library on the calling thread since the last reset
  * (bench.py reports it as gpu_launches). */
 int64_t vfi_launch_count(void);

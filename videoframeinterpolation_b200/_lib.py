@@ -54,6 +54,8 @@ SIGNATURES = {
     "vfi_dcndat_coords_f32": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
     "vfi_frame_metrics_workspace_bytes": (c_size_t, [c_int] * 4),
     "vfi_frame_metrics_f32": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_float, c_void_p, c_size_t, c_void_p]),
+    "vfi_frame_metrics_static_max_bytes": (c_size_t, []),
+    "vfi_frame_metrics_static_f32": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_float, c_void_p]),
     "vfi_resize2x_f32": (c_int, [c_void_p] * 4 + [c_float, c_void_p] + [c_int] * 4 + [c_void_p, c_void_p]),
     "vfi_launch_count": (c_int64, []),
     "vfi_launch_count_reset": (None, []),

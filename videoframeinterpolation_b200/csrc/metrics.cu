@@ -183,3 +183,56 @@ extern "C" int vfi_frame_metrics_f32(const float* img1, const float* img2, doubl
     VFI_CHECK_LAUNCH("metrics_reduce_kernel");
     return VFI_OK;
 }
+
+// ---- allocation-free variant -------------------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot allocate device
+// memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The partial sums that
+// vfi_frame_metrics_f32 keeps in a caller-supplied workspace live in a file-scope device array instead: 1 MiB, held by
+// every GPU that loads the library until the process exits.  Every call on a device shares that array, so calls that
+// overlap on the GPU (different streams, different host threads) race on it; calls on one stream are ordered and safe.
+// Nothing in it has to start at zero: ssim_psnr_kernel overwrites every partial that metrics_reduce_kernel reads, so the
+// previous call's contents are never seen.
+namespace vfi {
+
+constexpr size_t kStaticMetricsBytes = (size_t)1 << 20;
+static __device__ __align__(256) unsigned char g_metrics_scratch[kStaticMetricsBytes];
+
+// In host code `g_metrics_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int static_metrics_scratch(void** out) {
+    constexpr int kMaxDev = 64;
+    static void* ptrs[kMaxDev] = {};
+    static bool have[kMaxDev] = {};
+    int dev = -1;
+    VFI_CUDA(cudaGetDevice(&dev));
+    VFI_REQUIRE(dev >= 0 && dev < kMaxDev, "vfi_frame_metrics_static_f32: device ordinal %d out of range", dev);
+    // benign race: two host threads may both query the same device the first time and store the same address
+    if (!have[dev]) {
+        void* p = nullptr;
+        VFI_CUDA(cudaGetSymbolAddress(&p, g_metrics_scratch));
+        VFI_REQUIRE(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0, "vfi_frame_metrics_static_f32: bad scratch address");
+        ptrs[dev] = p;
+        have[dev] = true;
+    }
+    *out = ptrs[dev];
+    return VFI_OK;
+}
+
+}  // namespace vfi
+
+extern "C" size_t vfi_frame_metrics_static_max_bytes(void) { return vfi::kStaticMetricsBytes; }
+
+extern "C" int vfi_frame_metrics_static_f32(const float* img1, const float* img2, double* out, int B, int C, int H, int W,
+                                            float val_range, void* stream) {
+    using namespace vfi;
+    if (B == 0) return VFI_OK;
+    VFI_REQUIRE(B >= 1 && C >= 1 && H >= 1 && W >= 1, "vfi_frame_metrics_static_f32: bad shape");
+    const size_t need = vfi_frame_metrics_workspace_bytes(B, C, H, W);
+    if (need > kStaticMetricsBytes)
+        VFI_UNSUPPORTED("vfi_frame_metrics_static_f32: B=%d C=%d H=%d W=%d needs %zu B of scratch, the built-in array holds %zu B "
+                        "(use vfi_frame_metrics_f32 with a caller-supplied workspace)", B, C, H, W, need, kStaticMetricsBytes);
+    void* scratch = nullptr;
+    const int rc = static_metrics_scratch(&scratch);
+    if (rc) return rc;
+    return vfi_frame_metrics_f32(img1, img2, out, B, C, H, W, val_range, scratch, kStaticMetricsBytes, stream);
+}
