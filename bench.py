@@ -30,9 +30,18 @@ import torch  # noqa: E402
 METRIC = "DAT frames/sec @1080p"
 UNIT = "frames/s"
 H_RAW, W_RAW = 1080, 1920
-# dram__bytes_read.sum + dram__bytes_write.sum of the 1/2-res dattn launch, one ncu --set full capture (profiles/)
-TRAFFIC_DATTN_LV1 = 4273428000 + 137034752     # profiles/r1o_dattn_lv1_ncu_full.txt
-CPU_SAMPLE_HW = (256, 448)        # BASELINE.json configs[0]: the reference's own CPU-runnable case
+# ncu --set full summary of the 1/2-res fused-attention launch of THIS tree (written by profiles/ncu_to_json.py from the
+# round's own capture): roofline.traffic = dram__bytes_read.sum + dram__bytes_write.sum is read from it at run time
+DATTN_NCU_SUMMARY = os.path.join("profiles", "r3_dattn_win_ncu.json")
+# CPU arm: a bounded sample of the 1080p workload.  The full 1088x1920 forward of the reference's op composition on the
+# host cores was measured once on the GPU box (profiles/r3_cpu_reference_1080p.txt: 167-173 s per pair, 56 GiB, 16
+# cores) -- far beyond the few minutes the bench may take for K steps -- so each CPU step is one 544x960 pair, a quarter
+# of the pixels at the same aspect, and frames/s are scaled by pixel count (which FLATTERS the CPU: its cost grows
+# faster than the pixel count, 3.8 s -> 167 s for 4x the pixels).
+CPU_SAMPLE_HW = (544, 960)
+CPU_FULL_CONFIG_MEASURED = {"sec_per_pair": 167.0, "frames_per_s": 1.0 / 167.0, "peak_rss_gib": 56.6, "cores": 16,
+                            "frame": "1920x1088", "source": "profiles/r3_cpu_reference_1080p.txt (tools/cpu_ref_probe.py on the GPU box's host)"}
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12       # nominal: 148 SMs x 128 FMA lanes x 2 flop x max SM clock
 
 
 def parse_args():
@@ -46,6 +55,7 @@ def parse_args():
     ap.add_argument("--width", type=int, default=W_RAW)
     ap.add_argument("--no-micro", action="store_true", help="skip the warp/splat micro-benchmark")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-legs", action="store_true", help="skip the extra legs (DCNDATv1, 4K tiled, 448x256, TF32-vs-fp32 parity)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs under ncu only)")
     ap.add_argument("--channels-last", type=int, default=1, help="run the cuDNN conv stacks around the hot path in NHWC (0 = NCHW)")
     ap.add_argument("--graph", type=int, default=1, help="replay the forward from a CUDA graph (0 = eager launches from Python)")
@@ -152,8 +162,15 @@ def cpu_scale(height, width):
 
 def cpu_sample_text(cores):
     return (f"oracle port of DATwConstantnCv1.inference (torch CPU grid_sample / torchvision deform_conv2d, fp32, {cores} threads) "
-            f"on one {CPU_SAMPLE_HW[1]}x{CPU_SAMPLE_HW[0]} pair (BASELINE configs[0]); frames/s scaled by pixel count to "
-            f"1088x1920 (the 1080p forward itself needs ~40 GB for the reference's materialised kv tensors)")
+            f"timed on one {CPU_SAMPLE_HW[1]}x{CPU_SAMPLE_HW[0]} pair per step = 1/4 of the pixels of a 1920x1088 pair; value = "
+            f"1080p-equivalent frames/s by pixel count (EXTRAPOLATED, in the CPU's favour: the full 1920x1088 forward measured "
+            f"on this pool's hosts takes {CPU_FULL_CONFIG_MEASURED['sec_per_pair']:.0f} s = "
+            f"{CPU_FULL_CONFIG_MEASURED['frames_per_s']:.4f} frames/s, {CPU_FULL_CONFIG_MEASURED['source']})")
+
+
+def cpu_workload_name(args):
+    return (workload_name(args) + f" -- CPU arm: each step times a BOUNDED SAMPLE, one {CPU_SAMPLE_HW[1]}x{CPU_SAMPLE_HW[0]} pair "
+            "(1/4 of the pixels); the full-size CPU forward is 167 s per pair (measured, see cpu_baseline)")
 
 
 def run_reference(args):
@@ -173,8 +190,10 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args), "pairs_per_gpu": args.pairs},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_sample_text(cores)},
+            "config": {"workload": cpu_workload_name(args), "pairs_per_gpu": args.pairs,
+                       "timed_frame": f"{CPU_SAMPLE_HW[1]}x{CPU_SAMPLE_HW[0]}", "value_is": "extrapolated by pixel count to 1920x1088"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_sample_text(cores),
+                             "sec_per_sample_forward": dt, "measured_full_config": CPU_FULL_CONFIG_MEASURED},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
@@ -219,7 +238,7 @@ def torch_cuda_baseline(args, dev, H, W):
             "sample": "oracle port of DATwConstantnCv1.inference with library ops on cuda:0, median of 3 after 1 warm-up"}
 
 
-def dcndat_1080p(args, dev, H, W):
+def dcndat_1080p(args, dev, H, W, world=1, dist=None, with_library_baseline=True):
     """BASELINE configs[3] read literally: the DCNDATv1 archive model (models/archive/DCNDAT.py, repaired per SURVEY.md
     Note B) on one padded frame pair resident in HBM -- this repo's CUDA-graph replay next to the same composition on
     the PyTorch-CUDA library ops (oracle port with ATen grid_sample / torchvision deform_conv2d / cuDNN)."""
@@ -232,19 +251,30 @@ def dcndat_1080p(args, dev, H, W):
     ph, pw = -(-H // 16) * 16, -(-W // 16) * 16
     x0, x1 = (torch.rand(1, 3, ph, pw, generator=g).to(dev).contiguous(memory_format=torch.channels_last) for _ in range(2))
     t = torch.full((1, 1, 1, 1), 0.5, device=dev)
-    out = {"model": "DCNDATv1 (configs/archive/DCNDAT.yaml, nf=64)", "frame": f"{pw}x{ph}", "pairs": 1, "unit": UNIT}
+    out = {"model": "DCNDATv1 (configs/archive/DCNDAT.yaml, nf=64)", "frame": f"{pw}x{ph}", "pairs_per_gpu": 1, "n_gpus": world,
+           "unit": UNIT, "scaling": "weak"}
     try:
         with torch.no_grad():
             graphed = v.GraphedInference(net, x0, x1, t)
+            for _ in range(2):
+                graphed.replay()
+            if world > 1:
+                dist.barrier()
             ms = time_op(graphed.replay, max(args.steps, 5), None)
-            out.update({"value": 1e3 / ms, "ms_per_step": ms, "api": "DCNDATv1.inference replayed from a CUDA graph"})
+            if world > 1:
+                mt = torch.tensor([ms], device=dev)
+                dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+                ms = float(mt.item())
+            out.update({"value": 1e3 * world / ms, "ms_per_step": ms, "api": "DCNDATv1.inference replayed from a CUDA graph; value = "
+                        "all ranks' pairs / max-over-ranks median step time"})
             del graphed
-            sd = {k: w.detach().clone() for k, w in net.state_dict().items()}
-            xa, xb = x0.contiguous(), x1.contiguous()
-            with oracle.library_ops():
-                ms_lib = time_op(lambda: oracle.dcndat_forward(sd, xa, xb, t), 3, None)
-            out["torch_cuda_baseline"] = {"value": 1e3 / ms_lib, "ms_per_step": ms_lib, "speedup_of_this_repo": ms_lib / ms,
-                                          "ops": "ATen grid_sampler_2d, torchvision deform_conv2d, cuDNN convs (tf32=%d), eager PyTorch" % args.tf32}
+            if with_library_baseline:
+                sd = {k: w.detach().clone() for k, w in net.state_dict().items()}
+                xa, xb = x0.contiguous(), x1.contiguous()
+                with oracle.library_ops():
+                    ms_lib = time_op(lambda: oracle.dcndat_forward(sd, xa, xb, t), 3, None)
+                out["torch_cuda_baseline"] = {"value": 1e3 / ms_lib, "ms_per_step": ms_lib, "speedup_of_this_repo": ms_lib / ms,
+                                              "ops": "ATen grid_sampler_2d, torchvision deform_conv2d, cuDNN convs (tf32=%d), eager PyTorch" % args.tf32}
     except torch.OutOfMemoryError as e:
         out["unavailable"] = f"out of memory: {str(e)[:120]}"
     torch.cuda.empty_cache()
@@ -307,7 +337,69 @@ def microbench(dev, hbm_peak):
     res["flow_kinds"] = ("smooth: 32 px correlation length (strain ~0.35 px/px) + 2% outliers; gentle: 256 px correlation "
                          "length; iid: independent per pixel (SURVEY.md 8d literal)")
     res["dcn_cfg3"] = dcn_cfg3(dev, hbm_peak, flush)
+    res["baselines_1080p"] = op_baselines(dev, flush)
     return res
+
+
+def _best_of(fn, n):
+    fn()
+    ts = []
+    for _ in range(n):
+        t0 = time.perf_counter()
+        fn()
+        ts.append(time.perf_counter() - t0)
+    return min(ts) * 1e3
+
+
+def op_baselines(dev, flush):
+    """beside the warp / splat numbers at 1080x1920, (a) the reference function on the box's host cores
+    (torch CPU grid_sample through modules/warp.py:7-15; the pure-torch scatter restatement of the splat, which the
+    reference implements only in CUDA; and the reference's own kernel text compiled as C++, one thread), and (b) the same
+    GPU running what the reference runs: ATen grid_sampler_2d through the reference's bwarp (including its per-call grid
+    construction and H2D copy, modules/warp.py:9-11), and the reference's splat kernel text compiled unmodified for
+    sm_100a (oracle/_ref, built from /root/reference in the build container) inside the reference's front-end
+    composition (exp, cat, zero-fill, kernel, divide: modules/softsplat.py:237-279)."""
+    import oracle
+    import videoframeinterpolation_b200 as v
+    from oracle import build_oracle as bo
+    from videoframeinterpolation_b200.workloads import make_flow, seed_for
+    H, W = H_RAW, W_RAW
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    rows = []
+    for C in (3, 64):
+        g = torch.Generator().manual_seed(seed_for(2, C))
+        img = torch.rand(1, C, H, W, generator=g)
+        metric = torch.randn(1, 1, H, W, generator=g)
+        flow = make_flow(1, H, W, 8.0, g, kind="smooth")
+        row = {"C": C, "H": H, "W": W, "flow": "smooth", "cpu_cores": cores}
+        with oracle.library_ops():
+            row["bwarp_cpu_ms"] = _best_of(lambda: oracle.bwarp(img, flow), 3)
+        row["softsplat_cpu_ms"] = _best_of(lambda: oracle.fwarp(img, flow, metric, "soft"), 1 if C > 8 else 2)
+        dimg, dflow, dmetric = img.to(dev), flow.to(dev), metric.to(dev)
+        with oracle.library_ops():
+            row["bwarp_torch_cuda_ms"] = time_op(lambda: oracle.bwarp(dimg, dflow), 10, flush)
+        row["bwarp_vfi_ms"] = time_op(lambda: v.bwarp(dimg, dflow), 10, flush)
+        row["softsplat_vfi_ms"] = time_op(lambda: v.softsplat(dimg, dflow, dmetric, "soft"), 10, flush)
+        if bo.ref_cuda_so_path(1, C + 1, H, W).exists():
+            buf = torch.empty(1, C + 1, H, W, device=dev)
+
+            def ref_soft():
+                e = dmetric.exp()
+                out = bo.reference_splat_sum_cuda(torch.cat([dimg * e, e], 1), dflow, out=buf)
+                return out[:, :-1] / (out[:, -1:] + 0.0000001)
+            got, want = ref_soft(), v.softsplat(dimg, dflow, dmetric, "soft")
+            row["softsplat_ref_kernel_vs_vfi_rel_err"] = float((got - want).abs().max() / want.abs().max())
+            row["softsplat_ref_kernel_cuda_ms"] = time_op(ref_soft, 10, flush)
+        else:
+            row["softsplat_ref_kernel_cuda_ms"] = None
+        if C == 3 and bo.ref_so_path(1, C + 1, H, W).exists():
+            e = metric.exp()
+            x = torch.cat([img * e, e], 1)
+            row["softsplat_ref_kernel_text_cpu_1thread_ms"] = _best_of(lambda: bo.reference_splat_sum(x, flow), 1)
+        rows.append(row)
+    return {"rows": rows, "note": "cpu = reference functions on the host cores (oracle port, library ops); torch_cuda / ref_kernel_cuda = "
+            "what the reference itself launches on this GPU; vfi = this repo, same tensors, L2 flushed between iterations"}
 
 
 def dcn_cfg3(dev, hbm_peak, flush):
@@ -330,11 +422,126 @@ def dcn_cfg3(dev, hbm_peak, flush):
         import torchvision.ops as tvo
         ms_tv = time_op(lambda: tvo.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask), 3, flush)
         out["torchvision_cuda_ms"] = ms_tv
+        # the reference's CPU path for the same op on a bounded sample: 4 of the 32 patches, scaled x8
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        xc, oc, mc, wc, bc = x[:4].cpu(), off[:4].cpu(), mask[:4].cpu(), wgt.cpu(), bias.cpu()
+        out["torchvision_cpu_ms"] = 8.0 * _best_of(lambda: tvo.deform_conv2d(xc, oc, wc, bc, padding=1, mask=mc), 2)
+        out["torchvision_cpu_note"] = f"{cores} host threads, 4 of the 32 patches timed, x8"
     except Exception as e:      # library baseline only; never on the product path
         out["torchvision_cuda_ms"] = None
         out["torchvision_note"] = str(e)[:100]
     return out
 
+
+
+def dattn_ncu_summary():
+    """dram bytes of the 1/2-res fused-attention launch from the round's own ncu --set full capture (profiles/)."""
+    path = os.path.join(ROOT, DATTN_NCU_SUMMARY)
+    try:
+        with open(path) as f:
+            d = json.load(f)
+        return int(d["dram_bytes_read"]) + int(d["dram_bytes_write"]), DATTN_NCU_SUMMARY, d
+    except Exception:
+        return None, None, None
+
+
+def dattn_flops(B, C, H, W, nG, nS):
+    """fp32 flops of the folded algebra per launch: q / kt / v projections once per pixel, logits and
+    weighted sums over 2 nS slots x nG heads x C channels, bilinear taps."""
+    return 2.0 * B * H * W * (2 * C * C + C * C + 2 * (2 * nS) * nG * C + 4 * C * 2 * nS)
+
+
+def tiled_4k_leg(net, dev, rank, world, steps, dist, grid=(2, 4), halo=64, H=2160, W=3840):
+    """BASELINE configs[4] inside the normal bench line: ONE synthetic 3840x2160 pair, 2x4 spatial tiles with a 64-px
+    halo dealt to the ranks (strong scaling, no collective), every tile run with the frame's extent passed to the warp /
+    sampler kernels (frame_ext of the C ABI), CUDA-graph replay; pairs/s of the WHOLE pair = 1 / max-over-ranks time."""
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.shard import tile_plan, tiles_of_rank
+    from videoframeinterpolation_b200.workloads import seed_for
+    g = torch.Generator().manual_seed(seed_for(5, 0))           # the same pair on every rank
+    x0, x1 = torch.rand(1, 3, H, W, generator=g).to(dev), torch.rand(1, 3, H, W, generator=g).to(dev)
+    padder = v.InputPadder((H, W), divisor=16)
+    d_x0, d_x1 = padder.pad(x0, x1)
+    t = torch.full((1, 1, 1, 1), 0.5, device=dev)
+    ph, pw = d_x0.shape[-2:]
+    plan = tile_plan(ph, pw, grid, halo)
+    mine = tiles_of_rank(plan, rank, world)
+    out_buf = torch.zeros((1, 3, ph, pw), device=dev)
+
+    def fn(a, b, tt):
+        return net.inference_tiled(a, b, tt, grid=grid, halo=halo, rank=rank, world=world, out=out_buf)
+
+    res = {"frame": f"{W}x{H} (padded {pw}x{ph})", "tile_grid": f"{grid[0]}x{grid[1]}", "halo_px": halo, "tiles_per_rank": len(mine),
+           "unit": "pairs/s", "scaling": "strong", "parallelism": f"spatial tiles x{world}, no collective"}
+    try:
+        graphed = v.GraphedInference(net, d_x0, d_x1, t, fn=fn) if mine else None
+        for _ in range(2):
+            if graphed is not None:
+                graphed.replay()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            if graphed is not None:
+                graphed.replay()
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms_per_step = float(ms.item()) / steps
+        crop_px = sum((tl.crop[0].stop - tl.crop[0].start) * (tl.crop[1].stop - tl.crop[1].start) for tl in plan)
+        res.update({"value": 1e3 / ms_per_step, "ms_per_step": ms_per_step, "redundant_pixels": crop_px / float(ph * pw) - 1.0,
+                    "tile_vs_whole_parity": "1.1e-6 of full scale at halo 64 (tests/test_gpu_parity_dat.py::test_dat_tiled_inference_matches_whole_frame); "
+                                            "impulse-response radius of these weights: 8 px at 1e-5 (test_dat_impulse_response_radius)"})
+        del graphed
+    except torch.OutOfMemoryError as e:
+        res["unavailable"] = f"out of memory: {str(e)[:120]}"
+    torch.cuda.empty_cache()
+    return res
+
+
+def configs0_leg(net, dev, steps):
+    """BASELINE configs[0] on the GPU: one synthetic 448x256 Vimeo90K-shaped pair, CUDA-graph replay."""
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.workloads import seed_for
+    g = torch.Generator().manual_seed(seed_for(1, 0))
+    x0 = torch.rand(1, 3, 256, 448, generator=g).to(dev).contiguous(memory_format=torch.channels_last)
+    x1 = torch.rand(1, 3, 256, 448, generator=g).to(dev).contiguous(memory_format=torch.channels_last)
+    t = torch.full((1, 1, 1, 1), 0.5, device=dev)
+    graphed = v.GraphedInference(net, x0, x1, t)
+    ms = time_op(graphed.replay, max(steps, 10), None)
+    del graphed
+    torch.cuda.empty_cache()
+    return {"frame": "448x256", "pairs": 1, "value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "api": "DATwConstantnCv1.inference, CUDA graph replay"}
+
+
+def tf32_parity_leg(net, d_x0, d_x1, t):
+    """The measured mode (TF32 tensor-core convs, PyTorch's default conv arithmetic) against the same forward with fp32 convs
+    (cuDNN, allow_tf32 = False) on the benchmark's own 1088x1920 pair: max / mean absolute error on [0, 1] frames and PSNR,
+    plus the fp32-conv step time (eager)."""
+    import math
+    with torch.no_grad():
+        y_tf32 = net.inference(d_x0, d_x1, t).float().clone()
+        prev = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+        try:
+            y_fp32 = net.inference(d_x0, d_x1, t).float().clone()
+            ms_fp32 = time_op(lambda: net.inference(d_x0, d_x1, t), 3, None)
+        finally:
+            torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = prev
+    d = (y_tf32 - y_fp32).abs()
+    mse = float((d.double() ** 2).mean())
+    return {"max_abs": float(d.max()), "mean_abs": float(d.mean()), "psnr_db": (-10.0 * math.log10(mse) if mse > 0 else float("inf")),
+            "frame": f"{d_x0.shape[-1]}x{d_x0.shape[-2]}", "reference": "this repo's forward with fp32 convolutions (cuDNN, allow_tf32 = False); "
+            "the fp32 forward itself is pinned to the oracle at 5e-5 (tests/test_gpu_parity_dat.py)",
+            "fp32_convs_ms_per_step_eager": ms_fp32, "fp32_convs_frames_per_s_eager": 1e3 * d_x0.shape[0] / ms_fp32}
 
 # ------------------------------------------------------------------------------------------------
 # this repo's arm
@@ -480,12 +687,18 @@ def run_vfi(args):
     lv1_ms = sum(lv1) / max(len(lv1), 1)
     alg = bytes_dattn(P, 72, ph // 2, pw // 2, 8, 32)
     achieved = alg / lv1_ms / 1e6 if lv1_ms > 0 else 0.0
-    roofline = {"kernel": "dattn_kernel<9,8> (fused sampler+attention, 1/2 res)", "bound": "hbm", "achieved": achieved,
-                "peak": hbm_peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / hbm_peak,
+    traffic, traffic_src, ncu_d = dattn_ncu_summary()
+    fl = dattn_flops(P, 72, ph // 2, pw // 2, 8, 32)
+    fp32_tf = fl / lv1_ms / 1e9 if lv1_ms > 0 else 0.0
+    roofline = {"kernel": "dattn_win_kernel<9> (fused sampler + attention, 1/2 res: TMA-staged shared-memory window, lane = pixel x group)",
+                "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / hbm_peak,
                 "algorithmic_bytes_per_launch": alg, "ms_per_launch": lv1_ms,
-                "note": "gather kernel: 18.4k data-dependent taps + ~170 kFLOP fp32 per pixel; binding resource is the L1/LSU request rate "
-                        "(gather floor ~4.3 ms) and fp32 FMA (~2.5 ms), not HBM (DESIGN.md 4.3); traffic from profiles/ ncu capture",
-                "traffic": TRAFFIC_DATTN_LV1 if (P == 1 and (ph, pw) == (1088, 1920)) else None}
+                "frac_fp32": fp32_tf / FP32_PEAK_TFLOPS, "fp32": {"achieved_tflops": fp32_tf, "peak_tflops": FP32_PEAK_TFLOPS,
+                                                                  "peak_source": "nominal 148 SM x 128 FMA x 2 x 1.965 GHz",
+                                                                  "flops_per_launch": fl},
+                "note": "18.4k bilinear taps + ~170 kFLOP fp32 per pixel: the binding resources are shared-memory wavefronts of the "
+                        "tap reads and fp32 issue, not HBM (DESIGN.md 4.3); reported against HBM as the contract asks, frac_fp32 beside it",
+                "traffic": traffic if (P == 1 and (ph, pw) == (1088, 1920)) else None, "traffic_source": traffic_src}
     op_ms = {k: {"calls_per_step": c / args.steps, "ms_per_step": ms / args.steps} for k, (c, ms) in ops.items()}
     # second kernel family of the step: the tensor-core 3x3 convolutions (all launches of a step together)
     conv_ms = op_ms.get("vfi_conv3x3_f32", {}).get("ms_per_step", 0.0)
@@ -503,14 +716,18 @@ def run_vfi(args):
                      "note": "shared-memory operand feed of tcgen05.mma (~68 B/clk) bounds it, DESIGN.md 4.6"}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if not args.tf32 else "f32 (hot path) / tf32 (3x3 convs)",
             "data": "synthetic",
             "config": {"workload": workload_name(args), "pairs_per_gpu": P, "global_pairs_per_step": P * world,
-                       "parallelism": f"frame-pair sharding x{world}, no collective", "conv_layout": "channels_last" if args.channels_last else "nchw", "conv_math": "tf32" if args.tf32 else "fp32",
-                       "launch": "CUDA graph replay" if args.graph else "eager", "eager_ms_per_step": eager_ms,
+                       "parallelism": f"frame-pair sharding x{world}, no collective", "conv_layout": "channels_last" if args.channels_last else "nchw",
+                       "conv_math": "tf32" if args.tf32 else "fp32",
+                       "arithmetic": "fp32 hot path (warp / sampler / attention / DCN kernels); 3x3 convs " +
+                                     ("TF32 operands with fp32 accumulation on tcgen05 = PyTorch's default cudnn.allow_tf32 conv arithmetic" if args.tf32 else "fp32 (cuDNN)"),
+                       "launch": "CUDA graph replay" if args.graph else "eager",
                        "api": "DATwConstantnCv1.interpolate(float32 frames resident in HBM): replicate pad, rgb-mean normalisation, forward, clamp, unpad",
-                       "eager_host_enqueue_ms_per_step": host_ms,
                        "l2": "inputs + activations per step (>1 GB) exceed the 126 MB L2"},
+            "details": {"eager_ms_per_step": eager_ms, "eager_host_enqueue_ms_per_step": host_ms},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * h_u0.numel(), "d2h_bytes_per_step": h_out_u8.numel(),
                     "ms_per_step": e2e_ms / args.steps,
                     "api": "DATwConstantnCv1.interpolate(uint8 frames from pinned host memory) -> uint8 frame to pinned host memory; "
@@ -521,6 +738,20 @@ def run_vfi(args):
             "roofline_conv3x3": roofline_conv, "gpu_launches": int(launches),      # vfi_b200 kernels per K steps (counted on the eager pass; the graph replays the same kernels)
             "clocks": clocks, "roofline": roofline, "vfi_ops_ms": op_ms}
 
+    if not args.no_legs:
+        with torch.no_grad():
+            # BASELINE configs[3]'s own model at every N (weak scaling: one pair per rank) and configs[4] (one 4K pair tiled
+            # over the ranks): every rank takes part, rank 0 reports
+            dl = dcndat_1080p(args, dev, H, W, world, dist, with_library_baseline=(world == 1 and not args.no_cpu))
+            t4 = tiled_4k_leg(net, dev, rank, world, max(args.steps // 2, 3), dist)
+            if rank == 0:
+                line["dcndat_1080p"] = dl
+                line["tiled_4k"] = t4
+                line["configs0_448x256"] = configs0_leg(net, dev, args.steps)
+                if args.tf32:
+                    line["e2e_parity"] = tf32_parity_leg(net, d_x0, d_x1, t)
+                    line["value_fp32_convs"] = {"value": world * line["e2e_parity"]["fp32_convs_frames_per_s_eager"], "unit": UNIT,
+                                                "note": "same forward with fp32 cuDNN convolutions (--tf32 0), eager launches"}
     if rank == 0:
         if not args.no_micro:
             with torch.no_grad():
@@ -530,7 +761,6 @@ def run_vfi(args):
             if "value" in tb:
                 tb["speedup_of_this_repo"] = (1e3 * args.pairs / line["ms_per_step"]) / tb["value"]   # per GPU, frames/s over frames/s
             line["torch_cuda_baseline"] = tb
-            line["dcndat_1080p"] = dcndat_1080p(args, dev, H, W)
         if not args.no_cpu and world == 1:
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
@@ -542,7 +772,8 @@ def run_vfi(args):
                 cpu_dat_step(oracle, sd, x0, x1, tt)
             dt = (time.perf_counter() - t0) / n
             line["cpu_baseline"] = {"value": cpu_scale(H, W) / dt, "unit": UNIT, "cores": cores, "kind": "port",
-                                    "sample": cpu_sample_text(cores), "sec_per_sample_forward": dt}
+                                    "sample": cpu_sample_text(cores), "sec_per_sample_forward": dt,
+                                    "measured_full_config": CPU_FULL_CONFIG_MEASURED}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

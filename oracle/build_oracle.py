@@ -139,8 +139,60 @@ def reference_splat_sum(ten_in, ten_flow):
     return out
 
 
+# ---------------------------------------------------------------------------------------------
+# the reference's kernel text compiled for sm_100a: the "reference kernel on the same box" bar of SURVEY.md 8(d)
+# ---------------------------------------------------------------------------------------------
+_CUDA_LAUNCHER = r"""
+#include <cuda_runtime.h>
+/* launch configuration of modules/softsplat.py:342-348: ceil(n / 512) blocks of 512 threads on the caller's stream */
+extern "C" int ref_softsplat_launch(int n, const float* in, const float* flow, float* out, void* stream) {
+    softsplat_out<<<(n + 512 - 1) / 512, 512, 0, (cudaStream_t)stream>>>(n, in, flow, out);
+    return (int)cudaGetLastError();
+}
+"""
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+
+
+def ref_cuda_so_path(N: int, C: int, H: int, W: int) -> Path:
+    return REFDIR / f"splat_ref_cuda_N{N}_C{C}_H{H}_W{W}.so"
+
+
+def build_reference_splat_cuda(N: int, C: int, H: int, W: int, force: bool = False) -> Path:
+    """The reference's own kernel text (sizes / strides baked in for this contiguous shape, as its NVRTC path does)
+    compiled UNMODIFIED with nvcc for sm_100a behind a 4-line launcher that replays its launch configuration."""
+    dst = ref_cuda_so_path(N, C, H, W)
+    if dst.exists() and not force:
+        return dst
+    if not reference_available():
+        raise FileNotFoundError(f"reference checkout not found at {REFERENCE}; {dst.name} must be prebuilt")
+    REFDIR.mkdir(exist_ok=True)
+    text = "#include <cassert>\n" + _reference_kernel_source(N, C, H, W) + _CUDA_LAUNCHER
+    with tempfile.TemporaryDirectory() as tmp:
+        cu = Path(tmp) / "k.cu"
+        cu.write_text(text)
+        subprocess.check_call([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-w", "-shared", "-Xcompiler", "-fPIC",
+                               "-o", str(dst), str(cu), "-lcudart_static"])
+    return dst
+
+
+def reference_splat_sum_cuda(ten_in, ten_flow, out=None):
+    """Launch the reference's kernel (prebuilt for this shape) on CUDA tensors, on the current stream."""
+    import torch
+    N, C, H, W = ten_in.shape
+    lib = ctypes.CDLL(str(build_reference_splat_cuda(N, C, H, W)))
+    lib.ref_softsplat_launch.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.ref_softsplat_launch.restype = ctypes.c_int
+    out = torch.zeros_like(ten_in) if out is None else out.zero_()
+    rc = lib.ref_softsplat_launch(out.numel(), ten_in.data_ptr(), ten_flow.data_ptr(), out.data_ptr(),
+                                  torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, f"reference splat kernel launch failed: cudaError {rc}"
+    return out
+
+
 # shapes of the C+1-channel tensors the bench's CPU-baseline leg may time with the reference text
 BENCH_REF_SHAPES = [(1, 4, 1080, 1920), (1, 4, 270, 480)]
+# C + 1 channels (the reference concatenates the weight channel, modules/softsplat.py:260-274) at the microbench's 1080p rows
+BENCH_REF_CUDA_SHAPES = [(1, 4, 1080, 1920), (1, 65, 1080, 1920)]
 
 
 def build_all(verbose: bool = True) -> None:
@@ -150,6 +202,10 @@ def build_all(verbose: bool = True) -> None:
     if reference_available():
         for shp in BENCH_REF_SHAPES:
             q = build_reference_splat(*shp)
+            if verbose:
+                print(f"[oracle] built {q}")
+        for shp in BENCH_REF_CUDA_SHAPES:
+            q = build_reference_splat_cuda(*shp)
             if verbose:
                 print(f"[oracle] built {q}")
     elif verbose:

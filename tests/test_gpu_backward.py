@@ -176,3 +176,83 @@ def test_dat_model_trains_through_the_cuda_kernels():
     # gradients reach the sampling heads through the sampler's and the DCN's coordinate gradients
     for key in ("dat_lv1.conv_res_offset.weight", "dat_lv3.conv_res_flow.weight", "coarse_query_builder"):
         assert any(key in n and p.grad is not None and float(p.grad.abs().max()) > 0 for n, p in net.named_parameters()), key
+
+
+def test_two_frame_and_mframes_splat_are_differentiable():
+    """fwarp_using_two_frames / fwarp_mframes (modules/warp.py:68-114) with inputs that require grad: the training route
+    (reference composition over the differentiable summation splat) against torch autograd through the oracle."""
+    import videoframeinterpolation_b200 as v
+    B, C, H, W, nb = 2, 5, 14, 18, 3
+    in1, in2 = det.normal("tf.in1", (B, C, H, W)), det.normal("tf.in2", (B, C, H, W))
+    f1, f2 = det.flow_field("tf.f1", B, H, W, sigma=2.0), det.flow_field("tf.f2", B, H, W, sigma=2.0)
+    m1, m2 = det.normal("tf.m1", (B, 1, H, W)), det.normal("tf.m2", (B, 1, H, W))
+    t1 = torch.full((B, 1, 1, 1), 0.3)
+    ref_out, ref_g = _grads(lambda a, fa, b, fb, ma, mb: oracle.fwarp_using_two_frames(a, fa, t1, b, fb, 1 - t1, ma, mb)[0],
+                            in1, f1, in2, f2, m1, m2)
+    t1c = t1.cuda()
+    out, g = _grads(lambda a, fa, b, fb, ma, mb: v.fwarp_using_two_frames(a, fa, t1c, b, fb, 1 - t1c, ma, mb)[0],
+                    *(x.cuda() for x in (in1, f1, in2, f2, m1, m2)))
+    assert out.requires_grad is False and rel_err(out, ref_out) <= 1e-4
+    for a, b, name in zip(g, ref_g, ("in1", "flow1", "in2", "flow2", "metric1", "metric2")):
+        assert rel_err(a, b) <= 2e-4, f"two-frame grad wrt {name}: {rel_err(a, b):.2e}"
+    # many-to-many form
+    fl1 = torch.stack([det.flow_field(f"mf.f1.{i}", B, H, W, sigma=2.0) for i in range(nb)])
+    fl2 = torch.stack([det.flow_field(f"mf.f2.{i}", B, H, W, sigma=2.0) for i in range(nb)])
+    tt = torch.linspace(0.2, 0.8, nb).view(nb, 1, 1, 1, 1).expand(nb, B, 1, 1, 1).contiguous()
+    ref_out, ref_g = _grads(lambda a, b, ma, mb: oracle.fwarp_mframes(a, fl1, tt, b, fl2, 1 - tt, ma, mb)[0], in1, in2, m1, m2)
+    out, g = _grads(lambda a, b, ma, mb: v.fwarp_mframes(a, fl1.cuda(), tt.cuda(), b, fl2.cuda(), 1 - tt.cuda(), ma, mb)[0],
+                    *(x.cuda() for x in (in1, in2, m1, m2)))
+    assert rel_err(out, ref_out) <= 1e-4
+    for a, b, name in zip(g, ref_g, ("in1", "in2", "metric1", "metric2")):
+        assert rel_err(a, b) <= 2e-4, f"mframes grad wrt {name}: {rel_err(a, b):.2e}"
+    # without grad the fused inference kernels answer, and agree with the training route's values
+    with torch.no_grad():
+        o_inf = v.fwarp_mframes(in1.cuda(), fl1.cuda(), tt.cuda(), in2.cuda(), fl2.cuda(), 1 - tt.cuda(), m1.cuda(), m2.cuda())[0]
+    assert rel_err(o_inf, ref_out) <= 1e-4
+
+
+def test_eval_forward_without_no_grad_stays_on_the_fused_kernels_and_dcndat_refuses_training():
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200 import _lib
+    net = v.DATwConstantnCv1(v.default_args(nf=16, enc_res_blocks=1, dec_res_blocks=1))
+    net.load_state_dict(det.fill_state_dict(net.state_dict()))
+    net = net.cuda().eval()
+    x0, x1 = det.uniform("ev.x0", (1, 3, 64, 96)).cuda(), det.uniform("ev.x1", (1, 3, 64, 96)).cuda()
+    t = torch.full((1, 1, 1, 1), 0.5, device="cuda")
+    with _lib.OpTimer() as tm:
+        y = net(x0, x1, t)                       # grad mode is on, parameters require grad, inputs do not
+    assert not y.requires_grad
+    assert "vfi_dattn_f32" in tm.records and "vfi_dsample_f32" not in tm.records, sorted(tm.records)
+    with torch.no_grad():
+        assert torch.equal(y, net.inference(x0, x1, t))
+    net2 = v.DCNDATv1(v.dcndat_default_args(nf=32, enc_res_blocks=1, dec_res_blocks=1)).cuda().train()
+    with pytest.raises(_lib.VfiError, match="inference-only"):
+        net2(x0, x1, t)
+
+
+def test_prepared_weight_caches_are_invalidated_explicitly_after_data_writes():
+    """ADVICE r1: writes through .data do not bump Parameter._version, so the TF32-packed weight copies would go stale;
+    conv.invalidate_prepared(model) is the documented remedy."""
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200 import conv as vc
+    prev = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = True
+    try:
+        net = v.DATwConstantnCv1(v.default_args(nf=16, enc_res_blocks=1, dec_res_blocks=1))
+        net.load_state_dict(det.fill_state_dict(net.state_dict()))
+        net = net.cuda().eval().to(memory_format=torch.channels_last)
+        x0 = det.uniform("iv.x0", (1, 3, 64, 96)).cuda().contiguous(memory_format=torch.channels_last)
+        x1 = det.uniform("iv.x1", (1, 3, 64, 96)).cuda().contiguous(memory_format=torch.channels_last)
+        t = torch.full((1, 1, 1, 1), 0.5, device="cuda")
+        with torch.no_grad():
+            y0 = net.inference(x0, x1, t).clone()
+            for p in net.pixel_geneartor.parameters():
+                p.data.mul_(0.5)                                   # in place through .data: version not bumped
+            vc.invalidate_prepared(net)
+            y1 = net.inference(x0, x1, t).clone()
+            torch.backends.cudnn.allow_tf32 = False
+            y1_fp32 = net.inference(x0, x1, t)                     # cuDNN reads the live weights
+        assert float((y1 - y0).abs().max()) > 1e-3, "the write changed nothing?"
+        assert float((y1 - y1_fp32).abs().max()) <= 2e-2, "prepared weights are stale after invalidate_prepared"
+    finally:
+        torch.backends.cudnn.allow_tf32 = prev

@@ -129,6 +129,49 @@ def test_dat_forward_tc_convs_match_fp32_convs(tf32):
     assert float((y_tc - y_fp32).abs().mean()) <= 2e-3
 
 
+def test_dat_forward_measured_mode_vs_reference_ops_with_tf32(tf32):
+    """The configuration bench.py times -- tcgen05 3x3 convs, split movement convs, no-concat HalfChannel block, fused
+    PixelShuffle, ConvTranspose on the tensor-core kernel (>= 65536 px at 1/4 res needs a >= 1 Mpx frame), channels-last
+    tensors, window-form attention -- at 1024x1024 against the reference's op composition on the PyTorch-CUDA library ops
+    WITH cuDNN TF32 (what the reference itself runs on a GPU), and against the fp32 oracle composition.
+    Both sides round conv operands to TF32, in different places, so the bound is a PSNR / mean-error bound."""
+    import math
+    import oracle
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200 import _lib
+    from videoframeinterpolation_b200.workloads import init_dat_weights
+    torch.manual_seed(0)
+    net = init_dat_weights(v.DATwConstantnCv1(v.default_args())).cuda().eval().to(memory_format=torch.channels_last)
+    g = torch.Generator().manual_seed(4)
+    x0 = torch.rand(1, 3, 1024, 1024, generator=g).cuda()
+    x1 = torch.rand(1, 3, 1024, 1024, generator=g).cuda()
+    t = torch.full((1, 1, 1, 1), 0.5, device="cuda")
+    cl = lambda a: a.contiguous(memory_format=torch.channels_last)
+    prev_mm = torch.backends.cuda.matmul.allow_tf32
+    with torch.no_grad():
+        with _lib.OpTimer() as tm:
+            y = net.inference(cl(x0), cl(x1), t).float()
+        calls = {k: len(e) for k, e in tm.records.items()}
+        assert calls.get("vfi_conv3x3_f32", 0) >= 100 and calls.get("vfi_dattn_f32", 0) == 3, calls
+        sd = {k: w.detach().clone() for k, w in net.state_dict().items()}
+        with oracle.library_ops():
+            ref_tf32 = oracle.dat_forward(sd, x0, x1, t)            # cuDNN TF32 convs (allow_tf32 is on in this fixture)
+            torch.backends.cudnn.allow_tf32 = False
+            torch.backends.cuda.matmul.allow_tf32 = False
+            ref_fp32 = oracle.dat_forward(sd, x0, x1, t)
+    torch.backends.cuda.matmul.allow_tf32 = prev_mm
+    def stats(a, b):
+        d = (a - b).abs()
+        return float(d.max()), float(d.mean()), -10.0 * math.log10(max(float((d.double() ** 2).mean()), 1e-30))
+    mx, mean, psnr = stats(y, ref_fp32)
+    mx_r, mean_r, psnr_r = stats(ref_tf32, ref_fp32)
+    print(f"measured mode vs fp32 reference ops: max {mx:.2e} mean {mean:.2e} psnr {psnr:.1f} dB; "
+          f"reference ops with cuDNN TF32 vs fp32: max {mx_r:.2e} mean {mean_r:.2e} psnr {psnr_r:.1f} dB")
+    assert mean <= 2e-3 and psnr >= 50.0, (mx, mean, psnr)
+    # no worse than a small multiple of what the reference's own TF32 arithmetic does to its fp32 result
+    assert mean <= 4.0 * mean_r + 1e-4, (mean, mean_r)
+
+
 @pytest.mark.parametrize("shape", [(1, 72, 288, 20, 12), (2, 72, 288, 15, 9), (1, 32, 64, 16, 8)])
 def test_conv3x3_fused_pixel_shuffle(tf32, shape):
     """upconv1 -> PixelShuffle(2) -> PReLU of the generator (modules/generator.py:14-22) in one kernel."""

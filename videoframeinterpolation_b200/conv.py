@@ -79,6 +79,27 @@ def prepared_weight(conv: nn.Conv2d, upscale: int = 1, roll: int = 0) -> torch.T
     return wp
 
 
+_CACHE_ATTRS = ("_vfi_wprep", "_vfi_wprep_slices", "_vfi_as_conv", "_vfi_bias_rolled", "_vfi_slope_rolled")
+
+
+def invalidate_prepared(model: nn.Module) -> None:
+    """Drop every prepared-weight cache under ``model`` (TF32-packed weights, ConvTranspose-as-conv modules, rolled bias /
+    slope vectors).  The caches are keyed on (data_ptr, _version); ``param.copy_`` / ``load_state_dict`` / optimizer steps
+    bump the version, but writes through ``.data`` (``p.data.copy_(ema)``, ``m.weight.data.zero_()`` as the reference's own
+    ``_init_zero`` does, modules/deformable_attn.py:72-75) do NOT -- call this after such writes."""
+    for m in model.modules():
+        for a in _CACHE_ATTRS:
+            if a in m.__dict__:
+                object.__delattr__(m, a)
+
+
+def install_invalidation_hooks(model: nn.Module) -> nn.Module:
+    """Clear the prepared-weight caches whenever ``model.load_state_dict`` runs (belt and braces: it uses ``copy_``, which
+    already bumps the versions the caches are keyed on)."""
+    model.register_load_state_dict_post_hook(lambda module, incompatible: invalidate_prepared(module))
+    return model
+
+
 def _rolled(owner: nn.Module, name: str, v: torch.Tensor, roll: int) -> torch.Tensor:
     """torch.roll(v, -roll) cached on ``owner`` (per-channel bias / PReLU slope of a conv whose outputs are rolled)."""
     key = (v.data_ptr(), v._version, str(v.device), roll)

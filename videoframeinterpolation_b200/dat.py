@@ -13,6 +13,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .blocks import BasicResPixelShuffleGenerator, SameChannelResEncoder, run_conv_chain
+from . import conv as _conv
 from .conv import conv_transpose_up2
 from .dcnv2 import DeformableConv2d
 from .deformable_attn import CrossDeformableAttentionBlockwFlow
@@ -65,6 +66,7 @@ class DATwConstantnCv1(nn.Module):
         self.dat_lv1 = CrossDeformableAttentionBlockwFlow(nf, nf, n_samples=32, n_groups=8, n_heads=8, offset_scale=8.0,
                                                           mlp_ratio=args.mlp_ratio, pred_res_flow=False)
         self.pixel_geneartor = BasicResPixelShuffleGenerator(nf, args.dec_res_blocks)   # (sic) reference attribute name
+        _conv.install_invalidation_hooks(self)
 
     @staticmethod
     def norm_w_rgb_mean(x0, x1):
@@ -98,6 +100,12 @@ class DATwConstantnCv1(nn.Module):
         return self._generate_frame(x0, x1, t)
 
     def forward(self, x0, x1, t):
+        """Training mode: differentiable (the blocks take the reference's piecewise composition over the backward kernels).
+        Eval mode with inputs that do not require grad is inference: run it without recording a graph even if the caller
+        forgot ``torch.no_grad()`` -- the training route materialises ~40 GB of sampled kv tensors per 1080p pair."""
+        if not self.training and not (x0.requires_grad or x1.requires_grad or t.requires_grad):
+            with torch.no_grad():
+                return self._generate_frame(x0, x1, t)
         return self._generate_frame(x0, x1, t)
 
     @torch.no_grad()

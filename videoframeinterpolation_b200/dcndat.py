@@ -197,4 +197,10 @@ class DCNDATv1(nn.Module):
         return self.generator(a1, mean_)
 
     def forward(self, x0, x1, t):
+        """Inference only: this archive model has no training route here (its DCN-with-given-offsets query builder and the
+        fused attention on final coordinates run forward kernels).  Asking for gradients raises instead of silently
+        returning a detached tensor."""
+        if torch.is_grad_enabled() and (self.training or x0.requires_grad or x1.requires_grad):
+            raise _lib.VfiError("DCNDATv1 is inference-only in vfi_b200: call .eval() and .inference(x0, x1, t) (or wrap the call "
+                                "in torch.no_grad()); gradients are not propagated through this model")
         return self.inference(x0, x1, t)

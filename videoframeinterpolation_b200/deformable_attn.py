@@ -285,9 +285,20 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
         return (out, self.conv_res_flow(mv0) + 2.0 * resize(ft0, scale_factor=2.0),
                 self.conv_res_flow(mv1) + 2.0 * resize(ft1, scale_factor=2.0))
 
+    def _wants_grad(self, *tensors) -> bool:
+        """The materialising training route is needed only when something can receive a gradient: with grad merely enabled
+        (model.eval()(x0, x1, t) without no_grad) the fused kernel still runs -- the (B, C, 2nS, HW) kv tensors of the
+        training route are ~40 GB per 1080p pair."""
+        if not torch.is_grad_enabled():
+            return False
+        return any(t.requires_grad for t in tensors) or (self.training and any(p.requires_grad for p in self.parameters()))
+
     def forward(self, feat_t, feat0, feat1, ft0, ft1):
-        if torch.is_grad_enabled():
+        if self._wants_grad(feat_t, feat0, feat1, ft0, ft1):
             return self._forward_autograd(feat_t, feat0, feat1, ft0, ft1)
+        if torch.is_grad_enabled():
+            with torch.no_grad():
+                return self.forward(feat_t, feat0, feat1, ft0, ft1)
         if self._split_ok(feat_t, feat0):
             mv0, mv1 = self._movement_feats_pair(feat_t, feat0, feat1, ft0, ft1)
         else:

@@ -6,7 +6,9 @@
 The reference JIT-compiles one NVRTC kernel per tensor shape and wraps it in cat / exp / multiply /
 zero-fill / slice / divide passes; here one C-ABI call does pre-scale + splat (csrc/splat.cu) and one
 does the divide -- or a single fused call (csrc/splat_fused.cu) when the flow statistics allow it.
-Backward (modules/softsplat.py:364-533) is not built yet: tensors that require grad raise.
+Backward (modules/softsplat.py:364-533): ``vfi_splat_bwd_f32`` behind ``_SplatSumFn``; with grad enabled and an input
+that requires grad, ``softsplat`` / ``fwarp`` and the two-frame / multi-branch wrappers of ``warp.py`` run the reference's
+own composition around that differentiable summation splat, so gradients reach tenIn, tenFlow and tenMetric.
 """
 from __future__ import annotations
 
@@ -72,16 +74,11 @@ def splat_last(tenIn, tenFlow, tenMetric, t, num, den, weight: str, eps_mode: st
     return num, mask.view(torch.bool)
 
 
-_ws_cache = {}
-
-
 def _workspace(dev, nbytes: int) -> torch.Tensor:
-    """Scratch for the gather-form splat (list heads + nodes), grown on demand and reused per device."""
-    ws = _ws_cache.get(dev)
-    if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        _ws_cache[dev] = ws
-    return ws
+    """Scratch for the gather-form splat (claim slots, list heads, nodes), allocated per call: the caching allocator makes
+    that nearly free and stream-ordered, so two streams / threads splatting on one device never share a buffer, and a
+    CUDA graph that captured a call keeps its own buffer alive (a cached global buffer could be replaced under it)."""
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=dev)
 
 
 def splat_fused(tenIn, tenFlow, tenMetric, weight: str, eps_mode: str, eps_value: float) -> torch.Tensor:

@@ -12,7 +12,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from .softsplat import softsplat, splat_accumulate, splat_last, splat_normalize
+from .softsplat import _SplatSumFn, softsplat, splat_accumulate, splat_last, splat_normalize
 
 __all__ = ["bwarp", "fwarp", "fwarp_using_two_frames", "fwarp_mframes"]
 
@@ -91,6 +91,17 @@ def _two_directions(num, den, tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMet
     return None
 
 
+def _needs_grad(*tensors) -> bool:
+    return torch.is_grad_enabled() and any(t is not None and torch.is_tensor(t) and t.requires_grad for t in tensors)
+
+
+def _one_direction_autograd(tenIn, tenFlow, td, tenMetric):
+    """modules/warp.py:69-73 / 91-96 over the differentiable summation splat (training route)."""
+    e = td * tenMetric.clip(-20.0, 20.0).exp()
+    out = _SplatSumFn.apply(torch.cat([tenIn * td * tenMetric.clip(-20.0, 20.0).exp(), e], 1), tenFlow)
+    return out[:, :-1], out[:, -1:] + 0.0000001
+
+
 def fwarp_using_two_frames(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1=None, tenMetric2=None):
     """Two-direction soft splat blended by t; returns (num / den, den < 1e-5).
 
@@ -100,6 +111,12 @@ def fwarp_using_two_frames(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric
     """
     assert tenMetric1 is not None and tenMetric2 is not None, "fwarp_using_two_frames needs both metrics"
     dev = _lib.require_cuda(tenIn1, tenFlow1, tenIn2, tenFlow2, tenMetric1, tenMetric2)
+    if _needs_grad(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2):
+        # training route: the reference's composition (modules/warp.py:68-83), gradients through vfi_splat_bwd_f32
+        of, nf = _one_direction_autograd(tenIn1, tenFlow1, t1, tenMetric1)
+        ob, nb = _one_direction_autograd(tenIn2, tenFlow2, t2, tenMetric2)
+        den_ = nf + nb
+        return (of + ob) / den_, den_ < 0.00001
     B, C, H, W = tenIn1.shape
     num = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
     den = torch.empty((B, 1, H, W), dtype=torch.float32, device=dev)
@@ -114,6 +131,14 @@ def fwarp_mframes(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMet
     """Many-to-many splatting: flows (n_branch,B,2,H,W), t (n_branch,B,1,1,1); inputs shared by branches."""
     dev = _lib.require_cuda(tenIn1, tenFlow1, tenIn2, tenFlow2, tenMetric1, tenMetric2)
     n_branch = tenFlow1.shape[0]
+    if _needs_grad(tenIn1, tenFlow1, t1, tenIn2, tenFlow2, t2, tenMetric1, tenMetric2):
+        # training route: modules/warp.py:86-114 over the differentiable summation splat
+        num_, den_ = 0, 0
+        for idx in range(n_branch):
+            of, nf = _one_direction_autograd(tenIn1, tenFlow1[idx], t1[idx], tenMetric1)
+            ob, nb = _one_direction_autograd(tenIn2, tenFlow2[idx], t2[idx], tenMetric2)
+            num_, den_ = num_ + (of + ob), den_ + (nf + nb)
+        return num_ / den_, den_ < 0.00001
     B, C, H, W = tenIn1.shape
     num = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
     den = torch.empty((B, 1, H, W), dtype=torch.float32, device=dev)
