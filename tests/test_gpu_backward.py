@@ -224,7 +224,7 @@ def test_eval_forward_without_no_grad_stays_on_the_fused_kernels_and_dcndat_refu
     assert not y.requires_grad
     assert "vfi_dattn_f32" in tm.records and "vfi_dsample_f32" not in tm.records, sorted(tm.records)
     with torch.no_grad():
-        assert torch.equal(y, net.inference(x0, x1, t))
+        assert rel_err(y, net.inference(x0, x1, t)) <= 1e-6      # same kernels; cuDNN may pick another algorithm on a repeat call
     net2 = v.DCNDATv1(v.dcndat_default_args(nf=32, enc_res_blocks=1, dec_res_blocks=1)).cuda().train()
     with pytest.raises(_lib.VfiError, match="inference-only"):
         net2(x0, x1, t)
