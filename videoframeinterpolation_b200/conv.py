@@ -202,8 +202,11 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tenso
         if slope is not None and prelu_weight.numel() == Cs:
             slope = _rolled(prelu if prelu is not None else conv, "_vfi_slope_rolled", slope, roll)
     _flops[0] += 2 * 9 * (Cin if in_slice is None else in_slice[1] - in_slice[0]) * Cout * B * H * W
+    tag = None
+    if _lib._timer is not None and getattr(_lib._timer, "detailed", False):     # per-shape rows for tools/conv_table.py
+        tag = f"conv3x3 {H}x{W} {Cin}->{Cout} res{mode} up{upscale} ps{ps}"
     _lib.call("vfi_conv3x3_f32", dev, x.data_ptr(), wp.data_ptr(), _lib.ptr(bias), _lib.ptr(slope), _lib.ptr(res), out.data_ptr(),
-              B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, out_c, res_c, mode, upscale, _lib.stream_ptr(dev))
+              B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, out_c, res_c, mode, upscale, _lib.stream_ptr(dev), tag=tag)
     return out
 
 
