@@ -186,7 +186,7 @@ __device__ __forceinline__ float median9(float* v) {
     return v[4];
 }
 
-__global__ void __launch_bounds__(kTileThreads) bwarp_tile_kernel(const __grid_constant__ CUtensorMap tmap,
+__global__ void __launch_bounds__(kTileThreads, 3) bwarp_tile_kernel(const __grid_constant__ CUtensorMap tmap,
                                                                   const float* __restrict__ img, const float* __restrict__ flow,
                                                                   const float* __restrict__ lin_x, const float* __restrict__ lin_y,
                                                                   float* __restrict__ out, int C, int H, int W, Str4 sf,
@@ -255,7 +255,13 @@ __global__ void __launch_bounds__(kTileThreads) bwarp_tile_kernel(const __grid_c
     }
 
     // ---- consumers: geometry of my 4 pixels (x = lane, lane+32; y = warp, warp+8) ----
-    TilePix px[4];
+    // Per pixel the plane loop needs ONE shared-memory address (the north-west tap; the other three are at the constant
+    // offsets +4, +kRW*4, +kRW*4+4 bytes) and the four weights.  The east / south neighbours are always read, also
+    // where the reference clamps them onto the border pixel itself (x1 = min(x0 + 1, W - 1)): their weight is exactly
+    // 0 there and the window holds TMA's zero fill beyond the frame, so the product is an exact 0.
+    uint32_t a_nw[4];
+    float w_nw[4], w_ne[4], w_sw[4], w_se[4];
+    bool ok[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const int xr = x_t0 + lane + 32 * (k & 1), yr = y_t0 + warp + 8 * (k >> 1);
@@ -263,35 +269,49 @@ __global__ void __launch_bounds__(kTileThreads) bwarp_tile_kernel(const __grid_c
         const int x = min(xr, W - 1), y = min(yr, H - 1);
         const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
         const BwarpGeom g = bwarp_geom(ld_stream(fp), ld_stream(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, fe);
-        const int lx0 = g.x0 - rx0, ly0 = g.y0 - ry0, lx1 = g.x1 - rx0, ly1 = g.y1 - ry0;
-        const bool inside = lx0 >= 0 && lx1 < kRW && ly0 >= 0 && ly1 < kRH;
+        const int lx0 = g.x0 - rx0, ly0 = g.y0 - ry0;
+        // a clamped neighbour (x1 == x0 or y1 == y0: frame border, or the edge of a crop) must carry weight 0 for the
+        // fixed +1 offsets to be right; inside a crop that is not the case, those pixels take the tail pass
+        const bool plus1 = (g.x1 == g.x0 + 1 || g.w_ne + g.w_se == 0.0f) && (g.y1 == g.y0 + 1 || g.w_sw + g.w_se == 0.0f);
+        const bool inside = lx0 >= 0 && lx0 + 1 < kRW && ly0 >= 0 && ly0 + 1 < kRH && plus1;
         if (valid && !inside) s_outlist[atomicAdd(&s_nout, 1)] = (unsigned short)((yr - y_t0) * kTW + (xr - x_t0));
-        px[k].o_s = ly0 * kRW + lx0;
-        px[k].o_g = g.y0 * W + g.x0;
-        px[k].dxy = (g.x1 - g.x0) | ((g.y1 - g.y0) << 1) | (inside ? 4 : 0) | (valid ? 8 : 0);
-        px[k].w_nw = g.w_nw;
-        px[k].w_ne = g.w_ne;
-        px[k].w_sw = g.w_sw;
-        px[k].w_se = g.w_se;
+        a_nw[k] = (uint32_t)((ly0 * kRW + lx0) * 4);
+        ok[k] = valid && inside;
+        w_nw[k] = g.w_nw;
+        w_ne[k] = g.w_ne;
+        w_sw[k] = g.w_sw;
+        w_se[k] = g.w_se;
     }
-
+    // output pointers of my two rows at plane c_begin (the second pixel of a row is 32 floats further)
+    float* op0 = out + ((int64_t)b * C + c_begin) * HW + (int64_t)(y_t0 + warp) * W + (x_t0 + lane);
+    float* op1 = op0 + (int64_t)8 * W;
+    const uint32_t stage_u32 = smem_u32(stage);
+    int s = 0;
+    uint32_t parity = 0;
     for (int c = 0; c < n_c; ++c) {
-        const int s = c % kStages;
-        mbar_wait(&full[s], (c / kStages) & 1);
-        const float* st = stage + (size_t)s * kStageFloats;
-        float* oplane = out + ((int64_t)b * C + c_begin + c) * HW;
+        mbar_wait(&full[s], parity);
+        const uint32_t sb = stage_u32 + (uint32_t)s * (kStageFloats * 4);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            if ((px[k].dxy & 12) == 12) {      // inside the frame, taps inside the window
-                const int dx = px[k].dxy & 1, dy = (px[k].dxy >> 1) & 1;
-                const float* p = st + px[k].o_s;
-                const float r = p[0] * px[k].w_nw + p[dx] * px[k].w_ne + p[dy * kRW] * px[k].w_sw + p[dy * kRW + dx] * px[k].w_se;
-                const int xr = x_t0 + lane + 32 * (k & 1), yr = y_t0 + warp + 8 * (k >> 1);
-                st_stream(oplane + (int64_t)yr * W + xr, r);
+            if (ok[k]) {
+                const uint32_t ad = sb + a_nw[k];
+                float v0, v1, v2, v3;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v0) : "r"(ad));
+                asm volatile("ld.shared.f32 %0, [%1+4];" : "=f"(v1) : "r"(ad));
+                asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v2) : "r"(ad), "n"(kRW * 4));
+                asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v3) : "r"(ad), "n"(kRW * 4 + 4));
+                const float r = v0 * w_nw[k] + v1 * w_ne[k] + v2 * w_sw[k] + v3 * w_se[k];
+                st_stream(((k >> 1) ? op1 : op0) + 32 * (k & 1), r);
             }
         }
+        op0 += HW;
+        op1 += HW;
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);
+        if (++s == kStages) {
+            s = 0;
+            parity ^= 1;
+        }
     }
 
     // ---- pixels whose taps left the window: direct gathers, all channels, after the streamed part ----
