@@ -162,7 +162,13 @@ __global__ void __launch_bounds__(256) bwarp_cl_kernel(const float* __restrict__
 constexpr int kTW = 64, kTH = 16, kHVX = VFI_BWARP_HVX, kHVY = VFI_BWARP_HVY;
 constexpr int kRW = kTW + 2 * kHVX, kRH = kTH + 2 * kHVY;   // 96 x 32 window
 constexpr int kStageFloats = kRW * kRH;
-constexpr int kStages = 6;
+#ifndef VFI_BWARP_STAGES
+#define VFI_BWARP_STAGES 6
+#endif
+#ifndef VFI_BWARP_CTAS
+#define VFI_BWARP_CTAS 2
+#endif
+constexpr int kStages = VFI_BWARP_STAGES;
 constexpr int kTileThreads = 288;
 
 struct TilePix {
@@ -186,7 +192,7 @@ __device__ __forceinline__ float median9(float* v) {
     return v[4];
 }
 
-__global__ void __launch_bounds__(kTileThreads, 3) bwarp_tile_kernel(const __grid_constant__ CUtensorMap tmap,
+__global__ void __launch_bounds__(kTileThreads, VFI_BWARP_CTAS) bwarp_tile_kernel(const __grid_constant__ CUtensorMap tmap,
                                                                   const float* __restrict__ img, const float* __restrict__ flow,
                                                                   const float* __restrict__ lin_x, const float* __restrict__ lin_y,
                                                                   float* __restrict__ out, int C, int H, int W, Str4 sf,
@@ -218,6 +224,18 @@ __global__ void __launch_bounds__(kTileThreads, 3) bwarp_tile_kernel(const __gri
             mbar_init(&empty[s], 8);
         }
         fence_mbar_init();
+    }
+    // my 4 pixels' flow vectors: issued before the probe barrier so that the two global-memory latencies of the prologue
+    // (probe flows -> window origin, pixel flows -> geometry) overlap instead of following each other
+    float my_fx[4], my_fy[4];
+    if (warp < 8) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int x = min(x_t0 + lane + 32 * (k & 1), W - 1), y = min(y_t0 + warp + 8 * (k >> 1), H - 1);
+            const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
+            my_fx[k] = ld_stream(fp);
+            my_fy[k] = ld_stream(fp + sf.c);
+        }
     }
     if (tid < 9) {   // 3x3 probe grid inside the tile
         const int px = min(x_t0 + (kTW / 6) * (1 + 2 * (tid % 3)), W - 1);
@@ -267,8 +285,7 @@ __global__ void __launch_bounds__(kTileThreads, 3) bwarp_tile_kernel(const __gri
         const int xr = x_t0 + lane + 32 * (k & 1), yr = y_t0 + warp + 8 * (k >> 1);
         const bool valid = xr < W && yr < H;
         const int x = min(xr, W - 1), y = min(yr, H - 1);
-        const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
-        const BwarpGeom g = bwarp_geom(ld_stream(fp), ld_stream(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, fe);
+        const BwarpGeom g = bwarp_geom(my_fx[k], my_fy[k], __ldg(lin_x + x), __ldg(lin_y + y), H, W, fe);
         const int lx0 = g.x0 - rx0, ly0 = g.y0 - ry0;
         // a clamped neighbour (x1 == x0 or y1 == y0: frame border, or the edge of a crop) must carry weight 0 for the
         // fixed +1 offsets to be right; inside a crop that is not the case, those pixels take the tail pass
@@ -282,6 +299,37 @@ __global__ void __launch_bounds__(kTileThreads, 3) bwarp_tile_kernel(const __gri
         w_sw[k] = g.w_sw;
         w_se[k] = g.w_se;
     }
+    // ---- pixels whose taps left the window: direct gathers, all channels, BEFORE the streamed part: the producer warp
+    // is filling the ring meanwhile, so these gathers run under the first TMA round trip instead of after the last ----
+    asm volatile("bar.sync 1, 256;" ::: "memory");   // consumers only (the producer warp is not part of it)
+    const int n_out = s_nout;
+    constexpr int kCh = 8;                             // channels per work item
+    const int n_chunks = (n_c + kCh - 1) / kCh;
+    for (int item = tid; item < n_out * n_chunks; item += 256) {   // empty when every tap is inside the window
+        const int pid = s_outlist[item / n_chunks], c0 = c_begin + (item % n_chunks) * kCh;
+        const int x = x_t0 + pid % kTW, y = y_t0 + pid / kTW;
+        const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
+        const BwarpGeom g = bwarp_geom(__ldg(fp), __ldg(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, fe);
+        const int o_nw = g.y0 * W + g.x0, o_ne = g.y0 * W + g.x1, o_sw = g.y1 * W + g.x0, o_se = g.y1 * W + g.x1;
+        const float* ip = img + ((int64_t)b * C + c0) * HW;
+        float* op = out + ((int64_t)b * C + c0) * HW + (int64_t)y * W + x;
+        const int cn = min(kCh, c_end - c0);
+        float v[kCh][4];
+#pragma unroll
+        for (int u = 0; u < kCh; ++u) {
+            if (u < cn) {
+                const float* p = ip + (int64_t)u * HW;
+                v[u][0] = ld_gather(p + o_nw);
+                v[u][1] = ld_gather(p + o_ne);
+                v[u][2] = ld_gather(p + o_sw);
+                v[u][3] = ld_gather(p + o_se);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kCh; ++u)
+            if (u < cn) st_stream(op + (int64_t)u * HW, v[u][0] * g.w_nw + v[u][1] * g.w_ne + v[u][2] * g.w_sw + v[u][3] * g.w_se);
+    }
+
     // output pointers of my two rows at plane c_begin (the second pixel of a row is 32 floats further)
     float* op0 = out + ((int64_t)b * C + c_begin) * HW + (int64_t)(y_t0 + warp) * W + (x_t0 + lane);
     float* op1 = op0 + (int64_t)8 * W;
@@ -314,36 +362,6 @@ __global__ void __launch_bounds__(kTileThreads, 3) bwarp_tile_kernel(const __gri
         }
     }
 
-    // ---- pixels whose taps left the window: direct gathers, all channels, after the streamed part ----
-    asm volatile("bar.sync 1, 256;" ::: "memory");   // consumers only (the producer warp is not part of it)
-    const int n_out = s_nout;
-    if (n_out == 0) return;
-    constexpr int kCh = 8;                             // channels per work item
-    const int n_chunks = (n_c + kCh - 1) / kCh;
-    for (int item = tid; item < n_out * n_chunks; item += 256) {
-        const int pid = s_outlist[item / n_chunks], c0 = c_begin + (item % n_chunks) * kCh;
-        const int x = x_t0 + pid % kTW, y = y_t0 + pid / kTW;
-        const float* fp = flow + b * sf.n + y * sf.h + x * sf.w;
-        const BwarpGeom g = bwarp_geom(__ldg(fp), __ldg(fp + sf.c), __ldg(lin_x + x), __ldg(lin_y + y), H, W, fe);
-        const int o_nw = g.y0 * W + g.x0, o_ne = g.y0 * W + g.x1, o_sw = g.y1 * W + g.x0, o_se = g.y1 * W + g.x1;
-        const float* ip = img + ((int64_t)b * C + c0) * HW;
-        float* op = out + ((int64_t)b * C + c0) * HW + (int64_t)y * W + x;
-        const int cn = min(kCh, c_end - c0);
-        float v[kCh][4];
-#pragma unroll
-        for (int u = 0; u < kCh; ++u) {
-            if (u < cn) {
-                const float* p = ip + (int64_t)u * HW;
-                v[u][0] = ld_gather(p + o_nw);
-                v[u][1] = ld_gather(p + o_ne);
-                v[u][2] = ld_gather(p + o_sw);
-                v[u][3] = ld_gather(p + o_se);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < kCh; ++u)
-            if (u < cn) st_stream(op + (int64_t)u * HW, v[u][0] * g.w_nw + v[u][1] * g.w_ne + v[u][2] * g.w_sw + v[u][3] * g.w_se);
-    }
 }
 
 struct TmapCacheEntry {
