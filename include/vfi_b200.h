@@ -165,7 +165,9 @@ int vfi_dattn_f32(const float* q, const float* feat0, const float* feat1, const 
  * (call sites modules/dcnv2.py:60-66, models/archive/DCNDAT.py:71-77).
  * x (B,Cin,H,W); offset (B, OG*2*kh*kw, Ho, Wo) interleaved (dy,dx); mask (B, OG*kh*kw, Ho, Wo) or NULL;
  * weight (Cout, Cin/WG, kh, kw); bias (Cout) or NULL; out (B,Cout,Ho,Wo).  No im2col buffer in HBM.
- * algo: 0 = auto, 1 = SIMT fp32 FFMA, 2 = tcgen05 3xTF32 (3x3/s1/p1/d1, Cin/WG in {8,9,16}).
+ * algo: 0 = auto, 1 = SIMT fp32 FFMA with global gathers, 2 = tcgen05 3xTF32 (3x3/s1/p1/d1, Cin/WG in {8,9,16}),
+ *       3 = SIMT fp32 FFMA on a TMA-staged shared-memory window (<= 3x3 taps, stride 1, dilation 1, W % 4 == 0; what
+ *       auto picks from 4096 output pixels up).
  */
 int vfi_dcn_f32(const float* x, const float* offset, const float* mask, const float* weight, const float* bias,
                 float* out, int B, int Cin, int Cout, int H, int W, int kh, int kw, int stride, int pad, int dil,

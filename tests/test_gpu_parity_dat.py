@@ -109,6 +109,39 @@ def test_dcn_vs_oracle_dim64(vfi):
     assert_close(out0, ref0, TOL, "dcn zero offsets == grouped conv")
 
 
+@pytest.mark.parametrize("cfg", [dict(C=64, WG=8, OG=8, H=72, W=96), dict(C=72, WG=8, OG=8, H=68, W=120), dict(C=64, WG=8, OG=4, H=64, W=64),
+                                 dict(C=72, WG=8, OG=4, H=40, W=104)])
+def test_dcn_window_kernel_vs_oracle(vfi, cfg):
+    """The TMA-window form of the DCN (csrc/dcn_win.cu; what algo='auto' runs from 4096 output pixels up): ragged tiles in
+    both directions, offset groups == and != weight groups (row a7), offsets with 2 % of the taps far outside the staged
+    window (global-gather fallback) and outside the frame, against torchvision's op through the oracle; the SIMT kernel
+    on the same inputs for comparison."""
+    from videoframeinterpolation_b200._lib import VfiError
+    C, WG, OG, H, W = cfg["C"], cfg["WG"], cfg["OG"], cfg["H"], cfg["W"]
+    kw = gc._dcn_op(f"win.{C}.{OG}", 2, C, C, H, W, WG=WG, OG=OG)
+    g = torch.Generator().manual_seed(C + OG)
+    far = torch.rand(kw["offset"].shape, generator=g) < 0.02
+    kw["offset"] = torch.where(far, (torch.rand(kw["offset"].shape, generator=g) * 2 - 1) * W, kw["offset"] * 2.0)
+    with oracle.library_ops():
+        ref = oracle.deform_conv2d(**kw)
+    k = cu_kw(kw)
+    out = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"], algo="window")
+    assert_close(out, ref, TOL, f"dcn window {cfg}")
+    auto = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"])
+    assert torch.equal(auto, out) == (H * W >= 4096), "auto must pick the window kernel from 4096 output pixels up"
+    simt = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"], algo="simt")
+    assert_close(simt, ref, TOL, f"dcn simt {cfg}")
+    # no mask, no bias
+    out2 = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], None, stride=1, padding=1, mask=None, algo="window")
+    with oracle.library_ops():
+        ref2 = oracle.deform_conv2d(kw["x"], kw["offset"], kw["weight"], None, stride=1, padding=1, dilation=1, mask=None)
+    assert_close(out2, ref2, TOL, f"dcn window, no mask / bias {cfg}")
+    # shapes the window form does not cover are refused when asked for explicitly (stride 2)
+    with pytest.raises(VfiError, match="does not cover"):
+        vfi.deform_conv2d(k["x"], k["offset"][:, :, ::2, ::2].contiguous(), k["weight"], k["bias"], stride=2, padding=1,
+                          mask=k["mask"][:, :, ::2, ::2].contiguous(), algo="window")
+
+
 # ---- sampler / attention -------------------------------------------------------------------------
 def test_dsample_golden(vfi, golden):
     from videoframeinterpolation_b200.deformable_attn import grouped_sample

@@ -95,6 +95,9 @@ int dcn_tc_supported(const DcnParams& p);
 int launch_dcn_tc(const float* x, const float* offset, const float* mask, const float* weight, const float* bias, float* out,
                   int B, const DcnParams& p, void* workspace, size_t workspace_bytes, cudaStream_t st);
 size_t dcn_tc_workspace_bytes(int B, const DcnParams& p);
+int dcn_win_supported(const DcnParams& p, const float* x);
+int launch_dcn_win(const float* x, const float* offset, const float* mask, const float* weight, const float* bias, float* out, int B,
+                   const DcnParams& p, cudaStream_t st);
 
 }  // namespace vfi
 
@@ -116,7 +119,7 @@ extern "C" size_t vfi_dcn_workspace_bytes(int B, int Cin, int Cout, int H, int W
                                           int n_offset_grps, int algo) {
     vfi::DcnParams p;
     if (dcn_fill_params(p, Cin, Cout, H, W, kh, kw, 1, (kh - 1) / 2, 1, n_weight_grps, n_offset_grps) != VFI_OK) return 0;
-    if (algo == 1) return 0;
+    if (algo == 1 || algo == 3) return 0;
     return vfi::dcn_tc_workspace_bytes(B, p);
 }
 
@@ -133,7 +136,13 @@ extern "C" int vfi_dcn_f32(const float* x, const float* offset, const float* mas
     if (rc) return rc;
     if (B == 0) return VFI_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    VFI_REQUIRE(algo >= 0 && algo <= 2, "vfi_dcn_f32: bad algo %d", algo);
+    VFI_REQUIRE(algo >= 0 && algo <= 3, "vfi_dcn_f32: bad algo %d", algo);
+    // window form (dcn_win.cu): the default wherever it applies and the image is large enough to pay for the staging
+    if (algo == 3 && !dcn_win_supported(p, x)) VFI_UNSUPPORTED("vfi_dcn_f32: window path does not cover this configuration");
+    if (algo == 3 || (algo == 0 && dcn_win_supported(p, x) && (int64_t)p.Ho * p.Wo >= 4096)) {
+        rc = launch_dcn_win(x, offset, mask, weight, bias, out, B, p, st);
+        if (rc != VFI_ERR_UNSUPPORTED) return rc;
+    }
     if (algo == 2 && !dcn_tc_supported(p)) VFI_UNSUPPORTED("vfi_dcn_f32: tcgen05 path does not cover this configuration");
     if (algo == 2 || (algo == 0 && dcn_tc_supported(p) == 2))
         return launch_dcn_tc(x, offset, mask, weight, bias, out, B, p, workspace, workspace_bytes, st);

@@ -20,7 +20,7 @@ from .warp import bwarp
 
 __all__ = ["deform_conv2d", "DeformableConv2d", "DeformableConv2dGivenOffset"]
 
-_ALGOS = {"auto": 0, "simt": 1, "tcgen05": 2}
+_ALGOS = {"auto": 0, "simt": 1, "tcgen05": 2, "window": 3}
 
 
 def _pair(v: Union[int, Tuple[int, int]]) -> int:
