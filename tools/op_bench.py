@@ -134,7 +134,7 @@ def run_dcn(a, dev, flush):
     OG = WG = 8
     g = torch.Generator().manual_seed(wl.seed_for(3, 0))
     x = torch.randn(B, C, H, W, generator=g).to(dev)
-    flow = wl.make_flow(B, H, W, 2.0, g, device="cpu")
+    flow = wl.make_flow(B, H, W, 2.0, g, device="cpu", outlier_frac=a.outliers)
     off = (2 * torch.tanh(torch.randn(B, OG * 18, H, W, generator=g)) + flow.flip(1).repeat(1, OG * 9, 1, 1)).to(dev)
     mask = torch.sigmoid(torch.randn(B, OG * 9, H, W, generator=g)).to(dev)
     wgt = (torch.randn(C, C // WG, 3, 3, generator=g) * 0.1).to(dev)
@@ -143,7 +143,7 @@ def run_dcn(a, dev, flush):
     fn = lambda: v.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask, algo=algo)
     ms, best = timeit(fn, a.iters, flush)
     flops = 2.0 * C * (C // WG) * 9 * B * H * W
-    report("dcn", dict(B=B, C=C, H=H, W=W, OG=OG, WG=WG, algo=algo), ms, best, wl.bytes_dcn(B, C, C, H, W, OG),
+    report("dcn", dict(B=B, C=C, H=H, W=W, OG=OG, WG=WG, algo=algo, outliers=a.outliers), ms, best, wl.bytes_dcn(B, C, C, H, W, OG),
            {"gemm_tflops": round(flops / ms / 1e9, 2)})
 
 
@@ -157,6 +157,7 @@ def main():
     ap.add_argument("--mode", default="soft")
     ap.add_argument("--flow", default="smooth", choices=["smooth", "gentle", "iid"])
     ap.add_argument("--layout", default="cl", choices=["cl", "planar"], help="dattn: channels-last (model) or planar tensors")
+    ap.add_argument("--outliers", type=float, default=0.02, help="dcn: fraction of pixels whose flow leaves the frame (SURVEY.md 8d: 2 %)")
     ap.add_argument("--no-flush", action="store_true")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)

@@ -144,14 +144,22 @@ dcn_win_kernel(const __grid_constant__ CUtensorMap xmap, const float* __restrict
                     }
                 }
             } else {
-                for (int cl = 0; cl < cin_g; ++cl) {
-                    const float v = dcn_sample(xb + (int64_t)cl * HW + tp.o, tp, p.W) * m;
-                    const float4* wr = reinterpret_cast<const float4*>(wt + cl * COGP);
+                // this pixel's tap lies outside the staged window (a flow outlier): all of the group's corner loads are
+                // issued before the first one is consumed, so the tap costs one global-memory round trip, not cin_g
+                float vv[16];
 #pragma unroll
-                    for (int o4 = 0; o4 < COGP / 4; ++o4) {
-                        const float4 wv = wr[o4];
-                        acc[2 * o4] = fma2s(pack2(wv.x, wv.y), v, acc[2 * o4]);
-                        acc[2 * o4 + 1] = fma2s(pack2(wv.z, wv.w), v, acc[2 * o4 + 1]);
+                for (int cl = 0; cl < 16; ++cl) vv[cl] = cl < cin_g ? dcn_sample(xb + (int64_t)cl * HW + tp.o, tp, p.W) : 0.0f;
+#pragma unroll
+                for (int cl = 0; cl < 16; ++cl) {
+                    if (cl < cin_g) {
+                        const float v = vv[cl] * m;
+                        const float4* wr = reinterpret_cast<const float4*>(wt + cl * COGP);
+#pragma unroll
+                        for (int o4 = 0; o4 < COGP / 4; ++o4) {
+                            const float4 wv = wr[o4];
+                            acc[2 * o4] = fma2s(pack2(wv.x, wv.y), v, acc[2 * o4]);
+                            acc[2 * o4 + 1] = fma2s(pack2(wv.z, wv.w), v, acc[2 * o4 + 1]);
+                        }
                     }
                 }
             }
