@@ -137,11 +137,13 @@ extern "C" int vfi_dcn_f32(const float* x, const float* offset, const float* mas
     if (B == 0) return VFI_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     VFI_REQUIRE(algo >= 0 && algo <= 3, "vfi_dcn_f32: bad algo %d", algo);
-    // window form (dcn_win.cu): the default wherever it applies and the image is large enough to pay for the staging
-    if (algo == 3 && !dcn_win_supported(p, x)) VFI_UNSUPPORTED("vfi_dcn_f32: window path does not cover this configuration");
-    if (algo == 3 || (algo == 0 && dcn_win_supported(p, x) && (int64_t)p.Ho * p.Wo >= 4096)) {
-        rc = launch_dcn_win(x, offset, mask, weight, bias, out, B, p, st);
-        if (rc != VFI_ERR_UNSUPPORTED) return rc;
+    // window form (dcn_win.cu), opt-in: 1.5x the SIMT kernel when (nearly) every tap falls into the staged window --
+    // offsets predicted by a network around a smooth flow, as in the DCNDAT blocks -- but slower when a few per cent of
+    // the pixels carry frame-leaving offsets (each such lane serialises its warp on global round trips: measured 8.9 ms
+    // against 3.7 ms at BASELINE configs[2] with SURVEY.md 8(d)'s 2 % outliers, 2.5 against 3.7 ms without them)
+    if (algo == 3) {
+        if (!dcn_win_supported(p, x)) VFI_UNSUPPORTED("vfi_dcn_f32: window path does not cover this configuration");
+        return launch_dcn_win(x, offset, mask, weight, bias, out, B, p, st);
     }
     if (algo == 2 && !dcn_tc_supported(p)) VFI_UNSUPPORTED("vfi_dcn_f32: tcgen05 path does not cover this configuration");
     if (algo == 2 || (algo == 0 && dcn_tc_supported(p) == 2))

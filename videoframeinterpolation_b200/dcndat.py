@@ -28,7 +28,7 @@ from . import _lib
 from . import conv as _conv
 from .blocks import (BasicResPixelShuffleGenerator, FeadForward, HalfChannelConv5ResBlock, SameChannelResEncoder,
                      conv_bias_act, conv_prelu, flow_up2_add, resize, run_conv_chain)
-from .dcnv2 import DeformableConv2d, DeformableConv2dGivenOffset, deform_conv2d
+from .dcnv2 import DeformableConv2d, DeformableConv2dGivenOffset, deform_conv2d, window_or_auto
 from .deformable_attn import (Attn, fused_deformable_attention, fused_supported, grouped_sample, movement_feats_pair,
                               movement_split_ok)
 from .warp import bwarp
@@ -145,8 +145,9 @@ class DCNCrossDeformableAttentionBlockwFlow(nn.Module):
         rc = self.query_enhancer_dcn.regular_conv
         feat0, feat1 = _lib.planar(feat0), _lib.planar(feat1)      # gathered by the DCN and by the attention: one transpose each
         b, c, fh, fw = feat_t.shape
-        parts = (deform_conv2d(feat0, off0, rc.weight, rc.bias, padding=1, mask=m0), feat_t,
-                 deform_conv2d(feat1, off1, rc.weight, rc.bias, padding=1, mask=m1))
+        algo = window_or_auto(feat0, rc.weight)       # offsets = 2 tanh(.) + a smooth flow: the staged window holds the taps
+        parts = (deform_conv2d(feat0, off0, rc.weight, rc.bias, padding=1, mask=m0, algo=algo), feat_t,
+                 deform_conv2d(feat1, off1, rc.weight, rc.bias, padding=1, mask=m1, algo=algo))
         q = self._blend_query(parts)
         if fused_supported(self.in_c, self.n_groups, self.n_heads):
             attended = fused_deformable_attention(q, feat0, feat1, c0.reshape(b, -1, fh, fw), c1.reshape(b, -1, fh, fw), None, None,

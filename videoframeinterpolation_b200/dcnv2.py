@@ -108,6 +108,15 @@ def deform_conv2d(input: torch.Tensor, offset: torch.Tensor, weight: torch.Tenso
     return out
 
 
+def window_or_auto(x: torch.Tensor, weight: torch.Tensor, stride: int = 1) -> str:
+    """'window' (csrc/dcn_win.cu) for the network-predicted offsets of the DCN blocks when the shape is covered and large
+    enough to pay for the window staging, else 'auto'."""
+    if (stride == 1 and x.dim() == 4 and x.shape[2] * x.shape[3] >= 4096 and x.shape[3] % 4 == 0 and weight.shape[2] <= 3
+            and weight.shape[3] <= 3 and weight.shape[1] <= 16 and weight.shape[0] * weight.shape[1] // max(x.shape[1], 1) <= 16):
+        return "window"
+    return "auto"
+
+
 class DeformableConv2d(nn.Module):
     """DCNv2 block: flow head -> bwarp -> offset/mask head -> modulated deformable conv.  Returns (out, flow)."""
 
@@ -152,4 +161,4 @@ class DeformableConv2dGivenOffset(nn.Module):
         # same permute / flip / view as models/archive/DCNDAT.py:69 (channel order is the reference's, quirks included)
         offset = offset.permute(0, 2, 1, 3, 4).flip(1).contiguous().view(b, -1, fh, fw)
         return deform_conv2d(x, offset, self.regular_conv.weight, self.regular_conv.bias, stride=self.stride,
-                             padding=self.padding, mask=torch.sigmoid(mask))
+                             padding=self.padding, mask=torch.sigmoid(mask), algo=window_or_auto(x, self.regular_conv.weight))
