@@ -23,8 +23,6 @@
 // frame 1 -- that one lands under phases C / D, the epilogue and the next prologue.
 #include <stdlib.h>
 
-#include <type_traits>
-
 #include "dattn_common.cuh"
 #include "tma.cuh"
 #include "umma.cuh"
@@ -534,361 +532,6 @@ dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant_
     }
 }
 
-// One sample of one (pixel, group): coordinate replay of sampler_geom (sampler.cuh) in frame coordinates, then the four
-// bilinear taps of the group's GC channels from the shared-memory window (fast path) or from global memory (the lane's
-// sample left the window).  raw (dx, dy) = conv_res_offset output + bias.
-template <int GC, bool PAD, int REC, int CF>
-__device__ __forceinline__ void window_sample(float dx, float dy, float ftx, float fty, float lxv, float lyv, const DattnArgs& a,
-                                              const WinGeom& w, float wm1, float hm1, float half_h, float xmax, float ymax, int ox,
-                                              int oy, uint32_t win_g, const float* __restrict__ featg, int gsh, float (&xs)[GC]) {
-    constexpr int GCP = (GC + 3) & ~3;
-    constexpr int LDV = PAD ? GCP / 4 : (((GC * 7) & 3) + GC + 3) / 4;
-    dx = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dx)), ftx);
-    dy = __fadd_rn(__fmul_rn(a.offset_scale, tanhf(dy)), fty);
-    const float gx = __fadd_rn(lxv, __fmul_rn(div_rn(dx, wm1, w.r_wm1), 0.5f));
-    const float gy = __fadd_rn(lyv, div_rn(dy, half_h, w.r_half_h));
-    float ix = __fmul_rn(__fmul_rn(__fadd_rn(gx, 1.0f), 0.5f), wm1);
-    float iy = __fmul_rn(__fmul_rn(__fadd_rn(gy, 1.0f), 0.5f), hm1);
-    const bool finite = isfinite(ix) && isfinite(iy);
-    ix = fminf(fmaxf(finite ? ix : -2.0f, -2.0f), xmax);
-    iy = fminf(fmaxf(finite ? iy : -2.0f, -2.0f), ymax);
-    const float xf = floorf(ix), yf = floorf(iy);
-    const float tx_ = ix - xf, ty_ = iy - yf;
-    const float ex = 1.0f - tx_, ey = 1.0f - ty_;
-    const float w_nw = ey * ex, w_ne = ey * tx_, w_sw = ty_ * ex, w_se = ty_ * tx_;
-    const int x0 = (int)xf - a.fe.x0, y0 = (int)yf - a.fe.y0;      // crop coordinates
-    const int wx = x0 - ox, wy = y0 - oy;                          // window coordinates
-    const bool in_win = (unsigned)wx <= (unsigned)(w.Ww - 2) && (unsigned)wy <= (unsigned)(w.Hw - 2);
-    if (in_win) {
-        const uint32_t an = win_g + (uint32_t)(wy * w.Ww + wx) * (REC * 4);
-        const uint32_t as = an + w.row_bytes;
-        f32x2 v[2 * LDV], t[2 * LDV];
-#pragma unroll
-        for (int k = 0; k < LDV; ++k) lds_v2u64(an + 16 * k, t[2 * k], t[2 * k + 1]);
-#pragma unroll
-        for (int k = 0; k < 2 * LDV; ++k) v[k] = mul2s(t[k], w_nw);
-#pragma unroll
-        for (int k = 0; k < LDV; ++k) lds_v2u64(an + REC * 4 + 16 * k, t[2 * k], t[2 * k + 1]);
-#pragma unroll
-        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_ne, v[k]);
-#pragma unroll
-        for (int k = 0; k < LDV; ++k) lds_v2u64(as + 16 * k, t[2 * k], t[2 * k + 1]);
-#pragma unroll
-        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_sw, v[k]);
-#pragma unroll
-        for (int k = 0; k < LDV; ++k) lds_v2u64(as + REC * 4 + 16 * k, t[2 * k], t[2 * k + 1]);
-#pragma unroll
-        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_se, v[k]);
-        float vf[4 * LDV];
-#pragma unroll
-        for (int k = 0; k < 2 * LDV; ++k) unpack2(v[k], vf[2 * k], vf[2 * k + 1]);
-        if constexpr (PAD) {
-#pragma unroll
-            for (int cc = 0; cc < GC; ++cc) xs[cc] = vf[cc];
-        } else {
-            // my group's GC channels start gsh = (GC g) & 3 floats into the aligned block
-#pragma unroll
-            for (int cc = 0; cc < GC; ++cc) {
-                const float s01 = (gsh & 1) ? vf[(cc + 1) % (4 * LDV)] : vf[cc];
-                const float s23 = (gsh & 1) ? vf[(cc + 3) % (4 * LDV)] : vf[(cc + 2) % (4 * LDV)];
-                xs[cc] = (gsh & 2) ? s23 : s01;
-            }
-        }
-    } else {
-        const bool in_x0 = (unsigned)x0 < (unsigned)a.W, in_x1 = (unsigned)(x0 + 1) < (unsigned)a.W;
-        const bool in_y0 = (unsigned)y0 < (unsigned)a.H, in_y1 = (unsigned)(y0 + 1) < (unsigned)a.H;
-        const float* pn = featg + gsh + ((int64_t)y0 * a.W + x0) * CF;
-        const float* ps = pn + (int64_t)a.W * CF;
-#pragma unroll
-        for (int cc = 0; cc < GC; ++cc) {
-            float r = 0.0f;
-            if (in_x0 && in_y0) r = __ldg(pn + cc) * w_nw;
-            if (in_x1 && in_y0) r = fmaf(__ldg(pn + CF + cc), w_ne, r);
-            if (in_x0 && in_y1) r = fmaf(__ldg(ps + cc), w_sw, r);
-            if (in_x1 && in_y1) r = fmaf(__ldg(ps + CF + cc), w_se, r);
-            xs[cc] = r;
-        }
-    }
-}
-
-// ---- third form: lane = (pixel, head), sampled values exchanged through shared memory ------------------------------------
-// In dattn_win_kernel lane (p, g) keeps kt / yv of ALL 8 heads for its group's 9 channels, so every slot needs a 3-round
-// shuffle reduce-scatter of the partial logits and an 8-shuffle all-gather of the softmax weights: 4-7 dependent
-// latency hops per slot with two warps per scheduler to hide them (ncu: 23 % of the loop's stall samples sit on the
-// FADDs behind those shuffles).  Here lane (p, h) keeps kt_h / yv_h of ITS head for all 72 channels (the same 144
-// registers) and what is exchanged is the sampled vector itself: every lane stores the 9 values it sampled
-// (group g = h) into a per-warp shared-memory record, and after ONE __syncwarp reads the pixel's 72 values back with
-// 18 broadcast LDS.128.  Logit, softmax state and weighted accumulation are then lane-local: no shuffles, no selects
-// between lanes, and the prologue / epilogue projections are lane-local too.
-template <int GC, bool PAD>
-struct HxCfg {
-    static constexpr int NG = 8;
-    static constexpr int C = GC * NG;
-    static constexpr int GCP = (GC + 3) & ~3;
-    static constexpr int CF = PAD ? NG * GCP : C;
-    static constexpr int CF4 = (CF + 3) / 4;
-    static constexpr int REC4 = (CF4 & 1) ? CF4 : CF4 + 1;
-    static constexpr int REC = REC4 * 4;
-    static constexpr int LDV = (((GC * (NG - 1)) & 3) + GC + 3) / 4;
-    static constexpr int THREADS = 256;
-    static constexpr int WS = C + 4;                  // weight row stride: GC * WS = 12 (mod 32): the 8 heads' rows do not collide
-    static constexpr int WMAT = C * WS;
-    static constexpr int XS = C + 4;                  // exchange record stride per pixel
-    static constexpr int XBUF = 8 * 2 * 4 * XS;       // [warp][slot of the pair][pixel][XS]
-    static constexpr int OB = 512;
-    static constexpr int MISC = 16;
-    static constexpr int FIXED_FLOATS = 3 * WMAT + XBUF + OB + MISC;
-    static_assert(C % 4 == 0 && (GC * WS) % 32 == 12, "layout assumptions");
-};
-
-template <int GC, bool PAD>
-__global__ void __launch_bounds__(HxCfg<GC, PAD>::THREADS, 1)
-dattn_hx_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1, DattnArgs a, WinGeom w) {
-    using Cfg = HxCfg<GC, PAD>;
-    constexpr int NG = 8, C = Cfg::C, T = Cfg::THREADS, REC = Cfg::REC, LDV = Cfg::LDV, WS = Cfg::WS, XS = Cfg::XS;
-    constexpr int CF = Cfg::CF, GCP = Cfg::GCP, NP = C / 2;      // NP channel pairs
-    extern __shared__ __align__(128) uint8_t smem_raw[];
-    uint8_t* smem_al = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
-    float* win = reinterpret_cast<float*>(smem_al);                     // [Hw][Ww][REC]
-    float* Wq_s = win + (size_t)w.Ww * w.Hw * REC;                      // [C][WS] row-major, as given
-    float* Wk_s = Wq_s + Cfg::WMAT;
-    float* Wv_s = Wk_s + Cfg::WMAT;
-    float* xbuf = Wv_s + Cfg::WMAT;                                     // [warp][2][4][XS]
-    float* ob_s = xbuf + Cfg::XBUF;                                     // [s][g][2] bias of the offset head
-    int* org = reinterpret_cast<int*>(ob_s + Cfg::OB);                  // [3][2]
-    uint64_t* wbar = reinterpret_cast<uint64_t*>(org + 8);
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int g = lane & 7, p = lane >> 3;     // g: the group I sample == the head I own
-    const int64_t HW = (int64_t)a.H * a.W;
-    const float scale = rsqrtf((float)GC);
-    const int nS = a.nS;
-    const int tiles_per_img = a.tiles_x * a.tiles_y;
-    const int64_t n_tiles = (int64_t)a.B * tiles_per_img;
-
-    if (threadIdx.x == 0) {
-        mbar_init(wbar, 1);
-        fence_mbar_init();
-        tma_prefetch_desc(&tm0);
-        tma_prefetch_desc(&tm1);
-    }
-    for (int i = threadIdx.x; i < C * WS; i += T) {
-        const int r = i / WS, c = i - r * WS;
-        const bool ok = c < C;
-        Wq_s[i] = ok ? __ldg(a.Wq + r * C + c) : 0.0f;
-        Wk_s[i] = ok ? __ldg(a.Wk + r * C + c) : 0.0f;
-        Wv_s[i] = ok ? __ldg(a.Wv + r * C + c) : 0.0f;
-    }
-    for (int i = threadIdx.x; i < NG * nS * 2; i += T) {
-        const int xy = i & 1, gg = (i >> 1) & 7, s = i >> 4;
-        ob_s[i] = a.obias != nullptr ? __ldg(a.obias + (gg * nS + s) * 2 + xy) : 0.0f;
-    }
-    __syncthreads();
-    if ((int64_t)blockIdx.x < n_tiles && warp == 0) {      // first window of this CTA
-        const int b = (int)(blockIdx.x / tiles_per_img);
-        const int trem = (int)(blockIdx.x - (int64_t)b * tiles_per_img);
-        int ox, oy;
-        window_origin(a, w, 0, b, trem % a.tiles_x, trem / a.tiles_x, lane, ox, oy);
-        if (lane == 0) {
-            mbar_arrive_expect_tx(wbar, w.box_bytes);
-            tma_load_4d(win, &tm0, wbar, 0, ox, oy, b);
-        }
-    }
-    uint32_t wphase = 0;
-
-    const float wm1 = (float)(a.fe.Wg - 1), hm1 = (float)(a.fe.Hg - 1);
-    const float half_h = (float)((a.fe.Hg - 1.0) / 2.0);
-    const float xmax = (float)a.fe.Wg + 1.0f, ymax = (float)a.fe.Hg + 1.0f;
-    const int gbase = PAD ? g * GCP : ((g * GC) & ~3), gsh = PAD ? 0 : ((g * GC) & 3);
-    const uint32_t win_g = smem_u32(win) + gbase * 4;
-    float* xw = xbuf + warp * (2 * 4 * XS);                   // this warp's exchange records
-    float* xmine = xw + p * XS + g * GC;                      // where I store my 9 values (slot 0; slot 1 is 4 * XS further)
-    const float* xpix = xw + p * XS;                          // where I read my pixel's 72 values
-    const float* Wq_h = Wq_s + (g * GC) * WS;
-    const float* Wk_h = Wk_s + (g * GC) * WS;
-    const float* Wv_h = Wv_s + (g * GC) * WS;
-
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int b = (int)(tile / tiles_per_img);
-        const int trem = (int)(tile - (int64_t)b * tiles_per_img);
-        const int ty = trem / a.tiles_x, tx = trem - ty * a.tiles_x;
-        const int x_raw = tx * kWinTW + (warp & 1) * 4 + p, y_raw = ty * kWinTH + (warp >> 1);
-        const bool live = x_raw < a.W && y_raw < a.H;
-        const int x = min(x_raw, a.W - 1), y = min(y_raw, a.H - 1);
-        const int64_t pix = (int64_t)y * a.W + x;
-        const int64_t tile_next = tile + gridDim.x;
-        const bool has_next = tile_next < n_tiles;
-        const int b_next = has_next ? (int)(tile_next / tiles_per_img) : 0;
-
-        if (warp < 2) {
-            int ox, oy;
-            window_origin(a, w, warp, b, tx, ty, lane, ox, oy);
-            if (lane == 0) { org[2 * warp] = ox; org[2 * warp + 1] = oy; }
-        } else if (warp == 2 && has_next) {
-            const int trn = (int)(tile_next - (int64_t)b_next * tiles_per_img);
-            int ox, oy;
-            window_origin(a, w, 0, b_next, trn % a.tiles_x, trn / a.tiles_x, lane, ox, oy);
-            if (lane == 0) { org[4] = ox; org[5] = oy; }
-        }
-
-        // ---- prologue (lane-local): qp_h = Wq_h q + bq_h;  kt_h = scale * Wk_h^T qp_h;  cb = scale * qp_h . bk_h ----
-        f32x2 kt2[NP];       // kt_h[2i], kt_h[2i+1]
-        float cb;
-        {
-            float qp[GC];
-#pragma unroll
-            for (int j = 0; j < GC; ++j) qp[j] = __ldg(a.bq + g * GC + j);
-            if (a.qo_cl & 1) {
-                const float4* qv4 = reinterpret_cast<const float4*>(a.q + ((int64_t)b * HW + pix) * C);
-#pragma unroll 3
-                for (int c4 = 0; c4 < C / 4; ++c4) {
-                    const float4 qv = __ldg(qv4 + c4);
-#pragma unroll
-                    for (int j = 0; j < GC; ++j) {
-                        const float4 wv = *reinterpret_cast<const float4*>(Wq_h + j * WS + 4 * c4);
-                        qp[j] = fmaf(wv.x, qv.x, qp[j]);
-                        qp[j] = fmaf(wv.y, qv.y, qp[j]);
-                        qp[j] = fmaf(wv.z, qv.z, qp[j]);
-                        qp[j] = fmaf(wv.w, qv.w, qp[j]);
-                    }
-                }
-            } else {
-                const float* qpl = a.q + (int64_t)b * C * HW + pix;
-#pragma unroll 2
-                for (int c = 0; c < C; ++c) {
-                    const float qv = __ldg(qpl + (int64_t)c * HW);
-#pragma unroll
-                    for (int j = 0; j < GC; ++j) qp[j] = fmaf(Wq_h[j * WS + c], qv, qp[j]);
-                }
-            }
-            cb = 0.0f;
-#pragma unroll
-            for (int j = 0; j < GC; ++j) {
-                cb = fmaf(qp[j], __ldg(a.bk + g * GC + j), cb);
-                qp[j] *= scale;
-            }
-            cb *= scale;
-#pragma unroll
-            for (int i = 0; i < NP; ++i) kt2[i] = 0ull;
-#pragma unroll
-            for (int j = 0; j < GC; ++j) {
-#pragma unroll
-                for (int c4 = 0; c4 < C / 4; ++c4) {
-                    const float4 wv = *reinterpret_cast<const float4*>(Wk_h + j * WS + 4 * c4);
-                    kt2[2 * c4] = fma2s(pack2(wv.x, wv.y), qp[j], kt2[2 * c4]);
-                    kt2[2 * c4 + 1] = fma2s(pack2(wv.z, wv.w), qp[j], kt2[2 * c4 + 1]);
-                }
-            }
-        }
-        __syncthreads();   // org[] of this tile visible
-        const int org_f1x = org[2], org_f1y = org[3], org_nx = org[4], org_ny = org[5];
-
-        f32x2 yv2[NP];       // sum_s p_h[s] * x_s[2i], x_s[2i+1]
-#pragma unroll
-        for (int i = 0; i < NP; ++i) yv2[i] = 0ull;
-        float m_ref = -INFINITY, sum = 0.0f;
-        const float lxv = __ldg(a.lin_x + x), lyv = __ldg(a.lin_y + y);
-
-        for (int f = 0; f < 2; ++f) {
-            const float* fp = a.ft[f] + b * a.ft_sn + y * a.ft_sh + x * a.ft_sw;
-            const float ftx = __ldg(fp), fty = __ldg(fp + a.ft_sc);
-            const int ox = f == 0 ? org[0] : org_f1x, oy = f == 0 ? org[1] : org_f1y;
-            const float* offcl = a.offs[f] + ((int64_t)b * HW + pix) * (NG * nS * 2) + (int64_t)g * nS * 2;
-            const float* featg = a.feat[f] + (int64_t)b * HW * CF + gbase;
-            float4 od_a = ld_stream4(offcl), od_b = ld_stream4(offcl + 4);
-            mbar_wait(wbar, wphase);       // window (tile, f) has landed
-            wphase ^= 1;
-            float4 oc_a = od_a, oc_b = od_b;
-            for (int s0 = 0; s0 < nS; s0 += 2) {
-                if ((s0 & 2) == 0) {
-                    oc_a = od_a;
-                    oc_b = od_b;
-                    if (s0 + 4 < nS) {
-                        od_a = ld_stream4(offcl + 2 * (s0 + 4));
-                        od_b = ld_stream4(offcl + 2 * (s0 + 4) + 4);
-                    }
-                }
-                const float4 oc = (s0 & 2) ? oc_b : oc_a;
-                // ---- both slots of the pair: sample my group's channels, publish them to my pixel's record ----
-                __syncwarp();                       // the previous pair's records have been read by every lane
-#pragma unroll
-                for (int si = 0; si < 2; ++si) {
-                    const float2 ob = *reinterpret_cast<const float2*>(ob_s + ((s0 + si) * NG + g) * 2);
-                    float xs[GC];
-                    window_sample<GC, PAD, REC, CF>(__fadd_rn(si == 0 ? oc.x : oc.z, ob.x), __fadd_rn(si == 0 ? oc.y : oc.w, ob.y), ftx, fty,
-                                                    lxv, lyv, a, w, wm1, hm1, half_h, xmax, ymax, ox, oy, win_g, featg, gsh, xs);
-#pragma unroll
-                    for (int cc = 0; cc < GC; ++cc) xmine[si * (4 * XS) + cc] = xs[cc];
-                }
-                __syncwarp();
-                // ---- per slot: logit of my head over the pixel's 72 sampled values, softmax state, weighted accumulation ----
-#pragma unroll
-                for (int si = 0; si < 2; ++si) {
-                    f32x2 xv[NP];
-#pragma unroll
-                    for (int c4 = 0; c4 < C / 4; ++c4) {
-                        const float4 v4 = *reinterpret_cast<const float4*>(xpix + si * (4 * XS) + 4 * c4);
-                        xv[2 * c4] = pack2(v4.x, v4.y);
-                        xv[2 * c4 + 1] = pack2(v4.z, v4.w);
-                    }
-                    f32x2 d0 = 0ull, d1 = 0ull, d2 = 0ull, d3 = 0ull;
-#pragma unroll
-                    for (int i = 0; i < NP; i += 4) {
-                        d0 = fma2(kt2[i], xv[i], d0);
-                        d1 = fma2(kt2[i + 1], xv[i + 1], d1);
-                        d2 = fma2(kt2[i + 2], xv[i + 2], d2);
-                        d3 = fma2(kt2[i + 3], xv[i + 3], d3);
-                    }
-                    float e0, e1, e2, e3, e4, e5, e6, e7;
-                    unpack2(d0, e0, e1); unpack2(d1, e2, e3); unpack2(d2, e4, e5); unpack2(d3, e6, e7);
-                    const float lg = (((e0 + e1) + (e2 + e3)) + ((e4 + e5) + (e6 + e7))) + cb;
-                    if (lg - m_ref > 30.0f) {          // lazy re-base of the softmax shift (first slot: m_ref = -inf)
-                        const float alpha = expf(m_ref - lg);
-                        m_ref = lg;
-                        sum *= alpha;
-                        const f32x2 a2 = pack2(alpha, alpha);
-#pragma unroll
-                        for (int i = 0; i < NP; ++i) yv2[i] = mul2(yv2[i], a2);
-                    }
-                    const float pw = expf(lg - m_ref);
-                    sum += pw;
-#pragma unroll
-                    for (int i = 0; i < NP; ++i) yv2[i] = fma2s(xv[i], pw, yv2[i]);
-                }
-            }
-            __syncthreads();       // every warp is done with the window of (tile, f): start the next load
-            if (threadIdx.x == 0) {
-                if (f == 0) {
-                    mbar_arrive_expect_tx(wbar, w.box_bytes);
-                    tma_load_4d(win, &tm1, wbar, 0, org_f1x, org_f1y, b);
-                } else if (has_next) {
-                    mbar_arrive_expect_tx(wbar, w.box_bytes);
-                    tma_load_4d(win, &tm0, wbar, 0, org_nx, org_ny, b_next);
-                }
-            }
-        }
-
-        // ---- epilogue (lane-local): out_h = Wv_h (y_h / sum_h) + bv_h ----
-        const float inv = 1.0f / sum;
-        const int64_t o_sp = (a.qo_cl & 2) ? C : 1, o_sc = (a.qo_cl & 2) ? 1 : HW;
-        float* op = a.out + (int64_t)b * C * HW + pix * o_sp + (g * GC) * o_sc;
-#pragma unroll
-        for (int j = 0; j < GC; ++j) {
-            f32x2 d0 = 0ull, d1 = 0ull;
-#pragma unroll
-            for (int c4 = 0; c4 < C / 4; ++c4) {
-                const float4 wv = *reinterpret_cast<const float4*>(Wv_h + j * WS + 4 * c4);
-                d0 = fma2(pack2(wv.x, wv.y), yv2[2 * c4], d0);
-                d1 = fma2(pack2(wv.z, wv.w), yv2[2 * c4 + 1], d1);
-            }
-            float e0, e1, e2, e3;
-            unpack2(d0, e0, e1); unpack2(d1, e2, e3);
-            const float o = (e0 + e1) + (e2 + e3);
-            if (live) st_stream(op + (int64_t)j * o_sc, fmaf(o, inv, __ldg(a.bv + g * GC + j)));
-        }
-    }
-}
-
 // tensor maps of the two channels-last feature maps: box {REC, Ww, Hw, 1} of dims {C, W, H, B}
 struct WinTmapEntry {
     const void* base;
@@ -919,9 +562,9 @@ static int get_win_tmap(const float* feat, int B, int H, int W, int C, int rec, 
     return VFI_OK;
 }
 
-template <int GC, bool PAD, bool HX>
+template <int GC, bool PAD>
 static int launch_win(const DattnArgs& a_in, cudaStream_t st) {
-    using Cfg = typename std::conditional<HX, HxCfg<GC, PAD>, WinCfg<GC, PAD>>::type;
+    using Cfg = WinCfg<GC, PAD>;
     DattnArgs a = a_in;
     // reach of the residual offsets around pixel + flow (module comment): RX columns / RY rows on either side
     const int RX = (int)ceilf(a.offset_scale * 0.25f), RY = (int)ceilf(a.offset_scale);
@@ -959,16 +602,14 @@ static int launch_win(const DattnArgs& a_in, cudaStream_t st) {
     if (rc) return rc;
     static thread_local size_t smem_set = 0;
     if (smem > smem_set) {
-        if (HX) VFI_CUDA(cudaFuncSetAttribute(dattn_hx_kernel<GC, PAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        else VFI_CUDA(cudaFuncSetAttribute(dattn_win_kernel<GC, PAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VFI_CUDA(cudaFuncSetAttribute(dattn_win_kernel<GC, PAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set = smem;
     }
     a.tiles_x = (int)ceil_div(a.W, kWinTW);
     a.tiles_y = (int)ceil_div(a.H, kWinTH);
     const int64_t tiles = (int64_t)a.B * a.tiles_x * a.tiles_y;
     const int blocks = (int)min64(tiles, (int64_t)kNumSMs);
-    if (HX) dattn_hx_kernel<GC, PAD><<<blocks, Cfg::THREADS, smem, st>>>(*tm0, *tm1, a, w);
-    else dattn_win_kernel<GC, PAD><<<blocks, Cfg::THREADS, smem, st>>>(*tm0, *tm1, a, w);
+    dattn_win_kernel<GC, PAD><<<blocks, Cfg::THREADS, smem, st>>>(*tm0, *tm1, a, w);
     VFI_CHECK_LAUNCH("dattn_win_kernel");
     return VFI_OK;
 }
@@ -985,14 +626,7 @@ int launch_dattn_win(const DattnArgs& a, int C, int nG, cudaStream_t st) {
          reinterpret_cast<uintptr_t>(a.offs[1])) & 15)
         return VFI_ERR_UNSUPPORTED;
     if (a.fe.Wg < 2 || a.fe.Hg < 2) return VFI_ERR_UNSUPPORTED;      // degenerate normalisation: the gather kernel handles it
-    static const int form = [] {       // VFI_DATTN_FORM=shfl: the shuffle form (dattn_win_kernel); default: the exchange form
-        const char* e = getenv("VFI_DATTN_FORM");
-        return (e && e[0] == 's') ? 0 : 1;
-    }();
-    if (C == 72 && nG == 8) {
-        if (form == 1) return a.feat_cl == 2 ? launch_win<9, true, true>(a, st) : launch_win<9, false, true>(a, st);
-        return a.feat_cl == 2 ? launch_win<9, true, false>(a, st) : launch_win<9, false, false>(a, st);
-    }
+    if (C == 72 && nG == 8) return a.feat_cl == 2 ? launch_win<9, true>(a, st) : launch_win<9, false>(a, st);
     return VFI_ERR_UNSUPPORTED;
 }
 
