@@ -150,16 +150,9 @@ int vfi_attn_f32(const float* q, const float* kv, const float* Wq, const float* 
  *   (csrc/dattn_win.cu; the reach of the residual offsets is bounded by offset_scale); covered shapes:
  *   vfi_dattn_win_covers (C = 72, nG = 8, raw channels-last offsets, nS % 4 == 0, offset_scale <= 16) -- others return
  *   VFI_ERR_UNSUPPORTED and the caller passes planar features.
- * feat_channels_last == 2: as 1, but feat0 / feat1 are GROUP-PADDED channels-last maps (B, H, W, nG * 12) written by
- *   vfi_dattn_pack_f32 (group g's 9 channels at [12g, 12g + 9), zeros behind): a tap is then 2 x LDS.128 + 1 x LDS.32 of
- *   exactly the group's channels (19 % fewer shared-memory wavefronts, no per-lane alignment select).
  * Requires nG == nH (true for every block the reference instantiates; madat.py:121 asserts it).
  */
 int vfi_dattn_win_covers(int C, int nG, int nS, float offset_scale, int coords_final, int offs_channels_last);
-/* feat (B, H, W, C) channels-last with a pixel stride of feat_pix_stride floats -> out (B, H, W, nG * roundup4(C / nG)),
- * 16-byte aligned: the group-padded layout of vfi_dattn_f32(feat_channels_last = 2).  No reference counterpart: a layout
- * change in front of modules/deformable_attn.py:88-101's sampler. */
-int vfi_dattn_pack_f32(const float* feat, float* out, int B, int C, int H, int W, int nG, int64_t feat_pix_stride, void* stream);
 int vfi_dattn_f32(const float* q, const float* feat0, const float* feat1, const float* offs0, const float* offs1,
                   const float* ft0, const float* ft1, const int64_t ft_strides[4],
                   const float* Wq, const float* bq, const float* Wk, const float* bk, const float* Wv,

@@ -35,7 +35,6 @@ SIGNATURES = {
     "vfi_attn_f32": (c_int, [c_void_p] * 11 + [c_int] * 6 + [c_void_p]),
     "vfi_dattn_f32": (c_int, [c_void_p] * 19 + [c_int] * 7 + [c_float, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "vfi_dattn_win_covers": (c_int, [c_int, c_int, c_int, c_float, c_int, c_int]),
-    "vfi_dattn_pack_f32": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_int64, c_void_p]),
     "vfi_dcn_f32": (c_int, [c_void_p] * 6 + [c_int] * 13 + [c_void_p, c_size_t, c_void_p]),
     "vfi_dcn_workspace_bytes": (c_size_t, [c_int] * 10),
     "vfi_bias_act_f32": (c_int, [c_void_p] * 5 + [c_int] * 6 + [c_void_p]),

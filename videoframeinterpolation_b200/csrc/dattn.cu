@@ -403,7 +403,7 @@ extern "C" int vfi_dattn_f32(const float* q, const float* feat0, const float* fe
     a.coords_final = coords_final;
     a.tw_log2 = 5; a.tiles_x = a.tiles_y = 0; a.zero = 0;
     a.fe = frame_ext_of(frame_ext, H, W);
-    a.feat_cl = feat_channels_last == 2 ? 2 : (feat_channels_last ? 1 : 0);
+    a.feat_cl = feat_channels_last ? 1 : 0;
     VFI_REQUIRE(frame_ext_ok(a.fe, H, W), "vfi_dattn_f32: the crop does not lie inside the frame");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int gc = C / nG;

@@ -20,8 +20,7 @@ struct DattnArgs {
     int tiles_x, tiles_y;
     int zero;                 // always 0 (see the sampling loop)
     FrameExt fe;              // frame extent + origin of this crop in it (whole frame: {W, H, 0, 0})
-    int feat_cl;              // window form only: 1 = feat0 / feat1 are channels-last (B, H, W, C); 2 = group-padded
-                              // channels-last (B, H, W, nG * 12) as vfi_dattn_pack_f32 writes them
+    int feat_cl;              // feat0 / feat1 are channels-last (B, H, W, C) -- window form only
 };
 
 constexpr int cmax(int a, int b) { return a > b ? a : b; }

@@ -52,18 +52,13 @@ constexpr int kWinTW = 8, kWinTH = 4;   // pixel tile of a CTA (8 warps x 4 hori
 
 // Shared-memory plan (floats).  Row / block strides are padded so that the 8 lanes of a pixel (one per group, reading 8
 // different rows / blocks with LDS.128) fall into 8 different bank quads.
-// PAD: the feature maps are group-padded channels-last, (B, H, W, NG * GCP) with group g's GC channels at [g*GCP, g*GCP+GC)
-// and zeros behind them (written by dattn_pack_kernel): a group's channels then start 16-byte aligned, a tap is
-// GC/4 LDS.128 + (GC%4) LDS.32 of exactly its channels, and the per-lane alignment select of the dense layout disappears.
-template <int GC, bool PAD = false>
+template <int GC>
 struct WinCfg {
     static constexpr int NG = 8;
     static constexpr int C = GC * NG;
     static constexpr int C4 = (C + 3) & ~3;
     static constexpr int GCP = (GC + 3) & ~3;
-    static constexpr int CF = PAD ? NG * GCP : C;                        // floats per pixel of the feature map
-    static constexpr int CF4 = (CF + 3) / 4;
-    static constexpr int REC4 = (CF4 & 1) ? CF4 : CF4 + 1;              // window record length in 16-byte units, odd
+    static constexpr int REC4 = ((C4 / 4) & 1) ? C4 / 4 : C4 / 4 + 1;   // window record length in 16-byte units, odd
     static constexpr int REC = REC4 * 4;
     static constexpr int LDV = (((GC * (NG - 1)) & 3) + GC + 3) / 4;     // LDS.128 per tap covering any group's channels
     static constexpr int THREADS = 256;                                 // 8 warps x (4 pixels x 8 groups)
@@ -130,10 +125,10 @@ __device__ __forceinline__ float reduce_scatter8(const float (&d)[8], int g) {
 // logits and the exchange of the softmax weights are warp shuffles among the 8 lanes of a pixel, so the sample loop has
 // NO block barrier: the 8 warps of a CTA (8x4 pixel tile) drift freely and cover each other's latencies; they meet only
 // to swap the window (once per frame).
-template <int GC, bool PAD>
-__global__ void __launch_bounds__(WinCfg<GC, PAD>::THREADS, 1)
+template <int GC>
+__global__ void __launch_bounds__(WinCfg<GC>::THREADS, 1)
 dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1, DattnArgs a, WinGeom w) {
-    using Cfg = WinCfg<GC, PAD>;
+    using Cfg = WinCfg<GC>;
     constexpr int NG = 8, C = Cfg::C, GCP = Cfg::GCP, T = Cfg::THREADS, REC = Cfg::REC, LDV = Cfg::LDV;
     constexpr int WQS = Cfg::WQS, WTB = Cfg::WTB, HP = NG / 2;
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -192,9 +187,7 @@ dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant_
     const float wm1 = (float)(a.fe.Wg - 1), hm1 = (float)(a.fe.Hg - 1);
     const float half_h = (float)((a.fe.Hg - 1.0) / 2.0);
     const float xmax = (float)a.fe.Wg + 1.0f, ymax = (float)a.fe.Hg + 1.0f;
-    // dense layout: aligned channel base of my group + shift inside it; padded layout: the group starts aligned
-    const int gbase = PAD ? g * GCP : ((g * GC) & ~3), gsh = PAD ? 0 : ((g * GC) & 3);
-    constexpr int CF = Cfg::CF;
+    const int gbase = (g * GC) & ~3, gsh = (g * GC) & 3;                // aligned channel base of my group, shift inside it
     const uint32_t win_g = smem_u32(win) + gbase * 4;
     const float* WkT_g = WkT_s + g * WTB;
     const float* WvT_g = WvT_s + g * WTB;
@@ -303,7 +296,7 @@ dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant_
             const float ftx = __ldg(fp), fty = __ldg(fp + a.ft_sc);
             const int ox = f == 0 ? org[0] : org_f1x, oy = f == 0 ? org[1] : org_f1y;
             const float* offcl = a.offs[f] + ((int64_t)b * HW + pix) * (NG * nS * 2) + (int64_t)g * nS * 2;
-            const float* featg = a.feat[f] + (int64_t)b * HW * CF + gbase;     // channels-last, my group's aligned base
+            const float* featg = a.feat[f] + (int64_t)b * HW * C + gbase;      // channels-last, my group's aligned base
             // raw offsets of my group: 4 slots (32 B, one sector) per load group, loaded one group (two iterations of the
             // pair loop) ahead of their use
             float4 od_a = ld_stream4(offcl), od_b = ld_stream4(offcl + 4);
@@ -346,105 +339,56 @@ dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant_
                     const int x0 = (int)xf - a.fe.x0, y0 = (int)yf - a.fe.y0;      // crop coordinates
                     const int wx = x0 - ox, wy = y0 - oy;                          // window coordinates
                     const bool in_win = (unsigned)wx <= (unsigned)(w.Ww - 2) && (unsigned)wy <= (unsigned)(w.Hw - 2);
-                    if constexpr (PAD) {
-                        // group-padded records: 2 x LDS.128 + 1 x LDS.32 are exactly my 9 channels, in order
-                        static_assert(!PAD || GC == 9, "padded tap code is written for 9 channels per group");
-                        if (in_win) {
-                            const uint32_t an = win_g + (uint32_t)(wy * w.Ww + wx) * (REC * 4);
-                            const uint32_t as = an + w.row_bytes;
-                            f32x2 v[4], t[4];
-                            float v8, t8;
-                            lds_v2u64(an, t[0], t[1]); lds_v2u64(an + 16, t[2], t[3]);
-                            asm volatile("ld.shared.f32 %0, [%1+32];" : "=f"(t8) : "r"(an));
+                    f32x2 v[2 * LDV];
+                    if (in_win) {
+                        const uint32_t an = win_g + (uint32_t)(wy * w.Ww + wx) * (REC * 4);
+                        const uint32_t as = an + w.row_bytes;
+                        f32x2 t[2 * LDV];
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) v[k] = mul2s(t[k], w_nw);
-                            v8 = t8 * w_nw;
-                            lds_v2u64(an + REC * 4, t[0], t[1]); lds_v2u64(an + REC * 4 + 16, t[2], t[3]);
-                            asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(t8) : "r"(an), "n"(REC * 4 + 32));
+                        for (int k = 0; k < LDV; ++k) lds_v2u64(an + 16 * k, t[2 * k], t[2 * k + 1]);
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) v[k] = fma2s(t[k], w_ne, v[k]);
-                            v8 = fmaf(t8, w_ne, v8);
-                            lds_v2u64(as, t[0], t[1]); lds_v2u64(as + 16, t[2], t[3]);
-                            asm volatile("ld.shared.f32 %0, [%1+32];" : "=f"(t8) : "r"(as));
+                        for (int k = 0; k < 2 * LDV; ++k) v[k] = mul2s(t[k], w_nw);
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) v[k] = fma2s(t[k], w_sw, v[k]);
-                            v8 = fmaf(t8, w_sw, v8);
-                            lds_v2u64(as + REC * 4, t[0], t[1]); lds_v2u64(as + REC * 4 + 16, t[2], t[3]);
-                            asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(t8) : "r"(as), "n"(REC * 4 + 32));
+                        for (int k = 0; k < LDV; ++k) lds_v2u64(an + REC * 4 + 16 * k, t[2 * k], t[2 * k + 1]);
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) v[k] = fma2s(t[k], w_se, v[k]);
-                            v8 = fmaf(t8, w_se, v8);
+                        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_ne, v[k]);
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) unpack2(v[k], xs[si][2 * k], xs[si][2 * k + 1]);
-                            xs[si][8] = v8;
-                        } else {
-                            // this lane's sample lies outside the window (flow discontinuity): gather from global memory
-                            const bool in_x0 = (unsigned)x0 < (unsigned)a.W, in_x1 = (unsigned)(x0 + 1) < (unsigned)a.W;
-                            const bool in_y0 = (unsigned)y0 < (unsigned)a.H, in_y1 = (unsigned)(y0 + 1) < (unsigned)a.H;
-                            const float* pn = featg + ((int64_t)y0 * a.W + x0) * CF;
-                            const float* ps = pn + (int64_t)a.W * CF;
+                        for (int k = 0; k < LDV; ++k) lds_v2u64(as + 16 * k, t[2 * k], t[2 * k + 1]);
 #pragma unroll
-                            for (int cc = 0; cc < GC; ++cc) {
-                                float r = 0.0f;
-                                if (in_x0 && in_y0) r = __ldg(pn + cc) * w_nw;
-                                if (in_x1 && in_y0) r = fmaf(__ldg(pn + CF + cc), w_ne, r);
-                                if (in_x0 && in_y1) r = fmaf(__ldg(ps + cc), w_sw, r);
-                                if (in_x1 && in_y1) r = fmaf(__ldg(ps + CF + cc), w_se, r);
-                                xs[si][cc] = r;
-                            }
-                        }
+                        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_sw, v[k]);
+#pragma unroll
+                        for (int k = 0; k < LDV; ++k) lds_v2u64(as + REC * 4 + 16 * k, t[2 * k], t[2 * k + 1]);
+#pragma unroll
+                        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_se, v[k]);
                     } else {
-                        f32x2 v[2 * LDV];
-                        if (in_win) {
-                            const uint32_t an = win_g + (uint32_t)(wy * w.Ww + wx) * (REC * 4);
-                            const uint32_t as = an + w.row_bytes;
-                            f32x2 t[2 * LDV];
-    #pragma unroll
-                            for (int k = 0; k < LDV; ++k) lds_v2u64(an + 16 * k, t[2 * k], t[2 * k + 1]);
-    #pragma unroll
-                            for (int k = 0; k < 2 * LDV; ++k) v[k] = mul2s(t[k], w_nw);
-    #pragma unroll
-                            for (int k = 0; k < LDV; ++k) lds_v2u64(an + REC * 4 + 16 * k, t[2 * k], t[2 * k + 1]);
-    #pragma unroll
-                            for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_ne, v[k]);
-    #pragma unroll
-                            for (int k = 0; k < LDV; ++k) lds_v2u64(as + 16 * k, t[2 * k], t[2 * k + 1]);
-    #pragma unroll
-                            for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_sw, v[k]);
-    #pragma unroll
-                            for (int k = 0; k < LDV; ++k) lds_v2u64(as + REC * 4 + 16 * k, t[2 * k], t[2 * k + 1]);
-    #pragma unroll
-                            for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_se, v[k]);
-                        } else {
-                            // this lane's sample lies outside the window (flow discontinuity): gather from global memory
-                            const bool in_x0 = (unsigned)x0 < (unsigned)a.W, in_x1 = (unsigned)(x0 + 1) < (unsigned)a.W;
-                            const bool in_y0 = (unsigned)y0 < (unsigned)a.H, in_y1 = (unsigned)(y0 + 1) < (unsigned)a.H;
-                            const float4* pn = reinterpret_cast<const float4*>(featg + ((int64_t)y0 * a.W + x0) * C);
-                            const float4* ps = pn + (int64_t)a.W * (C / 4);
-                            const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    #pragma unroll
-                            for (int k = 0; k < LDV; ++k) {
-                                const float4 tnw = (in_x0 && in_y0) ? __ldg(pn + k) : z4;
-                                const float4 tne = (in_x1 && in_y0) ? __ldg(pn + C / 4 + k) : z4;
-                                const float4 tsw = (in_x0 && in_y1) ? __ldg(ps + k) : z4;
-                                const float4 tse = (in_x1 && in_y1) ? __ldg(ps + C / 4 + k) : z4;
-                                f32x2 r0 = mul2s(pack2(tnw.x, tnw.y), w_nw), r1 = mul2s(pack2(tnw.z, tnw.w), w_nw);
-                                r0 = fma2s(pack2(tne.x, tne.y), w_ne, r0); r1 = fma2s(pack2(tne.z, tne.w), w_ne, r1);
-                                r0 = fma2s(pack2(tsw.x, tsw.y), w_sw, r0); r1 = fma2s(pack2(tsw.z, tsw.w), w_sw, r1);
-                                r0 = fma2s(pack2(tse.x, tse.y), w_se, r0); r1 = fma2s(pack2(tse.z, tse.w), w_se, r1);
-                                v[2 * k] = r0; v[2 * k + 1] = r1;
-                            }
+                        // this lane's sample lies outside the window (flow discontinuity): gather from global memory
+                        const bool in_x0 = (unsigned)x0 < (unsigned)a.W, in_x1 = (unsigned)(x0 + 1) < (unsigned)a.W;
+                        const bool in_y0 = (unsigned)y0 < (unsigned)a.H, in_y1 = (unsigned)(y0 + 1) < (unsigned)a.H;
+                        const float4* pn = reinterpret_cast<const float4*>(featg + ((int64_t)y0 * a.W + x0) * C);
+                        const float4* ps = pn + (int64_t)a.W * (C / 4);
+                        const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+                        for (int k = 0; k < LDV; ++k) {
+                            const float4 tnw = (in_x0 && in_y0) ? __ldg(pn + k) : z4;
+                            const float4 tne = (in_x1 && in_y0) ? __ldg(pn + C / 4 + k) : z4;
+                            const float4 tsw = (in_x0 && in_y1) ? __ldg(ps + k) : z4;
+                            const float4 tse = (in_x1 && in_y1) ? __ldg(ps + C / 4 + k) : z4;
+                            f32x2 r0 = mul2s(pack2(tnw.x, tnw.y), w_nw), r1 = mul2s(pack2(tnw.z, tnw.w), w_nw);
+                            r0 = fma2s(pack2(tne.x, tne.y), w_ne, r0); r1 = fma2s(pack2(tne.z, tne.w), w_ne, r1);
+                            r0 = fma2s(pack2(tsw.x, tsw.y), w_sw, r0); r1 = fma2s(pack2(tsw.z, tsw.w), w_sw, r1);
+                            r0 = fma2s(pack2(tse.x, tse.y), w_se, r0); r1 = fma2s(pack2(tse.z, tse.w), w_se, r1);
+                            v[2 * k] = r0; v[2 * k + 1] = r1;
                         }
-                        float vf[4 * LDV];
-    #pragma unroll
-                        for (int k = 0; k < 2 * LDV; ++k) unpack2(v[k], vf[2 * k], vf[2 * k + 1]);
-                        // my group's GC channels start gsh = (9 g) & 3 = g & 3 floats into the aligned block
-    #pragma unroll
-                        for (int cc = 0; cc < GC; ++cc) {
-                            const float s01 = (gsh & 1) ? vf[(cc + 1) % (4 * LDV)] : vf[cc];
-                            const float s23 = (gsh & 1) ? vf[(cc + 3) % (4 * LDV)] : vf[(cc + 2) % (4 * LDV)];
-                            xs[si][cc] = (gsh & 2) ? s23 : s01;
-                        }
+                    }
+                    float vf[4 * LDV];
+#pragma unroll
+                    for (int k = 0; k < 2 * LDV; ++k) unpack2(v[k], vf[2 * k], vf[2 * k + 1]);
+                    // my group's GC channels start gsh = (9 g) & 3 = g & 3 floats into the aligned block
+#pragma unroll
+                    for (int cc = 0; cc < GC; ++cc) {
+                        const float s01 = (gsh & 1) ? vf[(cc + 1) % (4 * LDV)] : vf[cc];
+                        const float s23 = (gsh & 1) ? vf[(cc + 3) % (4 * LDV)] : vf[(cc + 2) % (4 * LDV)];
+                        xs[si][cc] = (gsh & 2) ? s23 : s01;
                     }
                     // ---- partial logits of all heads over my channels, summed over the 8 groups of the pixel ----
                     float d[NG];
@@ -562,9 +506,9 @@ static int get_win_tmap(const float* feat, int B, int H, int W, int C, int rec, 
     return VFI_OK;
 }
 
-template <int GC, bool PAD>
+template <int GC>
 static int launch_win(const DattnArgs& a_in, cudaStream_t st) {
-    using Cfg = WinCfg<GC, PAD>;
+    using Cfg = WinCfg<GC>;
     DattnArgs a = a_in;
     // reach of the residual offsets around pixel + flow (module comment): RX columns / RY rows on either side
     const int RX = (int)ceilf(a.offset_scale * 0.25f), RY = (int)ceilf(a.offset_scale);
@@ -596,20 +540,20 @@ static int launch_win(const DattnArgs& a_in, cudaStream_t st) {
     w.r_half_h = (float)(1.0 / (double)(float)((a.fe.Hg - 1.0) / 2.0));
     const size_t smem = fixed + w.box_bytes;
     const CUtensorMap *tm0 = nullptr, *tm1 = nullptr;
-    int rc = get_win_tmap(a.feat[0], a.B, a.H, a.W, Cfg::CF, Cfg::REC, w.Ww, w.Hw, &tm0);
+    int rc = get_win_tmap(a.feat[0], a.B, a.H, a.W, Cfg::C, Cfg::REC, w.Ww, w.Hw, &tm0);
     if (rc) return rc;
-    rc = get_win_tmap(a.feat[1], a.B, a.H, a.W, Cfg::CF, Cfg::REC, w.Ww, w.Hw, &tm1);
+    rc = get_win_tmap(a.feat[1], a.B, a.H, a.W, Cfg::C, Cfg::REC, w.Ww, w.Hw, &tm1);
     if (rc) return rc;
     static thread_local size_t smem_set = 0;
     if (smem > smem_set) {
-        VFI_CUDA(cudaFuncSetAttribute(dattn_win_kernel<GC, PAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VFI_CUDA(cudaFuncSetAttribute(dattn_win_kernel<GC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set = smem;
     }
     a.tiles_x = (int)ceil_div(a.W, kWinTW);
     a.tiles_y = (int)ceil_div(a.H, kWinTH);
     const int64_t tiles = (int64_t)a.B * a.tiles_x * a.tiles_y;
     const int blocks = (int)min64(tiles, (int64_t)kNumSMs);
-    dattn_win_kernel<GC, PAD><<<blocks, Cfg::THREADS, smem, st>>>(*tm0, *tm1, a, w);
+    dattn_win_kernel<GC><<<blocks, Cfg::THREADS, smem, st>>>(*tm0, *tm1, a, w);
     VFI_CHECK_LAUNCH("dattn_win_kernel");
     return VFI_OK;
 }
@@ -626,48 +570,8 @@ int launch_dattn_win(const DattnArgs& a, int C, int nG, cudaStream_t st) {
          reinterpret_cast<uintptr_t>(a.offs[1])) & 15)
         return VFI_ERR_UNSUPPORTED;
     if (a.fe.Wg < 2 || a.fe.Hg < 2) return VFI_ERR_UNSUPPORTED;      // degenerate normalisation: the gather kernel handles it
-    if (C == 72 && nG == 8) return a.feat_cl == 2 ? launch_win<9, true>(a, st) : launch_win<9, false>(a, st);
+    if (C == 72 && nG == 8) return launch_win<9>(a, st);
     return VFI_ERR_UNSUPPORTED;
 }
-
-// (B, H, W, C) channels-last -> (B, H, W, nG * GCP): group g's C/nG channels at [g*GCP, g*GCP + C/nG), zeros behind them
-__global__ void __launch_bounds__(256) dattn_pack_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t npix, int C,
-                                                         int nG, int x_pix_stride) {
-    const int gc = C / nG, gcp = (gc + 3) & ~3, q4 = nG * gcp / 4;          // float4 chunks per output pixel
-    const int64_t total = npix * q4;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t pix = i / q4;
-        const int q = (int)(i - pix * q4);
-        const int g = (q * 4) / gcp, c0 = q * 4 - g * gcp;
-        const float* src = x + pix * x_pix_stride + g * gc + c0;
-        float4 v;
-        v.x = c0 + 0 < gc ? __ldg(src + 0) : 0.0f;
-        v.y = c0 + 1 < gc ? __ldg(src + 1) : 0.0f;
-        v.z = c0 + 2 < gc ? __ldg(src + 2) : 0.0f;
-        v.w = c0 + 3 < gc ? __ldg(src + 3) : 0.0f;
-        st_stream4(out + i * 4, v);
-    }
-}
-
-}  // namespace vfi
-
-extern "C" int vfi_dattn_pack_f32(const float* feat, float* out, int B, int C, int H, int W, int nG, int64_t feat_pix_stride,
-                                  void* stream) {
-    using namespace vfi;
-    if (B == 0) return VFI_OK;
-    VFI_REQUIRE(feat && out, "vfi_dattn_pack_f32: null pointer");
-    VFI_REQUIRE(B >= 1 && C >= 1 && H >= 1 && W >= 1 && nG >= 1 && C % nG == 0 && feat_pix_stride >= C,
-                "vfi_dattn_pack_f32: bad shape");
-    VFI_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, "vfi_dattn_pack_f32: out must be 16-byte aligned");
-    const int64_t npix = (int64_t)B * H * W;
-    const int q4 = nG * (((C / nG) + 3) & ~3) / 4;
-    const int blocks = (int)min64(ceil_div(npix * q4, 256), (int64_t)kNumSMs * 16);
-    dattn_pack_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(feat, out, npix, C, nG, (int)feat_pix_stride);
-    VFI_CHECK_LAUNCH("dattn_pack_kernel");
-    return VFI_OK;
-}
-
-namespace vfi {
-
 
 }  // namespace vfi

@@ -77,15 +77,6 @@ def _dense_nhwc(t: torch.Tensor) -> bool:
     return tuple(t.stride()) == (H * W * C, 1, W * C, C)
 
 
-def _pack_groups(feat: torch.Tensor, n_groups: int) -> torch.Tensor:
-    """Dense channels-last (B,C,H,W view of B,H,W,C) -> group-padded (B, H, W, nG * roundup4(C / nG)) buffer."""
-    B, C, H, W = feat.shape
-    gcp = (C // n_groups + 3) // 4 * 4
-    out = torch.empty((B, H, W, n_groups * gcp), dtype=torch.float32, device=feat.device)
-    _lib.call("vfi_dattn_pack_f32", feat.device, feat.data_ptr(), out.data_ptr(), B, C, H, W, n_groups, C, _lib.stream_ptr(feat.device))
-    return out
-
-
 def _w2d(w: torch.Tensor) -> torch.Tensor:
     return _lib.f32c(w.reshape(w.shape[0], -1))
 
@@ -149,14 +140,7 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
                and os.environ.get("VFI_DATTN_ALGO", "win") != "gather"
                and bool(_lib.lib().vfi_dattn_win_covers(c, n_groups, n_samples, float(offset_scale), 1 if coords_final else 0,
                                                         1 if offs_cl else 0)))
-    feat_mode = 0
-    if feat_cl:
-        feat_mode = 1
-        if os.environ.get("VFI_DATTN_ALGO", "win") != "win_dense" and c // n_groups == 9:
-            # group-padded copies (12 floats per group): a tap of the window kernel becomes 2 LDS.128 + 1 LDS.32
-            feat0, feat1 = _pack_groups(feat0, n_groups), _pack_groups(feat1, n_groups)
-            feat_mode = 2
-    else:
+    if not feat_cl:
         feat0, feat1 = _lib.planar(feat0), _lib.planar(feat1)
     assert offs0.numel() == b * n_groups * n_samples * 2 * fh * fw and offs1.numel() == offs0.numel(), "offset shape"
     if not coords_final:
@@ -180,7 +164,7 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
               _w2d(wq).data_ptr(), _lib.f32c(bq).data_ptr(), _w2d(wk).data_ptr(), _lib.f32c(bk).data_ptr(), _w2d(wv).data_ptr(),
               _lib.f32c(bv).data_ptr(), lin_x.data_ptr(), lin_y.data_ptr(), out.data_ptr(), _lib.ptr(s0), _lib.ptr(s1),
               b, c, fh, fw, n_groups, n_samples, n_heads, float(offset_scale), 1 if coords_final else 0, _lib.ptr(offs_bias),
-              1 if offs_cl else 0, 1 if q_cl else 0, 1 if out_cl else 0, feat_mode, ext, _lib.stream_ptr(dev))
+              1 if offs_cl else 0, 1 if q_cl else 0, 1 if out_cl else 0, 1 if feat_cl else 0, ext, _lib.stream_ptr(dev))
     return (out, s0, s1) if want_scores else out
 
 
