@@ -188,7 +188,7 @@ dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant_
     const float half_h = (float)((a.fe.Hg - 1.0) / 2.0);
     const float xmax = (float)a.fe.Wg + 1.0f, ymax = (float)a.fe.Hg + 1.0f;
     const int gbase = (g * GC) & ~3, gsh = (g * GC) & 3;                // aligned channel base of my group, shift inside it
-    const float* win_gp = win + gbase;
+    const uint32_t win_g = smem_u32(win) + gbase * 4;
     const float* WkT_g = WkT_s + g * WTB;
     const float* WvT_g = WvT_s + g * WTB;
 
@@ -341,39 +341,25 @@ dattn_win_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant_
                     const bool in_win = (unsigned)wx <= (unsigned)(w.Ww - 2) && (unsigned)wy <= (unsigned)(w.Hw - 2);
                     f32x2 v[2 * LDV];
                     if (in_win) {
-                        // plain shared-memory loads (not asm volatile): the compiler may hoist the second slot's taps above
-                        // the first slot's arithmetic -- the loop is latency bound, every overlapped LDS round trip counts
-                        const float* pn = win_gp + (wy * w.Ww + wx) * REC;
-                        const float* ps = pn + w.Ww * REC;
-                        float4 t[LDV];
+                        const uint32_t an = win_g + (uint32_t)(wy * w.Ww + wx) * (REC * 4);
+                        const uint32_t as = an + w.row_bytes;
+                        f32x2 t[2 * LDV];
 #pragma unroll
-                        for (int k = 0; k < LDV; ++k) t[k] = *reinterpret_cast<const float4*>(pn + 4 * k);
+                        for (int k = 0; k < LDV; ++k) lds_v2u64(an + 16 * k, t[2 * k], t[2 * k + 1]);
 #pragma unroll
-                        for (int k = 0; k < LDV; ++k) {
-                            v[2 * k] = mul2s(pack2(t[k].x, t[k].y), w_nw);
-                            v[2 * k + 1] = mul2s(pack2(t[k].z, t[k].w), w_nw);
-                        }
+                        for (int k = 0; k < 2 * LDV; ++k) v[k] = mul2s(t[k], w_nw);
 #pragma unroll
-                        for (int k = 0; k < LDV; ++k) t[k] = *reinterpret_cast<const float4*>(pn + REC + 4 * k);
+                        for (int k = 0; k < LDV; ++k) lds_v2u64(an + REC * 4 + 16 * k, t[2 * k], t[2 * k + 1]);
 #pragma unroll
-                        for (int k = 0; k < LDV; ++k) {
-                            v[2 * k] = fma2s(pack2(t[k].x, t[k].y), w_ne, v[2 * k]);
-                            v[2 * k + 1] = fma2s(pack2(t[k].z, t[k].w), w_ne, v[2 * k + 1]);
-                        }
+                        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_ne, v[k]);
 #pragma unroll
-                        for (int k = 0; k < LDV; ++k) t[k] = *reinterpret_cast<const float4*>(ps + 4 * k);
+                        for (int k = 0; k < LDV; ++k) lds_v2u64(as + 16 * k, t[2 * k], t[2 * k + 1]);
 #pragma unroll
-                        for (int k = 0; k < LDV; ++k) {
-                            v[2 * k] = fma2s(pack2(t[k].x, t[k].y), w_sw, v[2 * k]);
-                            v[2 * k + 1] = fma2s(pack2(t[k].z, t[k].w), w_sw, v[2 * k + 1]);
-                        }
+                        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_sw, v[k]);
 #pragma unroll
-                        for (int k = 0; k < LDV; ++k) t[k] = *reinterpret_cast<const float4*>(ps + REC + 4 * k);
+                        for (int k = 0; k < LDV; ++k) lds_v2u64(as + REC * 4 + 16 * k, t[2 * k], t[2 * k + 1]);
 #pragma unroll
-                        for (int k = 0; k < LDV; ++k) {
-                            v[2 * k] = fma2s(pack2(t[k].x, t[k].y), w_se, v[2 * k]);
-                            v[2 * k + 1] = fma2s(pack2(t[k].z, t[k].w), w_se, v[2 * k + 1]);
-                        }
+                        for (int k = 0; k < 2 * LDV; ++k) v[k] = fma2s(t[k], w_se, v[k]);
                     } else {
                         // this lane's sample lies outside the window (flow discontinuity): gather from global memory
                         const bool in_x0 = (unsigned)x0 < (unsigned)a.W, in_x1 = (unsigned)(x0 + 1) < (unsigned)a.W;
