@@ -166,9 +166,9 @@ int vfi_dattn_f32(const float* q, const float* feat0, const float* feat1, const 
  * x (B,Cin,H,W); offset (B, OG*2*kh*kw, Ho, Wo) interleaved (dy,dx); mask (B, OG*kh*kw, Ho, Wo) or NULL;
  * weight (Cout, Cin/WG, kh, kw); bias (Cout) or NULL; out (B,Cout,Ho,Wo).  No im2col buffer in HBM.
  * algo: 0 = auto, 1 = SIMT fp32 FFMA with global gathers, 2 = tcgen05 3xTF32 (3x3/s1/p1/d1, Cin/WG in {8,9,16}),
- *       3 = SIMT fp32 FFMA on a TMA-staged shared-memory window (<= 3x3 taps, stride 1, dilation 1, W % 4 == 0): for
- *       offsets that stay within ~7 px of the tile's mean offset (network-predicted offsets around a smooth flow); the
- *       DCNDAT blocks ask for it, auto does not pick it (frame-leaving offsets make it slower than algo 1).
+ *       3 = SIMT fp32 FFMA on a TMA-staged shared-memory window (<= 3x3 taps, stride 1, dilation 1, W % 4 == 0,
+ *       <= 16 channels per group); taps outside the window are gathered cooperatively through a per-tile list.
+ *       auto picks 3 where it applies and the plane has >= 4096 pixels, else 1 (2 only for the widths it is faster at).
  */
 int vfi_dcn_f32(const float* x, const float* offset, const float* mask, const float* weight, const float* bias,
                 float* out, int B, int Cin, int Cout, int H, int W, int kh, int kw, int stride, int pad, int dil,

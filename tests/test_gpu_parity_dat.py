@@ -110,23 +110,25 @@ def test_dcn_vs_oracle_dim64(vfi):
 
 
 @pytest.mark.parametrize("cfg", [dict(C=64, WG=8, OG=8, H=72, W=96), dict(C=72, WG=8, OG=8, H=68, W=120), dict(C=64, WG=8, OG=4, H=64, W=64),
-                                 dict(C=72, WG=8, OG=4, H=40, W=104)])
+                                 dict(C=72, WG=8, OG=4, H=40, W=104), dict(C=64, WG=8, OG=8, H=72, W=96, far=0.6)])
 def test_dcn_window_kernel_vs_oracle(vfi, cfg):
-    """The TMA-window form of the DCN (csrc/dcn_win.cu; algo='window', what the DCNDAT blocks ask for): ragged tiles in
+    """The TMA-window form of the DCN (csrc/dcn_win.cu; algo='window', auto's choice for these shapes): ragged tiles in
     both directions, offset groups == and != weight groups (row a7), offsets with 2 % of the taps far outside the staged
-    window (global-gather fallback) and outside the frame, against torchvision's op through the oracle; the SIMT kernel
-    on the same inputs for comparison."""
+    window (cooperative gather list) and outside the frame, and with 60 % of them far (list overflow: in-thread global
+    gathers), against torchvision's op through the oracle; the SIMT kernel on the same inputs for comparison."""
     from videoframeinterpolation_b200._lib import VfiError
     C, WG, OG, H, W = cfg["C"], cfg["WG"], cfg["OG"], cfg["H"], cfg["W"]
     kw = gc._dcn_op(f"win.{C}.{OG}", 2, C, C, H, W, WG=WG, OG=OG)
     g = torch.Generator().manual_seed(C + OG)
-    far = torch.rand(kw["offset"].shape, generator=g) < 0.02
+    far = torch.rand(kw["offset"].shape, generator=g) < cfg.get("far", 0.02)
     kw["offset"] = torch.where(far, (torch.rand(kw["offset"].shape, generator=g) * 2 - 1) * W, kw["offset"] * 2.0)
     with oracle.library_ops():
         ref = oracle.deform_conv2d(**kw)
     k = cu_kw(kw)
     out = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"], algo="window")
     assert_close(out, ref, TOL, f"dcn window {cfg}")
+    auto = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"])
+    assert torch.equal(auto, out) or H * W < 4096, "auto takes the window kernel for covered shapes of >= 4096 pixels"
     simt = vfi.deform_conv2d(k["x"], k["offset"], k["weight"], k["bias"], stride=1, padding=1, mask=k["mask"], algo="simt")
     assert_close(simt, ref, TOL, f"dcn simt {cfg}")
     # no mask, no bias

@@ -137,14 +137,14 @@ extern "C" int vfi_dcn_f32(const float* x, const float* offset, const float* mas
     if (B == 0) return VFI_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     VFI_REQUIRE(algo >= 0 && algo <= 3, "vfi_dcn_f32: bad algo %d", algo);
-    // window form (dcn_win.cu), opt-in: 1.5x the SIMT kernel when (nearly) every tap falls into the staged window --
-    // offsets predicted by a network around a smooth flow, as in the DCNDAT blocks -- but slower when a few per cent of
-    // the pixels carry frame-leaving offsets (each such lane serialises its warp on global round trips: measured 8.9 ms
-    // against 3.7 ms at BASELINE configs[2] with SURVEY.md 8(d)'s 2 % outliers, 2.5 against 3.7 ms without them)
-    if (algo == 3) {
-        if (!dcn_win_supported(p, x)) VFI_UNSUPPORTED("vfi_dcn_f32: window path does not cover this configuration");
+    // window form (dcn_win.cu): the default where it applies (3x3, stride 1, <= 16 channels per group, a plane large enough
+    // to pay for the staging).  Taps outside the staged window go through a cooperative gather list, so frame-leaving
+    // offsets cost a bounded extra pass instead of a global round trip per lane: BASELINE configs[2] 2.55 ms with no
+    // outliers, 3.48 ms with SURVEY.md 8(d)'s 2 % (SIMT kernel: 3.66 / 3.67 ms); at 10 % outliers the SIMT kernel is the
+    // faster one again (3.69 against 4.34 ms) -- algo 1 selects it.
+    if (algo == 3 && !dcn_win_supported(p, x)) VFI_UNSUPPORTED("vfi_dcn_f32: window path does not cover this configuration");
+    if (algo == 3 || (algo == 0 && dcn_tc_supported(p) != 2 && dcn_win_supported(p, x) && (int64_t)p.Ho * p.Wo >= 4096))
         return launch_dcn_win(x, offset, mask, weight, bias, out, B, p, st);
-    }
     if (algo == 2 && !dcn_tc_supported(p)) VFI_UNSUPPORTED("vfi_dcn_f32: tcgen05 path does not cover this configuration");
     if (algo == 2 || (algo == 0 && dcn_tc_supported(p) == 2))
         return launch_dcn_tc(x, offset, mask, weight, bias, out, B, p, workspace, workspace_bytes, st);

@@ -25,6 +25,7 @@ constexpr int kDwHalo = 7;
 constexpr int kDwWW = kDwTW + 2 + 2 * kDwHalo;       // 48
 constexpr int kDwWH = kDwTH + 2 + 2 * kDwHalo;       // 24
 constexpr int kDwThreads = kDwTW * kDwTH;            // 256
+constexpr int kDwMaxE = 192;                         // out-of-window (pixel, tap) pairs served by the cooperative gather pass
 
 template <int COGP>
 __global__ void __launch_bounds__(kDwThreads, 3)
@@ -38,7 +39,9 @@ dcn_win_kernel(const __grid_constant__ CUtensorMap xmap, const float* __restrict
     float* win = reinterpret_cast<float*>(smem_al);                      // [cin_g][kDwWH][kDwWW]
     float* w_s = win + (size_t)cin_g * kDwWH * kDwWW;                    // [tap][cl][COGP]
     uint64_t* bar = reinterpret_cast<uint64_t*>(w_s + (size_t)taps * cin_g * COGP);
-    int* s_shift = reinterpret_cast<int*>(bar + 1);                      // [2] (y, x) window displacement
+    int* s_shift = reinterpret_cast<int*>(bar + 1);                      // [2] (y, x) window displacement, [2] = list length
+    float* s_list = reinterpret_cast<float*>(s_shift + 4);               // [kDwMaxE][4]: (h, w, mask, -) of out-of-window taps
+    float* s_val = s_list + kDwMaxE * 4;                                 // [kDwMaxE][16]: their masked bilinear values per channel
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = blockIdx.y;
@@ -82,6 +85,7 @@ dcn_win_kernel(const __grid_constant__ CUtensorMap xmap, const float* __restrict
         const int shy = (int)rintf(sy * 0.25f), shx = (int)rintf(sx * 0.25f);
         s_shift[0] = shy;
         s_shift[1] = shx;
+        s_shift[2] = 0;
         // window origin in input coordinates (x a multiple of 4: TMA's 16-byte rule for the innermost coordinate)
         const int wy0 = yo0 - p.pad + shy - kDwHalo;
         const int wx0 = (xo0 - p.pad + shx - kDwHalo) & ~3;
@@ -104,6 +108,48 @@ dcn_win_kernel(const __grid_constant__ CUtensorMap xmap, const float* __restrict
     f32x2 acc[COGP / 2];
 #pragma unroll
     for (int o = 0; o < COGP / 2; ++o) acc[o] = 0ull;
+
+    // ---- taps outside the staged window (flow outliers): collected once, gathered cooperatively ----
+    // A lane that fetched such a tap itself would stall its whole warp on a global round trip per tap (measured: 8.9 ms
+    // at BASELINE configs[2] with 2 % frame-leaving flows against 2.5 ms without them).  Instead every thread files its
+    // out-of-window (pixel, tap) pairs in a shared list, all 256 threads gather list entry x channel items with every
+    // load in flight at once (under the window's TMA round trip), and the main loop reads the values back from shared
+    // memory.  eidx: list slot per tap, 8 bits each (0xFF = none / list full: that tap takes the in-thread path).
+    uint32_t eidx[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
+    {
+        const float wy_lo = (float)wy0, wy_hi = (float)(wy0 + kDwWH - 1), wx_lo = (float)wx0, wx_hi = (float)(wx0 + kDwWW - 1);
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+            if (t < taps) {
+                const int ki = t / p.kw, kj = t - ki * p.kw;
+                const float h = base_h + (float)ki + dy[t], wq = base_w + (float)kj + dx[t];
+                // cheap conservative test first: floor(h) in [wy0, wy0 + WH - 2] <=> wy0 <= h < wy0 + WH - 1
+                const bool surely_in = h >= wy_lo && h < wy_hi && wq >= wx_lo && wq < wx_hi;
+                const bool in_frame = h > -1.0f && h < (float)p.H && wq > -1.0f && wq < (float)p.W;
+                if (!surely_in && in_frame) {
+                    const int e = atomicAdd(&s_shift[2], 1);
+                    if (e < kDwMaxE) {
+                        s_list[4 * e] = h;
+                        s_list[4 * e + 1] = wq;
+                        s_list[4 * e + 2] = mv[t];
+                        eidx[t >> 2] = (eidx[t >> 2] & ~(0xFFu << (8 * (t & 3)))) | ((uint32_t)e << (8 * (t & 3)));
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    {
+        const int n_e = min(s_shift[2], kDwMaxE);                        // uniform over the CTA
+        if (n_e > 0) {
+            for (int item = tid; item < n_e * cin_g; item += kDwThreads) {
+                const int e = item / cin_g, cl = item - e * cin_g;
+                const DcnTap tp = dcn_tap(s_list[4 * e], s_list[4 * e + 1], p.H, p.W);
+                s_val[e * 16 + cl] = dcn_sample(xb + (int64_t)cl * HW + tp.o, tp, p.W) * s_list[4 * e + 2];
+            }
+            __syncthreads();
+        }
+    }
 
     mbar_wait(bar, 0);
     const uint32_t win_u32 = smem_u32(win);
@@ -144,15 +190,25 @@ dcn_win_kernel(const __grid_constant__ CUtensorMap xmap, const float* __restrict
                     }
                 }
             } else {
-                // this pixel's tap lies outside the staged window (a flow outlier): all of the group's corner loads are
-                // issued before the first one is consumed, so the tap costs one global-memory round trip, not cin_g
-                float vv[16];
+                const uint32_t e = (eidx[t >> 2] >> (8 * (t & 3))) & 0xFFu;
+                if (e != 0xFFu) {
+                    // gathered by the cooperative pass above: already masked
+                    const float* sv = s_val + e * 16;
+#pragma unroll 4
+                    for (int cl = 0; cl < cin_g; ++cl) {
+                        const float v = sv[cl];
+                        const float4* wr = reinterpret_cast<const float4*>(wt + cl * COGP);
 #pragma unroll
-                for (int cl = 0; cl < 16; ++cl) vv[cl] = cl < cin_g ? dcn_sample(xb + (int64_t)cl * HW + tp.o, tp, p.W) : 0.0f;
-#pragma unroll
-                for (int cl = 0; cl < 16; ++cl) {
-                    if (cl < cin_g) {
-                        const float v = vv[cl] * m;
+                        for (int o4 = 0; o4 < COGP / 4; ++o4) {
+                            const float4 wv = wr[o4];
+                            acc[2 * o4] = fma2s(pack2(wv.x, wv.y), v, acc[2 * o4]);
+                            acc[2 * o4 + 1] = fma2s(pack2(wv.z, wv.w), v, acc[2 * o4 + 1]);
+                        }
+                    }
+                } else {
+                    // list full (more than kDwMaxE out-of-window taps in this tile): in-thread global gathers
+                    for (int cl = 0; cl < cin_g; ++cl) {
+                        const float v = dcn_sample(xb + (int64_t)cl * HW + tp.o, tp, p.W) * m;
                         const float4* wr = reinterpret_cast<const float4*>(wt + cl * COGP);
 #pragma unroll
                         for (int o4 = 0; o4 < COGP / 4; ++o4) {
@@ -190,7 +246,7 @@ template <int COGP>
 static int launch_dcn_win_t(const CUtensorMap& xmap, const float* x, const float* offset, const float* mask, const float* weight,
                             const float* bias, float* out, int B, const DcnParams& p, cudaStream_t st) {
     const int cin_g = p.Cin / p.WG, taps = p.kh * p.kw;
-    const size_t smem = (size_t)cin_g * kDwWH * kDwWW * 4 + (size_t)taps * cin_g * COGP * 4 + 64 + 128;
+    const size_t smem = (size_t)cin_g * kDwWH * kDwWW * 4 + (size_t)taps * cin_g * COGP * 4 + 64 + (size_t)kDwMaxE * 20 * 4 + 128;
     VFI_CUDA(cudaFuncSetAttribute(dcn_win_kernel<COGP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tiles_x = (int)ceil_div(p.Wo, kDwTW), tiles_y = (int)ceil_div(p.Ho, kDwTH);
     const int64_t gx = (int64_t)B * tiles_x * tiles_y;
