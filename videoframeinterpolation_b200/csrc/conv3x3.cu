@@ -41,7 +41,11 @@ constexpr int kCvM = kCvTW * kCvRows;
 constexpr int kCvWinW = kCvTW + 2;
 constexpr int kCvKSteps = 2;                            // 8-channel k-steps per stage (16 channels = one 64-byte swizzle row)
 constexpr int kCvStageBytes = kCvWinW * kCvRows * 64;   // 160 pixel rows x 64 B = 10240 B
-constexpr int kCvThreads = 320;                         // producer warp, MMA warp, 8 epilogue warps
+#ifndef VFI_CONV_EPI_WARPS
+#define VFI_CONV_EPI_WARPS 12
+#endif
+constexpr int kCvEpiWarps = VFI_CONV_EPI_WARPS;         // a multiple of 4: kCvEpiWarps / 4 warps share each TMEM lane quadrant
+constexpr int kCvThreads = 96 + 32 * kCvEpiWarps;       // producer warp, MMA warp, epilogue warps, store warp
 constexpr int kCvMaxStages = 12;
 constexpr int kCvSmemMax = 232448;                      // 227 KB opt-in limit
 constexpr int kCvAccStride = 256;                       // TMEM columns between the two accumulators
@@ -60,6 +64,7 @@ struct ConvArgs {
     int stages, tiles_x, tiles_y, n_tiles;
     int bias_stride;
     int staged;           // NHWC residual tiles are prefetched into shared memory by TMA (rmap), one tile ahead of the epilogue
+    int ostg;             // NHWC output tiles leave through shared memory and one TMA store per tile (omap)
     int dbg;              // bring-up switches (VFI_CONV_DBG): 1 = no TMA loads, 2 = no epilogue stores, 4 = no MMAs
 };
 
@@ -120,9 +125,14 @@ __device__ __forceinline__ bool elect_one() {
 // RSTG: the residual tile [8 x][14 y][cn] of every output tile is fetched by the producer warp with one TMA box into one
 // of two shared-memory buffers while the previous tile is still in its epilogue (a residual read straight from global
 // memory in the epilogue exposes one HBM latency per 8-channel chunk: 157 vs 95 us for 72 -> 72 at 544x960).
-template <int NPAD, int CTAS, bool RSTG>
+// OSTG: the epilogue warps write their results into a shared-memory tile [8 x][14 y][cn] (over the residual tile when
+// RSTG: same thread, same address) and a dedicated store warp sends it out with ONE TMA store per tile.  The direct path
+// (lane = pixel, one 32-byte sector per thread and chunk) makes every warp store touch 32 lines: with the stores switched
+// off the 72 -> 72 conv runs 84 -> 68 us, i.e. the LSU store path, not the tensor core, was the longest stage.
+template <int NPAD, int CTAS, bool RSTG, bool OSTG>
 __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArgs a, const __grid_constant__ CUtensorMap xmap,
-                                                                   const __grid_constant__ CUtensorMap rmap) {
+                                                                   const __grid_constant__ CUtensorMap rmap,
+                                                                   const __grid_constant__ CUtensorMap omap) {
     constexpr int N = CTAS == 1 ? 3 * NPAD : (3 * NPAD + 15) / 16 * 16;    // UMMA N (cta_group::2 wants a multiple of 16)
     constexpr int NH = N / CTAS;                                          // B rows held by this CTA
     const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
@@ -145,7 +155,9 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
     uint64_t* pfull = tempty + 2;    // [stages] CTA pairs: "the peer's stage s is full", signalled by the peer's forwarding warp
     uint64_t* rfull = pfull + kCvMaxStages;   // [2] RSTG: residual tile landed in its buffer
     uint64_t* rempty = rfull + 2;             // [2] RSTG: the 8 epilogue warps are done with the buffer
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rempty + 2);
+    uint64_t* ofull = rempty + 2;             // [2] OSTG: every epilogue warp has written its part of the output tile
+    uint64_t* oempty = ofull + 2;             // [2] OSTG without a residual: the TMA store has read the buffer
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(oempty + 2);
     // residual buffers: 2 x [8 x][14 y][cn] floats, 128-byte aligned, after the barriers
     float* rbuf = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot + 1) + 127) & ~(uintptr_t)127);
     const int rfloats = kCvTW * kCvTH * a.cn;
@@ -160,13 +172,16 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         mbar_init(wfull, 1);
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tfull[s], 1);
-            mbar_init(&tempty[s], CTAS * 8);  // one arrival per epilogue warp (of both CTAs, on the leader's barrier)
+            mbar_init(&tempty[s], CTAS * kCvEpiWarps);  // one arrival per epilogue warp (of both CTAs, on the leader's barrier)
             mbar_init(&rfull[s], 1);
-            mbar_init(&rempty[s], 8);
+            mbar_init(&rempty[s], OSTG ? 1 : kCvEpiWarps);   // OSTG: released by the store warp once the tile has left
+            mbar_init(&ofull[s], kCvEpiWarps);
+            mbar_init(&oempty[s], 1);
         }
         fence_mbar_init();
         tma_prefetch_desc(&xmap);
         if (RSTG) tma_prefetch_desc(&rmap);
+        if (OSTG) tma_prefetch_desc(&omap);
     }
     __syncthreads();      // barriers initialised before any thread of this CTA touches them
     if (warp == 1) {
@@ -206,7 +221,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             const int tile = unit * CTAS + (int)rank;
             const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
-            if (RSTG) {
+            if (RSTG && !OSTG) {
                 // residual tile of this output tile into the buffer the epilogue released two tiles ago (rows / columns
                 // / images outside the tensor read as 0 and still count their bytes)
                 mbar_wait(&rempty[i & 1], ((i >> 1) & 1) ^ 1);
@@ -291,9 +306,48 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                 if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
             }
         }
+    } else if (warp == 2 + kCvEpiWarps) {
+        // ---- store warp (OSTG): one TMA store per finished output tile, then hand the buffer back ----
+        if (OSTG) {
+            // With a residual the same warp also fetches the residual tiles (two tiles ahead, into the buffer a store has
+            // just left): the window producer never waits for an epilogue.
+            auto fetch_residual = [&](const int unit, const uint32_t slot) {
+                const int tile = unit * CTAS + (int)rank;
+                const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
+                const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
+                mbar_arrive_expect_tx(&rfull[slot], (uint32_t)rfloats * 4);     // (outside the tensor: zeros, bytes still count)
+                tma_load_4d(rbuf + slot * rfloats, &rmap, &rfull[slot], 0, ty * kCvTH, tx * kCvTW, b);
+            };
+            if (RSTG && lane == 0) {
+                if (unit0 < n_units) fetch_residual(unit0, 0);
+                if (unit0 + unit_step < n_units) fetch_residual(unit0 + unit_step, 1);
+            }
+            uint32_t i = 0;
+            for (int unit = unit0; unit < n_units; unit += unit_step, ++i) {
+                const int tile = unit * CTAS + (int)rank;
+                const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
+                const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
+                mbar_wait(&ofull[i & 1], (i >> 1) & 1);
+                if (lane == 0) {
+                    if (tile < a.n_tiles && !(a.dbg & 2)) {
+                        // rows / columns past the image edge are dropped by the TMA unit
+                        tma_store_4d(&omap, rbuf + (i & 1) * rfloats, 0, ty * kCvTH, tx * kCvTW, b);
+                        bulk_commit_group();
+                        bulk_wait_group_read<0>();                       // the tile has left shared memory
+                    }
+                    if (RSTG) {
+                        if (unit + 2 * unit_step < n_units) fetch_residual(unit + 2 * unit_step, i & 1);
+                    } else {
+                        mbar_arrive(&oempty[i & 1]);                     // -> the epilogue warps may write the next tile
+                    }
+                }
+                __syncwarp();
+            }
+            if (lane == 0) bulk_wait_group<0>();                         // global writes complete before the grid ends
+        }
     } else if (warp >= 2) {
         // ---- epilogue warps: TMEM lane group = warp % 4; lane = pixel (column-major: m = 16 * column + row) ----
-        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int q = warp & 3, sub = (warp - 2) >> 2;
         const int m = q * 32 + lane, lx = m >> 4, ly = m & 15;
         const uint32_t lead_tempty0 = CTAS == 2 ? mapa_shared(smem_u32(&tempty[0]), 0) : 0u;
         uint32_t i = 0;
@@ -303,8 +357,10 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
             const uint32_t acc = i & 1;
             // my pixel's residual in the shared-memory tile [x][y][cn] (rows 1..14 of the 16-row window are outputs)
-            const float* rslot = rbuf + (i & 1) * rfloats + (lx * kCvTH + ly - 1) * a.cn;
+            float* rslot = rbuf + (i & 1) * rfloats + (lx * kCvTH + ly - 1) * a.cn;
+            const bool rowok = ly >= 1 && ly <= kCvTH;       // rows 0 and 15 of the window are halo
             if (RSTG) mbar_wait(&rfull[i & 1], (i >> 1) & 1);
+            else if (OSTG) mbar_wait(&oempty[i & 1], ((i >> 1) & 1) ^ 1);
             mbar_wait(&tfull[acc], (i >> 1) & 1);
             __syncwarp();                  // tcgen05.ld and the shuffles below are warp-collective
             umma::fence_after();
@@ -313,22 +369,41 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             const bool valid = ly >= 1 && ly <= kCvTH && y < a.H && x < a.W && tile < a.n_tiles && !(a.dbg & 2);
             float* o = a.out + b * a.out_sb + y * a.out_sy + x * a.out_sx;
             const float* rp = a.res ? a.res + b * a.res_sb + y * a.res_sy + x * a.res_sx : nullptr;
-            // two warps share each TMEM lane quadrant and take alternate 8-channel chunks (latency hiding: the
-            // TMEM-load -> shuffle -> store chain of one warp per scheduler cannot keep up with the MMAs)
-#pragma unroll 1
-            for (int c0 = 8 * half; c0 < a.cn; c0 += 16) {
-                float p0[8], p1[8], p2[8], t[8];
-                umma::tmem_ld8(taddr + c0, p0);
-                umma::tmem_ld8(taddr + NPAD + c0, p1);
-                umma::tmem_ld8(taddr + 2 * NPAD + c0, p2);
-                umma::tmem_ld_wait();
+            // kCvEpiWarps / 4 warps share each TMEM lane quadrant and take every (kCvEpiWarps / 4)-th 8-channel chunk; the
+            // TMEM loads of a warp's next chunk are in flight while it shuffles / stores the current one (two register sets)
+            auto emit = [&](const float (&p0)[8], const float (&p1)[8], const float (&p2)[8], const int c0) {
+                float t[8];
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     const float up = __shfl_up_sync(0xffffffffu, p0[k], 1);      // plane dy=-1 of the row above
                     const float dn = __shfl_down_sync(0xffffffffu, p2[k], 1);    // plane dy=+1 of the row below
                     t[k] = __fadd_rn(__fadd_rn(up, p1[k]), dn);
                 }
-                if (valid && a.vec) {
+                if (OSTG) {
+                    // through the shared-memory tile (the residual, when there is one, sits in the very slot)
+                    if (rowok) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            if (c0 + 4 * h < a.cn) {
+                                float4* sp = reinterpret_cast<float4*>(rslot + c0) + h;
+                                float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
+                                if (RSTG) rr = *sp;
+                                const float rv[4] = {rr.x, rr.y, rr.z, rr.w};
+                                float u[4];
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    const int c = c0 + 4 * h + k;
+                                    float w = __fadd_rn(t[4 * h + k], bias_s[c]);
+                                    if (RSTG && a.res_mode == 1) w = __fadd_rn(rv[k], w);
+                                    if (a.slope) w = w > 0.0f ? w : __fmul_rn(slope_s[c], w);
+                                    if (RSTG && a.res_mode == 2) w = __fadd_rn(rv[k], w);
+                                    u[k] = w;
+                                }
+                                *sp = make_float4(u[0], u[1], u[2], u[3]);
+                            }
+                        }
+                    }
+                } else if (valid && a.vec) {
                     // NHWC: lane = pixel, 8 consecutive channels = one 32-byte sector per thread
                     float rv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                     const bool full8 = c0 + 8 <= a.cn;
@@ -383,15 +458,61 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                         }
                     }
                 }
+            };
+            // the accumulator goes back to the MMA warp as soon as this warp's last TMEM load has landed in registers,
+            // i.e. before the last chunk is shuffled and stored
+            auto release_acc = [&]() {
+                __syncwarp();
+                umma::fence_before();
+                if (lane == 0) {
+                    if (CTAS == 2) mbar_arrive_cluster(lead_tempty0 + acc * 8);
+                    else mbar_arrive(&tempty[acc]);
+                }
+            };
+            constexpr int cstep = 2 * kCvEpiWarps;
+            float pa0[8], pa1[8], pa2[8], pb0[8], pb1[8], pb2[8];
+            int c0 = 8 * sub;
+            if (c0 < a.cn) {
+                umma::tmem_ld8(taddr + c0, pa0);
+                umma::tmem_ld8(taddr + NPAD + c0, pa1);
+                umma::tmem_ld8(taddr + 2 * NPAD + c0, pa2);
+            } else {
+                release_acc();             // no chunk for this warp in this Cout tile
+            }
+#pragma unroll 1
+            for (; c0 < a.cn; c0 += 2 * cstep) {
+                const int c1 = c0 + cstep, c2 = c0 + 2 * cstep;
+                umma::tmem_ld_wait();
+                if (c1 < a.cn) {
+                    umma::tmem_ld8(taddr + c1, pb0);
+                    umma::tmem_ld8(taddr + NPAD + c1, pb1);
+                    umma::tmem_ld8(taddr + 2 * NPAD + c1, pb2);
+                } else {
+                    release_acc();
+                }
+                emit(pa0, pa1, pa2, c0);
                 __syncwarp();              // reconverge before the next warp-collective TMEM load
+                if (c1 < a.cn) {
+                    umma::tmem_ld_wait();
+                    if (c2 < a.cn) {
+                        umma::tmem_ld8(taddr + c2, pa0);
+                        umma::tmem_ld8(taddr + NPAD + c2, pa1);
+                        umma::tmem_ld8(taddr + 2 * NPAD + c2, pa2);
+                    } else {
+                        release_acc();
+                    }
+                    emit(pb0, pb1, pb2, c1);
+                    __syncwarp();
+                }
             }
             __syncwarp();
-            umma::fence_before();
-            if (lane == 0) {               // every TMEM read of this warp is done: the MMA warp may overwrite the accumulator
-                if (CTAS == 2) mbar_arrive_cluster(lead_tempty0 + acc * 8);
-                else mbar_arrive(&tempty[acc]);
+            if (OSTG) {
+                fence_proxy_async_smem();                            // my writes to the tile -> visible to the TMA store
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ofull[i & 1]);
+            } else if (RSTG && lane == 0) {
+                mbar_arrive(&rempty[i & 1]);                         // (after the __syncwarp above: all lanes have read it)
             }
-            if (RSTG && lane == 0) mbar_arrive(&rempty[i & 1]);      // (after the __syncwarp above: all lanes have read it)
         }
     }
     umma::fence_before();
@@ -434,15 +555,15 @@ static ConvTiling conv_tiling(int Cout, int Cin) {
     t.wbytes = (size_t)3 * t.nchunkP * 2 * (t.ntot / t.ctas) * 16;
     return t;
 }
-static size_t conv_smem_fixed(int NPAD) { return 2048 + 2 * NPAD * 4 + (3 * kCvMaxStages + 9) * 8 + 16 + 128; }
+static size_t conv_smem_fixed(int NPAD) { return 2048 + 2 * NPAD * 4 + (3 * kCvMaxStages + 13) * 8 + 16 + 128; }
 static size_t conv_rbuf_bytes(int cn) { return (size_t)2 * kCvTW * kCvTH * cn * 4; }   // two residual tiles
 
-template <int NPAD, int CTAS, bool RSTG>
-static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& rmap, size_t smem,
+template <int NPAD, int CTAS, bool RSTG, bool OSTG>
+static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& rmap, const CUtensorMap& omap, size_t smem,
                        cudaStream_t st) {
     static bool attr = false;
     if (!attr) {
-        VFI_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<NPAD, CTAS, RSTG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCvSmemMax));
+        VFI_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<NPAD, CTAS, RSTG, OSTG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCvSmemMax));
         attr = true;
     }
     const int n_units = (a.n_tiles + CTAS - 1) / CTAS;
@@ -471,7 +592,7 @@ static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtenso
         at[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.numAttrs = 2;
     }
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_tc_kernel<NPAD, CTAS, RSTG>, a, xmap, rmap);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_tc_kernel<NPAD, CTAS, RSTG, OSTG>, a, xmap, rmap, omap);
     if (e != cudaSuccess) {
         set_error("conv3x3_tc_kernel: launch failed: %s", cudaGetErrorString(e));
         return VFI_ERR_CUDA;
@@ -480,10 +601,15 @@ static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtenso
     return VFI_OK;
 }
 template <int NPAD>
-static int conv_launch_any(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& rmap, size_t smem,
+static int conv_launch_any(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& rmap, const CUtensorMap& omap, size_t smem,
                            int ctas, cudaStream_t st) {
-    if (ctas == 2) return a.staged ? conv_launch<NPAD, 2, true>(a, xmap, rmap, smem, st) : conv_launch<NPAD, 2, false>(a, xmap, rmap, smem, st);
-    return conv_launch<NPAD, 1, false>(a, xmap, rmap, smem, st);
+    if (ctas == 2) {
+        if (a.ostg) return a.staged ? conv_launch<NPAD, 2, true, true>(a, xmap, rmap, omap, smem, st)
+                                    : conv_launch<NPAD, 2, false, true>(a, xmap, rmap, omap, smem, st);
+        return a.staged ? conv_launch<NPAD, 2, true, false>(a, xmap, rmap, omap, smem, st)
+                        : conv_launch<NPAD, 2, false, false>(a, xmap, rmap, omap, smem, st);
+    }
+    return conv_launch<NPAD, 1, false, false>(a, xmap, rmap, omap, smem, st);
 }
 
 }  // namespace vfi
@@ -592,13 +718,19 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
             const size_t base = conv_smem_fixed(t.NPAD) + t.wbytes;
             a.staged = (t.ctas == 2 && a.vec && a.res && !no_rstg &&
                         base + conv_rbuf_bytes(a.cn) + 3 * (size_t)kCvStageBytes <= (size_t)kCvSmemMax) ? 1 : 0;
-            const size_t rb = a.staged ? conv_rbuf_bytes(a.cn) : 0;
+            // output through shared memory + TMA store (CTA pairs, NHWC, 16-byte aligned rows): the tile buffers are the
+            // residual's when there is one (results written in place), else two buffers of the same size; a residual
+            // that is not staged keeps the direct path.  VFI_CONV_OSTG=0: A/B switch
+            static const bool no_ostg = getenv("VFI_CONV_OSTG") && atoi(getenv("VFI_CONV_OSTG")) == 0;
+            a.ostg = (t.ctas == 2 && a.vec && !no_ostg && (a.staged || a.res == nullptr) &&
+                      base + conv_rbuf_bytes(a.cn) + 3 * (size_t)kCvStageBytes <= (size_t)kCvSmemMax) ? 1 : 0;
+            const size_t rb = (a.staged || a.ostg) ? conv_rbuf_bytes(a.cn) : 0;
             int stages = (int)(((size_t)kCvSmemMax - base - rb) / kCvStageBytes);
             if (stages > kCvMaxStages) stages = kCvMaxStages;
             if (const char* e = getenv("VFI_CONV_STAGES")) stages = atoi(e) >= 2 && atoi(e) < stages ? atoi(e) : stages;
             a.stages = stages;
             const size_t smem = base + rb + (size_t)stages * kCvStageBytes;
-            CUtensorMap rmap = xmap;      // placeholder when the direct path runs
+            CUtensorMap rmap = xmap, omap = xmap;      // placeholders when the direct paths run
             if (a.staged) {
                 // (channel, y, x, image) view of this Cout tile of the residual; box = one output tile [8 x][14 y][cn]
                 const uint64_t dims[4] = {(uint64_t)a.cn, (uint64_t)H, (uint64_t)W, (uint64_t)B};
@@ -607,13 +739,22 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
                 const int rc2 = make_tmap_f32_nd(&rmap, a.res, 4, dims, sr, box, 0);
                 if (rc2 != VFI_OK) return rc2;
             }
+            if (a.ostg) {
+                // the same view of the output, indexed by CONV pixel (with the fused PixelShuffle the strides step over
+                // the other sub-pixels)
+                const uint64_t dims[4] = {(uint64_t)a.cn, (uint64_t)H, (uint64_t)W, (uint64_t)B};
+                const uint32_t box[4] = {(uint32_t)a.cn, (uint32_t)kCvTH, (uint32_t)kCvTW, 1};
+                const uint64_t so[3] = {(uint64_t)a.out_sy * 4, (uint64_t)a.out_sx * 4, (uint64_t)a.out_sb * 4};
+                const int rc3 = make_tmap_f32_nd(&omap, a.out, 4, dims, so, box, 0);
+                if (rc3 != VFI_OK) return rc3;
+            }
             int rc;
             switch (t.NPAD) {
-                case 16: rc = conv_launch_any<16>(a, xmap, rmap, smem, t.ctas, st); break;
-                case 32: rc = conv_launch_any<32>(a, xmap, rmap, smem, t.ctas, st); break;
-                case 48: rc = conv_launch_any<48>(a, xmap, rmap, smem, t.ctas, st); break;
-                case 64: rc = conv_launch_any<64>(a, xmap, rmap, smem, t.ctas, st); break;
-                case 72: rc = conv_launch_any<72>(a, xmap, rmap, smem, t.ctas, st); break;
+                case 16: rc = conv_launch_any<16>(a, xmap, rmap, omap, smem, t.ctas, st); break;
+                case 32: rc = conv_launch_any<32>(a, xmap, rmap, omap, smem, t.ctas, st); break;
+                case 48: rc = conv_launch_any<48>(a, xmap, rmap, omap, smem, t.ctas, st); break;
+                case 64: rc = conv_launch_any<64>(a, xmap, rmap, omap, smem, t.ctas, st); break;
+                case 72: rc = conv_launch_any<72>(a, xmap, rmap, omap, smem, t.ctas, st); break;
                 default:
                     set_error("vfi_conv3x3_f32: no kernel for a Cout tile padded to %d", t.NPAD);
                     return VFI_ERR_UNSUPPORTED;
