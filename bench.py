@@ -713,7 +713,7 @@ def run_vfi(args):
                      "achieved": conv_tf, "peak": tf32_peak, "peak_source": "nominal dense TF32 (B200_PROFILING.md)",
                      "peak_half_of_measured_bf16": tf32_peak_meas, "unit": "TFLOP/s", "frac": conv_tf / tf32_peak,
                      "flops_per_step": conv_flops, "ms_per_step": conv_ms, "traffic": None,
-                     "note": "shared-memory operand feed of tcgen05.mma (~68 B/clk) bounds it, DESIGN.md 4.6"}
+                     "note": "steady state within 10% of the kernel's own tcgen05.mma issue rate (27 MMAs of M=256 x N=224 x K=8 per tile pair); 2 halo rows of 16 and the per-launch prologue / tail are the rest, DESIGN.md 4.6"}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -50,6 +50,28 @@ constexpr int kCvMaxStages = 12;
 constexpr int kCvSmemMax = 232448;                      // 227 KB opt-in limit
 constexpr int kCvAccStride = 256;                       // TMEM columns between the two accumulators
 
+#ifdef VFI_CONV_TRACE
+// bring-up only (tools/build_variant.sh ... -DVFI_CONV_TRACE): clock64 samples of every role of CTA 0, printed at the end
+__device__ long long g_tr[10][64];
+__device__ long long g_ph[8][2];      // phase marks of CTA 0: (clock64, globaltimer ns)
+__device__ __forceinline__ void cv_phase(int k) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        long long g;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+        g_ph[k][0] = clock64();
+        g_ph[k][1] = g;
+    }
+}
+#define CV_PHASE(k) cv_phase(k)
+#define CV_TRACE(role, idx)                                                            \
+    do {                                                                               \
+        if (blockIdx.x == 0 && (idx) < 64) g_tr[role][idx] = clock64();                \
+    } while (0)
+#else
+#define CV_TRACE(role, idx) do { } while (0)
+#define CV_PHASE(k) do { } while (0)
+#endif
+
 struct ConvArgs {
     const float* wprep;   // this Cout tile: [dx 3][chunk nchunkP][k-half 2][n = dy * NPAD + co][4] floats
     const float* bias;    // cn floats (element stride bias_stride) or null
@@ -65,7 +87,7 @@ struct ConvArgs {
     int bias_stride;
     int staged;           // NHWC residual tiles are prefetched into shared memory by TMA (rmap), one tile ahead of the epilogue
     int ostg;             // NHWC output tiles leave through shared memory and one TMA store per tile (omap)
-    int dbg;              // bring-up switches (VFI_CONV_DBG): 1 = no TMA loads, 2 = no epilogue stores, 4 = no MMAs
+    int dbg;              // bring-up switches (VFI_CONV_DBG): 1 = no TMA loads, 2 = no epilogue stores, 4 = no MMAs, 8 = no epilogue work
 };
 
 // weight (Cout, Cin, 3, 3) contiguous -> per Cout tile of T channels:
@@ -163,6 +185,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
     const int rfloats = kCvTW * kCvTH * a.cn;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    CV_PHASE(0);
     if (tid == 0) {
         for (int s = 0; s < a.stages; ++s) {
             mbar_init(&full[s], 1);
@@ -195,8 +218,10 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
     }
     // PDL: let the next conv of the stream start its own weight prologue on the SMs this grid frees first, and do not
     // read or write an activation before the previous kernel has completed and flushed
+    CV_PHASE(1);
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    CV_PHASE(2);
     for (int i = tid; i < NPAD; i += kCvThreads) {
         bias_s[i] = (a.bias && i < a.cn) ? a.bias[(size_t)i * a.bias_stride] : 0.0f;
         slope_s[i] = (a.slope && i < a.cn) ? a.slope[i] : 1.0f;
@@ -209,6 +234,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         __syncthreads();
     }
     umma::fence_after();
+    CV_PHASE(3);
     const uint32_t tmem_base = *tmem_slot;
     const int tiles_per_img = a.tiles_x * a.tiles_y;
     // work unit = CTAS horizontally consecutive tiles; a unit past the end gives this CTA an all-padding tile
@@ -233,6 +259,8 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             }
             for (int st = 0; st < a.nstage_tile; ++st) {
                 mbar_wait(&empty[s], ph ^ 1);
+                if (st == 0 && lane == 0) CV_TRACE(0, i);
+                if (st == a.nstage_tile - 1 && lane == 0) CV_TRACE(1, i);
                 if (elect_one()) {
                     // box {16 ch, 16 y, 10 x, 1 image} at (16 st, y0 - 1, x0 - 1, b); channels >= Cin and images >= B read as 0
                     // every CTA fills its own ring and signals its own barrier; in a pair the peer's warp 1 forwards
@@ -258,7 +286,9 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
         uint32_t s = 0, ph = 0, i = 0;
         for (int unit = unit0; unit < n_units; unit += unit_step, ++i) {
             const uint32_t acc = i & 1;
+            if (lane == 0) CV_TRACE(2, i);
             mbar_wait(&tempty[acc], ((i >> 1) & 1) ^ 1);
+            if (lane == 0) CV_TRACE(3, i);
             umma::fence_after();
             const uint32_t d = tmem_base + acc * kCvAccStride;
             for (int st = 0; st < a.nstage_tile; ++st) {
@@ -294,6 +324,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                 __syncwarp();
                 if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
             }
+            if (lane == 0) CV_TRACE(4, i);
         }
     } else if (warp == 1) {
         // ---- peer CTA of a pair: forward "my stage s is full" to the leader's MMA warp ----
@@ -335,6 +366,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                         bulk_commit_group();
                         bulk_wait_group_read<0>();                       // the tile has left shared memory
                     }
+                    CV_TRACE(9, i);
                     if (RSTG) {
                         if (unit + 2 * unit_step < n_units) fetch_residual(unit + 2 * unit_step, i & 1);
                     } else {
@@ -361,7 +393,9 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             const bool rowok = ly >= 1 && ly <= kCvTH;       // rows 0 and 15 of the window are halo
             if (RSTG) mbar_wait(&rfull[i & 1], (i >> 1) & 1);
             else if (OSTG) mbar_wait(&oempty[i & 1], ((i >> 1) & 1) ^ 1);
+            if (warp == 2 && lane == 0) CV_TRACE(5, i);
             mbar_wait(&tfull[acc], (i >> 1) & 1);
+            if (warp == 2 && lane == 0) CV_TRACE(6, i);
             __syncwarp();                  // tcgen05.ld and the shuffles below are warp-collective
             umma::fence_after();
             const uint32_t taddr = tmem_base + acc * kCvAccStride + ((uint32_t)(q * 32) << 16);
@@ -369,8 +403,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             const bool valid = ly >= 1 && ly <= kCvTH && y < a.H && x < a.W && tile < a.n_tiles && !(a.dbg & 2);
             float* o = a.out + b * a.out_sb + y * a.out_sy + x * a.out_sx;
             const float* rp = a.res ? a.res + b * a.res_sb + y * a.res_sy + x * a.res_sx : nullptr;
-            // kCvEpiWarps / 4 warps share each TMEM lane quadrant and take every (kCvEpiWarps / 4)-th 8-channel chunk; the
-            // TMEM loads of a warp's next chunk are in flight while it shuffles / stores the current one (two register sets)
+            // kCvEpiWarps / 4 warps share each TMEM lane quadrant and take every (kCvEpiWarps / 4)-th 8-channel chunk
             auto emit = [&](const float (&p0)[8], const float (&p1)[8], const float (&p2)[8], const int c0) {
                 float t[8];
 #pragma unroll
@@ -459,8 +492,6 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                     }
                 }
             };
-            // the accumulator goes back to the MMA warp as soon as this warp's last TMEM load has landed in registers,
-            // i.e. before the last chunk is shuffled and stored
             auto release_acc = [&]() {
                 __syncwarp();
                 umma::fence_before();
@@ -469,39 +500,29 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                     else mbar_arrive(&tempty[acc]);
                 }
             };
+            // all of this warp's chunks are loaded first (<= 3 x 24 registers), the accumulator goes back to the MMA warp,
+            // and only then the chunks are shuffled / written: the MMAs of tile i + 2 wait for TMEM reads, not for stores
             constexpr int cstep = 2 * kCvEpiWarps;
-            float pa0[8], pa1[8], pa2[8], pb0[8], pb1[8], pb2[8];
-            int c0 = 8 * sub;
-            if (c0 < a.cn) {
-                umma::tmem_ld8(taddr + c0, pa0);
-                umma::tmem_ld8(taddr + NPAD + c0, pa1);
-                umma::tmem_ld8(taddr + 2 * NPAD + c0, pa2);
-            } else {
-                release_acc();             // no chunk for this warp in this Cout tile
-            }
-#pragma unroll 1
-            for (; c0 < a.cn; c0 += 2 * cstep) {
-                const int c1 = c0 + cstep, c2 = c0 + 2 * cstep;
-                umma::tmem_ld_wait();
-                if (c1 < a.cn) {
-                    umma::tmem_ld8(taddr + c1, pb0);
-                    umma::tmem_ld8(taddr + NPAD + c1, pb1);
-                    umma::tmem_ld8(taddr + 2 * NPAD + c1, pb2);
-                } else {
-                    release_acc();
+            constexpr int kMaxC = (NPAD / 8 + kCvEpiWarps / 4 - 1) / (kCvEpiWarps / 4);
+            const int cbase = (a.dbg & 8) ? a.cn : 8 * sub;    // dbg 8: handshakes only, no epilogue work
+            float pv[kMaxC][3][8];
+#pragma unroll
+            for (int j = 0; j < kMaxC; ++j) {
+                const int c = cbase + j * cstep;
+                if (c < a.cn) {
+                    umma::tmem_ld8(taddr + c, pv[j][0]);
+                    umma::tmem_ld8(taddr + NPAD + c, pv[j][1]);
+                    umma::tmem_ld8(taddr + 2 * NPAD + c, pv[j][2]);
                 }
-                emit(pa0, pa1, pa2, c0);
-                __syncwarp();              // reconverge before the next warp-collective TMEM load
-                if (c1 < a.cn) {
-                    umma::tmem_ld_wait();
-                    if (c2 < a.cn) {
-                        umma::tmem_ld8(taddr + c2, pa0);
-                        umma::tmem_ld8(taddr + NPAD + c2, pa1);
-                        umma::tmem_ld8(taddr + 2 * NPAD + c2, pa2);
-                    } else {
-                        release_acc();
-                    }
-                    emit(pb0, pb1, pb2, c1);
+            }
+            umma::tmem_ld_wait();
+            release_acc();
+            if (warp == 2 && lane == 0) CV_TRACE(7, i);
+#pragma unroll
+            for (int j = 0; j < kMaxC; ++j) {
+                const int c = cbase + j * cstep;
+                if (c < a.cn) {
+                    emit(pv[j][0], pv[j][1], pv[j][2], c);
                     __syncwarp();
                 }
             }
@@ -510,14 +531,32 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                 fence_proxy_async_smem();                            // my writes to the tile -> visible to the TMA store
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ofull[i & 1]);
+                if (warp == 2 && lane == 0) CV_TRACE(8, i);
             } else if (RSTG && lane == 0) {
                 mbar_arrive(&rempty[i & 1]);                         // (after the __syncwarp above: all lanes have read it)
             }
         }
     }
+    CV_PHASE(4);
     umma::fence_before();
     if (CTAS == 2) cluster_sync_all();
     else __syncthreads();
+    CV_PHASE(5);
+#ifdef VFI_CONV_TRACE
+    if (blockIdx.x == 0 && tid == 0) {
+        printf("phases (clk / ns from entry): barriers+tmem %lld / %lld, pdl wait %lld / %lld, weights+sync %lld / %lld, thread0 loop end %lld / %lld, all roles done %lld / %lld; first tile go at %lld clk, tiles of this CTA: last traced index\n",
+               g_ph[1][0] - g_ph[0][0], g_ph[1][1] - g_ph[0][1], g_ph[2][0] - g_ph[0][0], g_ph[2][1] - g_ph[0][1],
+               g_ph[3][0] - g_ph[0][0], g_ph[3][1] - g_ph[0][1], g_ph[4][0] - g_ph[0][0], g_ph[4][1] - g_ph[0][1],
+               g_ph[5][0] - g_ph[0][0], g_ph[5][1] - g_ph[0][1], g_tr[3][0] - g_ph[0][0]);
+        for (int i = 0; i < 34; i += 3)
+            printf("  tile %2d: M go %7lld  E done %7lld  S left %7lld (clk from entry)\n", i, g_tr[3][i] - g_ph[0][0], g_tr[8][i] - g_ph[0][0], g_tr[9][i] - g_ph[0][0]);
+        const long long t0 = g_tr[3][8];
+        for (int i = 8; i < 16; ++i)
+            printf("tile %2d  P first %6lld last %6lld | M enter %6lld go %6lld issued %6lld | E enter %6lld tfull %6lld loaded %6lld done %6lld | S left %6lld\n",
+                   i, g_tr[0][i] - t0, g_tr[1][i] - t0, g_tr[2][i] - t0, g_tr[3][i] - t0, g_tr[4][i] - t0, g_tr[5][i] - t0,
+                   g_tr[6][i] - t0, g_tr[7][i] - t0, g_tr[8][i] - t0, g_tr[9][i] - t0);
+    }
+#endif
     if (warp == 1) {
         if (CTAS == 2) umma::tmem_dealloc_2sm(tmem_base, 2 * kCvAccStride);
         else umma::tmem_dealloc(tmem_base, 2 * kCvAccStride);
