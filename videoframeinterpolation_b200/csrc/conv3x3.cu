@@ -52,7 +52,7 @@ constexpr int kCvAccStride = 256;                       // TMEM columns between 
 
 #ifdef VFI_CONV_TRACE
 // bring-up only (tools/build_variant.sh ... -DVFI_CONV_TRACE): clock64 samples of every role of CTA 0, printed at the end
-__device__ long long g_tr[10][64];
+__device__ long long g_tr[12][64];
 __device__ long long g_ph[8][2];      // phase marks of CTA 0: (clock64, globaltimer ns)
 __device__ __forceinline__ void cv_phase(int k) {
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -71,6 +71,8 @@ __device__ __forceinline__ void cv_phase(int k) {
 #define CV_TRACE(role, idx) do { } while (0)
 #define CV_PHASE(k) do { } while (0)
 #endif
+
+__host__ __device__ static inline int conv_tile_pitch(int cn);
 
 struct ConvArgs {
     const float* wprep;   // this Cout tile: [dx 3][chunk nchunkP][k-half 2][n = dy * NPAD + co][4] floats
@@ -182,7 +184,8 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(oempty + 2);
     // residual buffers: 2 x [8 x][14 y][cn] floats, 128-byte aligned, after the barriers
     float* rbuf = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_slot + 1) + 127) & ~(uintptr_t)127);
-    const int rfloats = kCvTW * kCvTH * a.cn;
+    const int rpitch = conv_tile_pitch(a.cn);
+    const int rfloats = kCvTW * kCvTH * rpitch;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     CV_PHASE(0);
@@ -389,7 +392,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
             const uint32_t acc = i & 1;
             // my pixel's residual in the shared-memory tile [x][y][cn] (rows 1..14 of the 16-row window are outputs)
-            float* rslot = rbuf + (i & 1) * rfloats + (lx * kCvTH + ly - 1) * a.cn;
+            float* rslot = rbuf + (i & 1) * rfloats + (lx * kCvTH + ly - 1) * rpitch;
             const bool rowok = ly >= 1 && ly <= kCvTH;       // rows 0 and 15 of the window are halo
             if (RSTG) mbar_wait(&rfull[i & 1], (i >> 1) & 1);
             else if (OSTG) mbar_wait(&oempty[i & 1], ((i >> 1) & 1) ^ 1);
@@ -422,13 +425,17 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                                 float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
                                 if (RSTG) rr = *sp;
                                 const float rv[4] = {rr.x, rr.y, rr.z, rr.w};
+                                // bias / slopes as two broadcast 128-bit loads (shared-memory wavefronts are what this
+                                // kernel runs out of: the tensor core's operand reads share them)
+                                const float4 b4 = *reinterpret_cast<const float4*>(bias_s + c0 + 4 * h);
+                                const float4 s4 = *reinterpret_cast<const float4*>(slope_s + c0 + 4 * h);
+                                const float bv[4] = {b4.x, b4.y, b4.z, b4.w}, sv[4] = {s4.x, s4.y, s4.z, s4.w};
                                 float u[4];
 #pragma unroll
                                 for (int k = 0; k < 4; ++k) {
-                                    const int c = c0 + 4 * h + k;
-                                    float w = __fadd_rn(t[4 * h + k], bias_s[c]);
+                                    float w = __fadd_rn(t[4 * h + k], bv[k]);
                                     if (RSTG && a.res_mode == 1) w = __fadd_rn(rv[k], w);
-                                    if (a.slope) w = w > 0.0f ? w : __fmul_rn(slope_s[c], w);
+                                    if (a.slope) w = w > 0.0f ? w : __fmul_rn(sv[k], w);
                                     if (RSTG && a.res_mode == 2) w = __fadd_rn(rv[k], w);
                                     u[k] = w;
                                 }
@@ -527,6 +534,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                 }
             }
             __syncwarp();
+            if (warp == 2 && lane == 0) CV_TRACE(10, i);
             if (OSTG) {
                 fence_proxy_async_smem();                            // my writes to the tile -> visible to the TMA store
                 __syncwarp();
@@ -552,9 +560,9 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             printf("  tile %2d: M go %7lld  E done %7lld  S left %7lld (clk from entry)\n", i, g_tr[3][i] - g_ph[0][0], g_tr[8][i] - g_ph[0][0], g_tr[9][i] - g_ph[0][0]);
         const long long t0 = g_tr[3][8];
         for (int i = 8; i < 16; ++i)
-            printf("tile %2d  P first %6lld last %6lld | M enter %6lld go %6lld issued %6lld | E enter %6lld tfull %6lld loaded %6lld done %6lld | S left %6lld\n",
+            printf("tile %2d  P first %6lld last %6lld | M enter %6lld go %6lld issued %6lld | E enter %6lld tfull %6lld loaded %6lld emitted %6lld done %6lld | S left %6lld\n",
                    i, g_tr[0][i] - t0, g_tr[1][i] - t0, g_tr[2][i] - t0, g_tr[3][i] - t0, g_tr[4][i] - t0, g_tr[5][i] - t0,
-                   g_tr[6][i] - t0, g_tr[7][i] - t0, g_tr[8][i] - t0, g_tr[9][i] - t0);
+                   g_tr[6][i] - t0, g_tr[7][i] - t0, g_tr[10][i] - t0, g_tr[8][i] - t0, g_tr[9][i] - t0);
     }
 #endif
     if (warp == 1) {
@@ -595,7 +603,12 @@ static ConvTiling conv_tiling(int Cout, int Cin) {
     return t;
 }
 static size_t conv_smem_fixed(int NPAD) { return 2048 + 2 * NPAD * 4 + (3 * kCvMaxStages + 13) * 8 + 16 + 128; }
-static size_t conv_rbuf_bytes(int cn) { return (size_t)2 * kCvTW * kCvTH * cn * 4; }   // two residual tiles
+// Pixel stride (floats) of the shared-memory residual / output tiles: the smallest P >= cn with P = 4 (mod 8), i.e. an odd
+// number of 16-byte words, so that the 8 lanes of a quarter warp (8 consecutive pixels, 16 bytes each) hit 8 different
+// bank groups (cn = 72 was a 2-way, cn = 64 an 8-way conflict).  The TMA boxes are P channels wide: the P - cn channels
+// past the tensor's extent are zero-filled on loads and dropped on stores.
+__host__ __device__ static inline int conv_tile_pitch(int cn) { return ((cn + 3) / 8) * 8 + 4; }
+static size_t conv_rbuf_bytes(int cn) { return (size_t)2 * kCvTW * kCvTH * conv_tile_pitch(cn) * 4; }   // two tiles
 
 template <int NPAD, int CTAS, bool RSTG, bool OSTG>
 static int conv_launch(const ConvArgs& a, const CUtensorMap& xmap, const CUtensorMap& rmap, const CUtensorMap& omap, size_t smem,
@@ -773,7 +786,7 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
             if (a.staged) {
                 // (channel, y, x, image) view of this Cout tile of the residual; box = one output tile [8 x][14 y][cn]
                 const uint64_t dims[4] = {(uint64_t)a.cn, (uint64_t)H, (uint64_t)W, (uint64_t)B};
-                const uint32_t box[4] = {(uint32_t)a.cn, (uint32_t)kCvTH, (uint32_t)kCvTW, 1};
+                const uint32_t box[4] = {(uint32_t)conv_tile_pitch(a.cn), (uint32_t)kCvTH, (uint32_t)kCvTW, 1};
                 const uint64_t sr[3] = {(uint64_t)a.res_sy * 4, (uint64_t)a.res_sx * 4, (uint64_t)a.res_sb * 4};
                 const int rc2 = make_tmap_f32_nd(&rmap, a.res, 4, dims, sr, box, 0);
                 if (rc2 != VFI_OK) return rc2;
@@ -782,7 +795,7 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
                 // the same view of the output, indexed by CONV pixel (with the fused PixelShuffle the strides step over
                 // the other sub-pixels)
                 const uint64_t dims[4] = {(uint64_t)a.cn, (uint64_t)H, (uint64_t)W, (uint64_t)B};
-                const uint32_t box[4] = {(uint32_t)a.cn, (uint32_t)kCvTH, (uint32_t)kCvTW, 1};
+                const uint32_t box[4] = {(uint32_t)conv_tile_pitch(a.cn), (uint32_t)kCvTH, (uint32_t)kCvTW, 1};
                 const uint64_t so[3] = {(uint64_t)a.out_sy * 4, (uint64_t)a.out_sx * 4, (uint64_t)a.out_sb * 4};
                 const int rc3 = make_tmap_f32_nd(&omap, a.out, 4, dims, so, box, 0);
                 if (rc3 != VFI_OK) return rc3;
