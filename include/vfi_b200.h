@@ -236,6 +236,21 @@ int vfi_dsample_bwd_f32(const float* feat, const float* coords, const float* gra
                         const float* lin_y, float* grad_feat, float* grad_coords, int B, int C, int H, int W,
                         int nG, int nS, void* stream);
 
+/* ---- a8 / f1 over a window of OUTPUT rows: the sampler and its backward for the rows [row0, row0 + rows) of the
+ * (H, W) output grid, sampling the WHOLE feature map.  coords (B, nG*nS, 2, rows, W), out / grad_out (B, C, nS, rows*W),
+ * grad_coords (B, nG*nS, 2, rows, W) hold those rows only; feat / grad_feat are (B, C, H, W); lin_y is the frame's
+ * whole vector.  accumulate != 0: grad_feat is added to, not zero-filled first.
+ * The reference has no counterpart: these are the pieces of the memory-bounded backward of the fused attention
+ * (videoframeinterpolation_b200/deformable_attn.py:_FusedAttnTrainFn), which recomputes the samples of
+ * modules/deformable_attn.py:88-101 strip by strip instead of keeping the (B, C, 2 nS, H*W) kv tensor of
+ * modules/deformable_attn.py:33-34 (9.6 GB per 1080p pair at 1/2 resolution) alive for autograd. */
+int vfi_dsample_rows_f32(const float* feat, const float* coords, const float* lin_x, const float* lin_y, float* out,
+                         float* grid_out, int B, int C, int H, int W, int nG, int nS, int row0, int rows,
+                         const int* frame_ext, void* stream);
+int vfi_dsample_rows_bwd_f32(const float* feat, const float* coords, const float* grad_out, const float* lin_x,
+                             const float* lin_y, float* grad_feat, float* grad_coords, int B, int C, int H, int W,
+                             int nG, int nS, int row0, int rows, int accumulate, void* stream);
+
 /* ---- f1: backward of the modulated deformable convolution -- torchvision deform_conv2d autograd semantics
  * (modules/dcnv2.py:60-66, models/archive/DCNDAT.py:71-77).  Two data-dependent steps; the dense contractions between
  * them (grad_weight = grad_out . columns^T and grad_columns = W^T . grad_out per weight group) are library GEMMs in the

@@ -256,3 +256,84 @@ def test_prepared_weight_caches_are_invalidated_explicitly_after_data_writes():
         assert float((y1 - y1_fp32).abs().max()) <= 2e-2, "prepared weights are stale after invalidate_prepared"
     finally:
         torch.backends.cudnn.allow_tf32 = prev
+
+
+@pytest.mark.parametrize("cfg", [dict(c=72, nG=8, nS=8, H=22, W=36, strip=3), dict(c=16, nG=8, nS=4, H=17, W=24, strip=5)])
+def test_fused_attention_train_matches_the_materialising_composition(cfg):
+    """the fused sampler + attention with its strip-wise recomputing backward against autograd
+    through the reference's own composition (grouped sampler -> Attn, modules/deformable_attn.py:26-40, 88-101, on the
+    oracle's library ops): output and the gradients wrt query, both feature maps, both coordinate fields and the six
+    projection tensors.  The strip size forces several strips with a ragged last one."""
+    from videoframeinterpolation_b200.deformable_attn import fused_attention_train
+    c, nG, nS, H, W, B = cfg["c"], cfg["nG"], cfg["nS"], cfg["H"], cfg["W"], 2
+    tag = f"bwd.fat.{c}.{nS}"
+    q, f0, f1 = (det.normal(f"{tag}.{n}", (B, c, H, W)) for n in ("q", "f0", "f1"))
+    c0, c1 = (det.normal(f"{tag}.{n}", (B, nG * nS, 2, H, W), std=2.5) for n in ("c0", "c1"))
+    c0[:, 1, :, :3] = 2.0 * W                   # samples that leave the frame
+    ws = [det.normal(f"{tag}.w{i}", (c, c) if i % 2 == 0 else (c,), std=(c ** -0.5 if i % 2 == 0 else 0.1)) for i in range(6)]
+
+    def ref(q, f0, f1, c0, c1, *w):
+        kv = torch.cat((oracle.dsample(f0, c0, nG, nS), oracle.dsample(f1, c1, nG, nS)), dim=2)
+        hc = c // nG
+        qp = torch.nn.functional.conv2d(q, w[0].view(c, c, 1, 1), w[1]).reshape(B * nG, hc, H * W)
+        k = torch.nn.functional.conv2d(kv, w[2].view(c, c, 1, 1), w[3]).reshape(B * nG, hc, 2 * nS, H * W)
+        v = torch.nn.functional.conv2d(kv, w[4].view(c, c, 1, 1), w[5]).reshape(B * nG, hc, 2 * nS, H * W)
+        a = torch.softmax(torch.einsum("bcd,bcsd->bsd", qp, k) * hc ** -0.5, dim=1)
+        return torch.einsum("bsd,bcsd->bcd", a, v).reshape(B, c, H, W)
+
+    with oracle.library_ops():
+        ref_out, ref_g = _grads(ref, q, f0, f1, c0, c1, *ws)
+    strip_bytes = cfg["strip"] * B * c * 2 * nS * W * 4
+    out, got = _grads(lambda *a: fused_attention_train(*a, n_groups=nG, n_samples=nS, n_heads=nG, strip_bytes=strip_bytes),
+                      *(t.cuda() for t in (q, f0, f1, c0, c1, *ws)))
+    assert rel_err(out, ref_out) <= 1e-5
+    names = ["q", "feat0", "feat1", "coords0", "coords1", "Wq", "bq", "Wk", "bk", "Wv", "bv"]
+    for n, a, r in zip(names, got, ref_g):
+        if n == "bk":                           # cancels in the softmax: pure rounding noise on both sides
+            assert float(a.abs().max()) <= 1e-4 * float(ref_g[7].abs().max())
+            continue
+        assert rel_err(a, r) <= (2e-4 if n.startswith("coords") else 5e-5), (n, rel_err(a, r))
+    # gradient wrt a subset only (frozen projections, detached coordinates) takes the same route
+    x = f0.cuda().requires_grad_(True)
+    fused_attention_train(q.cuda(), x, f1.cuda(), c0.cuda(), c1.cuda(), *(w.cuda() for w in ws), n_groups=nG, n_samples=nS,
+                          n_heads=nG, strip_bytes=strip_bytes).sum().backward()
+    assert x.grad is not None and torch.isfinite(x.grad).all() and float(x.grad.abs().max()) > 0
+
+
+def test_fused_attention_training_memory_is_bounded_by_the_strip():
+    """The point of the recomputing backward: at the 1/8-resolution shape of a 1080p pair (136 x 240, C = 72, 2 x 8 samples)
+    the kv-materialising composition keeps several (B, C, 16, HW) tensors alive for autograd (150 MB each); the fused route's
+    peak must stay far below it -- at 1/2 resolution the same ratio is 40 GB against ~1.5 GB."""
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.deformable_attn import CrossDeformableAttentionBlockwFlow
+    import os
+    torch.manual_seed(0)
+    blk = CrossDeformableAttentionBlockwFlow(72, 72, n_samples=8, n_groups=8, n_heads=8, offset_scale=8.0).cuda().train()
+    with torch.no_grad():
+        blk.conv_res_offset.weight.normal_(0, 0.02)
+    B, H, W = 1, 136, 240
+    ft, f0, f1 = (det.normal(f"bwd.mem.{n}", (B, 72, H, W)).cuda().requires_grad_(True) for n in ("t", "0", "1"))
+    fl0, fl1 = (det.normal(f"bwd.mem.fl{n}", (B, 2, H, W), std=2.0).cuda() for n in "01")
+    peaks, grads = {}, {}
+    for mode in ("fused", "materialize"):
+        os.environ["VFI_DATTN_TRAIN"] = mode
+        os.environ["VFI_DATTN_TRAIN_STRIP_MB"] = "8"          # 18 strips of 8 rows at this shape
+        try:
+            for t in (ft, f0, f1):
+                t.grad = None
+            blk.zero_grad(set_to_none=True)
+            torch.cuda.synchronize()
+            torch.cuda.reset_peak_memory_stats()
+            base = torch.cuda.memory_allocated()
+            out = blk(ft, f0, f1, fl0, fl1)[0]
+            out.square().mean().backward()
+            torch.cuda.synchronize()
+            peaks[mode] = torch.cuda.max_memory_allocated() - base
+            grads[mode] = [ft.grad.clone(), f0.grad.clone(), blk.attn.k_proj.weight.grad.clone(), blk.conv_res_offset.weight.grad.clone()]
+        finally:
+            os.environ.pop("VFI_DATTN_TRAIN", None)
+    print(f"peak training memory of one block at 136x240: fused {peaks['fused'] / 2**20:.0f} MiB, materialising "
+          f"{peaks['materialize'] / 2**20:.0f} MiB")
+    assert peaks["fused"] < 0.6 * peaks["materialize"], peaks
+    for a, b_ in zip(grads["fused"], grads["materialize"]):
+        assert rel_err(a, b_) <= 2e-3

@@ -46,6 +46,8 @@ SIGNATURES = {
     "vfi_splat_bwd_f32": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "vfi_bwarp_bwd_f32": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p]),
     "vfi_dsample_bwd_f32": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_void_p]),
+    "vfi_dsample_rows_f32": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p, c_void_p]),
+    "vfi_dsample_rows_bwd_f32": (c_int, [c_void_p] * 7 + [c_int] * 9 + [c_void_p]),
     "vfi_frame_prep_workspace_bytes": (c_size_t, [c_int]),
     "vfi_frame_prep": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p] + [c_int] * 7 + [c_void_p, c_size_t, c_void_p]),
     "vfi_frame_finish": (c_int, [c_void_p] * 4 + [c_int] * 8 + [c_void_p]),

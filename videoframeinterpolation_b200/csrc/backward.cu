@@ -114,15 +114,17 @@ __global__ void __launch_bounds__(256) bwarp_bwd_kernel(const float* __restrict_
 __global__ void __launch_bounds__(256) dsample_bwd_kernel(const float* __restrict__ feat, const float* __restrict__ coords,
                                                           const float* __restrict__ gout, const float* __restrict__ lin_x,
                                                           const float* __restrict__ lin_y, float* __restrict__ gfeat,
-                                                          float* __restrict__ gcoords, int C, int H, int W, int nG, int nS) {
-    const int64_t HW = (int64_t)H * W;
+                                                          float* __restrict__ gcoords, int C, int H, int W, int nG, int nS,
+                                                          int row0, int rows) {
+    // coords / gout / gcoords hold the output rows [row0, row0 + rows) only (the whole plane when rows == H)
+    const int64_t HW = (int64_t)H * W, HWs = (int64_t)rows * W;
     const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (pix >= HW) return;
+    if (pix >= HWs) return;
     const int gs = blockIdx.y, g = gs / nS, s = gs - g * nS, b = blockIdx.z;
-    const int y = (int)(pix / W), x = (int)(pix - (int64_t)y * W);
+    const int ys = (int)(pix / W), x = (int)(pix - (int64_t)ys * W), y = row0 + ys;
     const int gc = C / nG;
-    const float* cp = coords + (((int64_t)b * nG * nS + gs) * 2) * HW + pix;
-    const float dx = __ldg(cp), dy = __ldg(cp + HW);
+    const float* cp = coords + (((int64_t)b * nG * nS + gs) * 2) * HWs + pix;
+    const float dx = __ldg(cp), dy = __ldg(cp + HWs);
     const float wm1 = (float)(W - 1), hm1 = (float)(H - 1), half_h = (float)((H - 1.0) / 2.0);
     const float gxn = __fadd_rn(lin_x[x], __fmul_rn(__fdiv_rn(dx, wm1), 0.5f));
     const float gyn = __fadd_rn(lin_y[y], __fdiv_rn(dy, half_h));
@@ -140,7 +142,7 @@ __global__ void __launch_bounds__(256) dsample_bwd_kernel(const float* __restric
     const int64_t o_nw = (int64_t)y0 * W + x0;
     const float* fp = feat + ((int64_t)b * C + (int64_t)g * gc) * HW;
     float* gf = gfeat ? gfeat + ((int64_t)b * C + (int64_t)g * gc) * HW : nullptr;
-    const float* gp = gout + (((int64_t)b * C + (int64_t)g * gc) * nS + s) * HW + pix;
+    const float* gp = gout + (((int64_t)b * C + (int64_t)g * gc) * nS + s) * HWs + pix;
     float gx = 0.0f, gy = 0.0f;
     for (int c = 0; c < gc; ++c) {
         const float go = __ldg(gp);
@@ -158,13 +160,13 @@ __global__ void __launch_bounds__(256) dsample_bwd_kernel(const float* __restric
             gy += go * ((v_sw - v_nw) * ex + (v_se - v_ne) * tx);
         }
         fp += HW;
-        gp += (int64_t)nS * HW;
+        gp += (int64_t)nS * HWs;
     }
     if (gcoords) {
-        float* gcp = gcoords + (((int64_t)b * nG * nS + gs) * 2) * HW + pix;
+        float* gcp = gcoords + (((int64_t)b * nG * nS + gs) * 2) * HWs + pix;
         // unnormalise: d ix / d gx = (W-1)/2; then the reference's own (dx / (W-1)) / 2 and dy / ((H-1)/2)
         gcp[0] = finite ? __fmul_rn(__fdiv_rn(gx * (wm1 * 0.5f), wm1), 0.5f) : 0.0f;
-        gcp[HW] = finite ? __fdiv_rn(gy * (hm1 * 0.5f), half_h) : 0.0f;
+        gcp[HWs] = finite ? __fdiv_rn(gy * (hm1 * 0.5f), half_h) : 0.0f;
     }
 }
 
@@ -183,7 +185,25 @@ extern "C" int vfi_dsample_bwd_f32(const float* feat, const float* coords, const
     if (grad_feat) VFI_CUDA(cudaMemsetAsync(grad_feat, 0, sizeof(float) * (size_t)B * C * H * W, st));
     const int64_t HW = (int64_t)H * W;
     dim3 grid((unsigned)ceil_div(HW, 256), (unsigned)(nG * nS), (unsigned)B);
-    dsample_bwd_kernel<<<grid, 256, 0, st>>>(feat, coords, grad_out, lin_x, lin_y, grad_feat, grad_coords, C, H, W, nG, nS);
+    dsample_bwd_kernel<<<grid, 256, 0, st>>>(feat, coords, grad_out, lin_x, lin_y, grad_feat, grad_coords, C, H, W, nG, nS, 0, H);
+    VFI_CHECK_LAUNCH("dsample_bwd_kernel");
+    return VFI_OK;
+}
+
+extern "C" int vfi_dsample_rows_bwd_f32(const float* feat, const float* coords, const float* grad_out, const float* lin_x,
+                                        const float* lin_y, float* grad_feat, float* grad_coords, int B, int C, int H, int W,
+                                        int nG, int nS, int row0, int rows, int accumulate, void* stream) {
+    using namespace vfi;
+    if (B == 0 || rows == 0) return VFI_OK;
+    VFI_REQUIRE(feat && coords && grad_out && lin_x && lin_y, "vfi_dsample_rows_bwd_f32: null pointer");
+    VFI_REQUIRE(B >= 0 && C >= 1 && H >= 1 && W >= 1 && nG >= 1 && nS >= 1 && C % nG == 0, "vfi_dsample_rows_bwd_f32: bad shape");
+    VFI_REQUIRE(row0 >= 0 && rows >= 0 && row0 + rows <= H, "vfi_dsample_rows_bwd_f32: rows [%d, %d) outside 0..%d", row0, row0 + rows, H);
+    VFI_REQUIRE((int64_t)nG * nS <= 65535 && B <= 65535, "vfi_dsample_rows_bwd_f32: nG*nS or B exceeds grid limits");
+    if (!grad_feat && !grad_coords) return VFI_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (grad_feat && !accumulate) VFI_CUDA(cudaMemsetAsync(grad_feat, 0, sizeof(float) * (size_t)B * C * H * W, st));
+    dim3 grid((unsigned)ceil_div((int64_t)rows * W, 256), (unsigned)(nG * nS), (unsigned)B);
+    dsample_bwd_kernel<<<grid, 256, 0, st>>>(feat, coords, grad_out, lin_x, lin_y, grad_feat, grad_coords, C, H, W, nG, nS, row0, rows);
     VFI_CHECK_LAUNCH("dsample_bwd_kernel");
     return VFI_OK;
 }

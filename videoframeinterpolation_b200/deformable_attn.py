@@ -23,7 +23,8 @@ from . import conv as _conv
 from .blocks import FeadForward, HalfChannelConv5ResBlock, conv_bias_act, conv_prelu, flow_up2_add, resize
 from .warp import bwarp, _bwarp_forward
 
-__all__ = ["Attn", "CrossDeformableAttentionBlockwFlow", "grouped_sample", "attention_over_samples", "fused_deformable_attention"]
+__all__ = ["Attn", "CrossDeformableAttentionBlockwFlow", "grouped_sample", "attention_over_samples", "fused_deformable_attention",
+           "fused_attention_train"]
 
 
 class _GroupedSampleFn(torch.autograd.Function):
@@ -168,6 +169,110 @@ def fused_deformable_attention(q, feat0, feat1, offs0, offs1, ft0: Optional[torc
     return (out, s0, s1) if want_scores else out
 
 
+def _attn_math(q, kv, wq, bq, wk, bk, wv, bv, n_heads: int):
+    """Attn.forward of the reference (modules/deformable_attn.py:26-40) as library ops: q (b,c,h,w), kv (b,c,S,h*w)."""
+    b, c, fh, fw = q.shape
+    S, hc = kv.shape[2], c // n_heads
+    qp = F.conv2d(q, wq.reshape(c, c, 1, 1), bq).reshape(b * n_heads, hc, fh * fw)
+    k = F.conv2d(kv, wk.reshape(c, c, 1, 1), bk).reshape(b * n_heads, hc, S, fh * fw)
+    v = F.conv2d(kv, wv.reshape(c, c, 1, 1), bv).reshape(b * n_heads, hc, S, fh * fw)
+    w = F.softmax(torch.einsum("bcd,bcsd->bsd", qp, k) * hc ** -0.5, dim=1)
+    return torch.einsum("bsd,bcsd->bcd", w, v).reshape(b, c, fh, fw)
+
+
+def _sample_rows(feat, coords_rows, n_groups, n_samples, row0, lin_x, lin_y):
+    """grouped_sample for the output rows [row0, row0 + rows): coords_rows (b, nG*nS, 2, rows, w) -> (b, c, nS, rows*w)."""
+    b, c, fh, fw = feat.shape
+    rows = coords_rows.shape[3]
+    out = torch.empty((b, c, n_samples, rows * fw), dtype=torch.float32, device=feat.device)
+    _lib.call("vfi_dsample_rows_f32", feat.device, feat.data_ptr(), coords_rows.data_ptr(), lin_x.data_ptr(), lin_y.data_ptr(),
+              out.data_ptr(), None, b, c, fh, fw, n_groups, n_samples, row0, rows, None, _lib.stream_ptr(feat.device))
+    return out
+
+
+class _FusedAttnTrainFn(torch.autograd.Function):
+    """Training form of the fused sampler + attention.
+
+    forward: vfi_dattn_f32 on final coordinates -- the (b, c, 2 nS, h*w) kv tensor of modules/deformable_attn.py:33-34
+    is never formed and nothing but the inputs is kept for the backward.
+    backward: the output rows are walked in strips; per strip the samples are RECOMPUTED (vfi_dsample_rows_f32), the
+    attention of modules/deformable_attn.py:26-40 is re-run on the strip's kv under autograd (library ops, exactly what the
+    reference differentiates), and the strip's d kv goes through the sampler's backward kernel (vfi_dsample_rows_bwd_f32:
+    atomics into the whole-frame feature gradients, per-pixel coordinate gradients).  Peak extra memory is ~8x one strip of
+    kv (``strip_bytes``, default 64 MB; the block reads ``VFI_DATTN_TRAIN_STRIP_MB``) instead of ~8x the 9.6 GB kv tensor
+    of a 1080p pair at 1/2 resolution."""
+
+    @staticmethod
+    def forward(ctx, q, feat0, feat1, coords0, coords1, wq, bq, wk, bk, wv, bv, n_groups, n_samples, n_heads, strip_bytes):
+        q_c, f0, f1 = _lib.f32c(q), _lib.f32c(feat0), _lib.f32c(feat1)
+        c0, c1 = _lib.f32c(coords0), _lib.f32c(coords1)
+        ws = tuple(_lib.f32c(t) for t in (wq, bq, wk, bk, wv, bv))
+        ctx.save_for_backward(q_c, f0, f1, c0, c1, *ws)
+        ctx.conf = (n_groups, n_samples, n_heads, int(strip_bytes))
+        with torch.no_grad():
+            return fused_deformable_attention(q_c, f0, f1, c0, c1, None, None, *ws, n_groups=n_groups, n_samples=n_samples,
+                                              n_heads=n_heads, offset_scale=0.0, coords_final=True, out_channels_last=False)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        q, f0, f1, c0, c1, wq, bq, wk, bk, wv, bv = ctx.saved_tensors
+        nG, nS, nH, strip_bytes = ctx.conf
+        dev = q.device
+        b, c, fh, fw = q.shape
+        g = _lib.f32c(grad_out)
+        need = ctx.needs_input_grad
+        lin_x, lin_y = _lib.linspace_m11(fw, dev), _lib.linspace_m11(fh, dev)
+        g_q = torch.empty_like(q) if need[0] else None
+        g_f0 = torch.zeros_like(f0) if need[1] else None
+        g_f1 = torch.zeros_like(f1) if need[2] else None
+        g_c0 = torch.empty_like(c0) if need[3] else None
+        g_c1 = torch.empty_like(c1) if need[4] else None
+        w_leaf = [t.detach().requires_grad_(need[5 + i]) for i, t in enumerate((wq, bq, wk, bk, wv, bv))]
+        g_w = [torch.zeros_like(t) if need[5 + i] else None for i, t in enumerate(w_leaf)]
+        rows_per = max(1, min(fh, strip_bytes // max(1, b * c * 2 * nS * fw * 4)))
+        c0v, c1v = c0.view(b, nG * nS, 2, fh, fw), c1.view(b, nG * nS, 2, fh, fw)
+        st = _lib.stream_ptr(dev)
+        for r0 in range(0, fh, rows_per):
+            rows = min(rows_per, fh - r0)
+            cs0, cs1 = c0v[:, :, :, r0:r0 + rows].contiguous(), c1v[:, :, :, r0:r0 + rows].contiguous()
+            kv = torch.cat((_sample_rows(f0, cs0, nG, nS, r0, lin_x, lin_y), _sample_rows(f1, cs1, nG, nS, r0, lin_x, lin_y)), dim=2)
+            need_kv = need[1] or need[2] or need[3] or need[4]
+            kv.requires_grad_(need_kv)
+            q_s = q[:, :, r0:r0 + rows].detach().requires_grad_(need[0])
+            inputs = [t for t in [q_s, kv, *w_leaf] if t.requires_grad]
+            if not inputs:
+                break
+            with torch.enable_grad():
+                att = _attn_math(q_s, kv, *w_leaf, n_heads=nH)
+            grads = list(torch.autograd.grad(att, inputs, g[:, :, r0:r0 + rows]))
+            if need[0]:
+                g_q[:, :, r0:r0 + rows] = grads.pop(0)
+            g_kv = grads.pop(0) if need_kv else None
+            for i in range(6):
+                if need[5 + i]:
+                    g_w[i] += grads.pop(0)
+            if need_kv:
+                for (f, cs, g_f, g_c, lo) in ((f0, cs0, g_f0, g_c0, 0), (f1, cs1, g_f1, g_c1, nS)):
+                    if g_f is None and g_c is None:
+                        continue
+                    gk = g_kv[:, :, lo:lo + nS].contiguous()
+                    g_cs = torch.empty_like(cs) if g_c is not None else None
+                    _lib.call("vfi_dsample_rows_bwd_f32", dev, f.data_ptr(), cs.data_ptr(), gk.data_ptr(), lin_x.data_ptr(),
+                              lin_y.data_ptr(), _lib.ptr(g_f), _lib.ptr(g_cs), b, c, fh, fw, nG, nS, r0, rows, 1, st)
+                    if g_c is not None:
+                        g_c.view(b, nG * nS, 2, fh, fw)[:, :, :, r0:r0 + rows] = g_cs
+            del kv, g_kv, grads
+        return (g_q, g_f0, g_f1, g_c0, g_c1, *g_w, None, None, None, None)
+
+
+def fused_attention_train(q, feat0, feat1, coords0, coords1, wq, bq, wk, bk, wv, bv, n_groups: int, n_samples: int, n_heads: int,
+                          strip_bytes: int = 64 << 20):
+    """Differentiable fused sampler + attention: q (b,c,h,w), feat0 / feat1 (b,c,h,w), coords0 / coords1 (b, nG*nS, 2, h, w)
+    final displacements -> (b, c, h, w).  See :class:`_FusedAttnTrainFn`."""
+    return _FusedAttnTrainFn.apply(q, feat0, feat1, coords0, coords1, wq, bq, wk, bk, wv, bv, n_groups, n_samples, n_heads,
+                                   strip_bytes)
+
+
 class Attn(nn.Module):
     def __init__(self, in_c, out_c, n_samples, n_heads):
         super().__init__()
@@ -273,12 +378,20 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
     # -- fused forward ------------------------------------------------------------------------------
     def _forward_autograd(self, feat_t, feat0, feat1, ft0, ft1):
         """Training route (grad enabled): the reference's piecewise composition (modules/deformable_attn.py:103-133) over
-        the differentiable drop-ins -- bwarp and grouped_sample run the CUDA kernels forward and backward."""
+        the differentiable drop-ins -- bwarp runs its CUDA kernels forward and backward, and the sampler + attention run
+        fused forward with a strip-wise recomputing backward (:func:`fused_attention_train`; ``VFI_DATTN_TRAIN=materialize``
+        restores the kv-materialising composition)."""
         mv0 = self._get_movement_feats(feat_t, feat0, ft0)
         mv1 = self._get_movement_feats(feat_t, feat1, ft1)
-        kv = torch.cat((self._get_ref_feats(feat0, self._get_ref_coords(feat_t, ft0, mv0)),
-                        self._get_ref_feats(feat1, self._get_ref_coords(feat_t, ft1, mv1))), dim=2)
-        attended = self.attn(feat_t, kv)
+        c0, c1 = self._get_ref_coords(feat_t, ft0, mv0), self._get_ref_coords(feat_t, ft1, mv1)
+        if fused_supported(self.in_c, self.n_groups, self.n_heads) and os.environ.get("VFI_DATTN_TRAIN", "fused") != "materialize":
+            # fused forward, strip-wise recomputing backward: no (b, c, 2 nS, h*w) tensor is kept for autograd
+            attended = fused_attention_train(feat_t, feat0, feat1, c0, c1, *self.attn._weights(), n_groups=self.n_groups,
+                                             n_samples=self.n_samples, n_heads=self.n_heads,
+                                             strip_bytes=int(os.environ.get("VFI_DATTN_TRAIN_STRIP_MB", "64")) << 20)
+        else:
+            kv = torch.cat((self._get_ref_feats(feat0, c0), self._get_ref_feats(feat1, c1)), dim=2)
+            attended = self.attn(feat_t, kv)
         out = attended + self.mlp(attended)
         if not self.pred_res_flow:
             return out
