@@ -229,6 +229,35 @@ def test_splat_vs_oracle(vfi, mode, shape):
     assert_close(vfi.fwarp(*cu(x, fl, metric), mode), oracle.fwarp(x, fl, metric, mode), TOL_SPLAT, f"fwarp {mode} {shape}")
 
 
+@pytest.mark.parametrize("shape", [(1, 16, 272, 480), (2, 40, 264, 260)])
+def test_splat_large_planes_with_folding_and_far_outliers(vfi, shape, monkeypatch):
+    """The link + gather splat at plane sizes where every list feature is exercised at once: every weight / eps mode
+    against the oracle with folding flows (overflow nodes beyond the 4 kept in registers: the re-walk path), 1 % far
+    outliers, non-finite flows, ragged 32x8 tiles and a channel count that is not a multiple of the chunk; then the
+    accumulate modes through the two-frame splat."""
+    B, C, H, W = shape
+    x = det.normal(f"spt.{shape}", shape)
+    fl = det.flow_field(f"spt.f.{shape}", B, H, W, sigma=5.0, nonfinite_frac=0.001)
+    far = det.uniform(f"spt.far.{shape}", (B, 1, H, W)) < 0.01
+    fl = torch.where(far, (det.uniform(f"spt.big.{shape}", (B, 2, H, W)) * 2 - 1) * W, fl)
+    fl[:, :, : H // 3] *= 3.0                        # strong folding in the upper third: lists longer than the registers hold
+    for mode in ("sum", "avg", "linear", "soft", "soft-zeroeps", "linear-clipeps"):
+        head = mode.split("-")[0]
+        metric = None if head in ("sum", "avg") else (det.normal(f"spt.m.{shape}", (B, 1, H, W)) if head == "soft"
+                                                      else det.uniform(f"spt.m.{shape}", (B, 1, H, W), lo=0.01, hi=1.0))
+        assert_close(vfi.fwarp(*cu(x, fl, metric), mode), oracle.fwarp(x, fl, metric, mode), TOL_SPLAT, f"fwarp {mode} {shape}")
+    monkeypatch.setenv("VFI_SPLAT_ALGO", "gather")
+    tag = f"spt2.{shape}"
+    in2 = det.normal(tag + ".b", shape)
+    f2 = det.flow_field(tag + ".f2", B, H, W, sigma=4.0)
+    t1 = det.uniform(tag + ".t", (B, 1, 1, 1), lo=0.1, hi=0.9)
+    m1, m2 = det.normal(tag + ".m1", (B, 1, H, W), std=2.0), det.normal(tag + ".m2", (B, 1, H, W), std=2.0)
+    ref, ref_mask = oracle.fwarp_using_two_frames(x, fl, t1, in2, f2, 1 - t1, m1, m2)
+    o, m = vfi.fwarp_using_two_frames(*cu(x, fl, t1, in2, f2, 1 - t1, m1, m2))
+    assert_close(o, ref, TOL_SPLAT, f"two-frame, gather route {shape}")
+    assert (m.cpu() != ref_mask).float().mean() < 0.01
+
+
 def test_splat_rejects_cpu_and_bad_modes(vfi):
     x, fl = torch.zeros(1, 1, 4, 4), torch.zeros(1, 2, 4, 4)
     with pytest.raises(Exception):
