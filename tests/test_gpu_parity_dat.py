@@ -423,3 +423,28 @@ def test_frame_edge_interpolate_matches_pad_inference_unpad(vfi, hw):
     assert out_u.dtype == torch.uint8
     q = (ref * 255.0).round()
     assert int((out_u.cpu().float() - q).abs().max()) <= 1, "uint8 frames: at most one code value from the rounded reference"
+
+
+def test_pipelined_inference_matches_direct_calls(vfi):
+    """graph.py:PipelinedInference (uploads / downloads on copy streams around the replayed graph): a stream of different
+    pairs gives, in order, exactly the frames of direct interpolate() calls -- no slot is overwritten early."""
+    import videoframeinterpolation_b200 as v
+    from videoframeinterpolation_b200.workloads import init_dat_weights
+    net = init_dat_weights(v.DATwConstantnCv1(v.default_args(nf=16, enc_res_blocks=1, dec_res_blocks=1))).cuda().eval()
+    H, W, n = 72, 104, 7
+    g = torch.Generator().manual_seed(3)
+    frames = [(torch.rand(1, 3, H, W, generator=g) * 255).round().to(torch.uint8).pin_memory() for _ in range(n + 1)]
+    t = torch.full((1, 1, 1, 1), 0.5, device="cuda")
+    with torch.no_grad():
+        want = [net.interpolate(frames[i].cuda(), frames[i + 1].cuda(), t).cpu() for i in range(n)]
+    pipe = v.PipelinedInference(net, frames[0], frames[1], t, fn=net.interpolate)
+    got = []
+    for i in range(n):
+        pipe.submit(frames[i], frames[i + 1])
+        if pipe.pending() > 1:
+            got.append(pipe.collect().clone())
+    while pipe.pending():
+        got.append(pipe.collect().clone())
+    assert len(got) == n
+    for i in range(n):
+        assert got[i].dtype == torch.uint8 and (got[i].int() - want[i].int()).abs().max() <= 1, i

@@ -11,7 +11,7 @@ from .madat import DeformAttnwMotion, DATwithMotionEstimation
 from .dat import DATwConstantnCv1, DCNInterFeatBuilderwithT, InputPadder, default_args
 from . import dcndat
 from .dcndat import DCNDATv1, dcndat_default_args
-from .graph import GraphedInference
+from .graph import GraphedInference, PipelinedInference
 from .metrics import calculate_psnr, calculate_ssim, frame_metrics
 from .checkpoint import load_reference_checkpoint, save_reference_checkpoint, strip_ddp_prefix
 
