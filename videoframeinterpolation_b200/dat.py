@@ -81,8 +81,15 @@ class DATwConstantnCv1(nn.Module):
             x0, x1, mean_ = self.norm_w_rgb_mean(x0, x1)
         else:       # tile of a larger frame: the mean is the GLOBAL one (models/BaseModel.py:14-17)
             x0, x1 = x0 - mean_, x1 - mean_
-        f0 = self.feature_encoder(x0)
-        f1 = self.feature_encoder(x1)
+        if torch.is_grad_enabled() or x0.shape != x1.shape:
+            f0 = self.feature_encoder(x0)
+            f1 = self.feature_encoder(x1)
+        else:
+            # inference: both frames through the encoder as one batch (the same convolutions on twice the pixels: half
+            # the launches, and the 1/4 .. 1/16-resolution levels fill the machine better); per-frame pyramids are views
+            nb = x0.shape[0]
+            fb = self.feature_encoder(torch.cat((x0, x1), dim=0))
+            f0, f1 = [f[:nb] for f in fb], [f[nb:] for f in fb]
         q4, ft0_4, ft1_4 = self.coarse_query_builder(f0[3], f1[3], t)
         s3 = conv_transpose_up2(self.lv4_to_lv3, torch.cat((q4, ft0_4, ft1_4), dim=1))
         q3, ft0_3, ft1_3 = s3[:, :nf], s3[:, nf:nf + 2], s3[:, nf + 2:nf + 4]
