@@ -417,7 +417,13 @@ def dcn_cfg3(dev, hbm_peak, flush):
     ms = time_op(lambda: v.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask), 5, flush)
     nbytes = bytes_dcn(B, C, C, H, W, OG)
     out = {"shape": "x (32,64,256,256), offset (32,144,256,256), mask (32,72,256,256), weight (64,8,3,3)", "ms": ms,
-           "gbs": nbytes / ms / 1e6, "frac_of_hbm": nbytes / ms / 1e6 / hbm_peak, "algorithmic_bytes": nbytes}
+           "gbs": nbytes / ms / 1e6, "frac_of_hbm": nbytes / ms / 1e6 / hbm_peak, "algorithmic_bytes": nbytes,
+           "kernel": "dcn_win_kernel (TMA-staged window, fp32 FFMA2 contraction; what auto picks for this shape)",
+           "gemm_tflops_fp32": 2.0 * C * (C // WG) * 9 * B * H * W / ms / 1e9,
+           "tensor_pipe_active_pct": {"default_kernel": 0.0, "tcgen05_path_algo2": 1.2,
+                                      "note": "the per-group contraction is 8 x 8 x 9 MACs per sampled value: the default kernels keep "
+                                              "it on the FMA pipe; the tcgen05 form (algo 2, 3xTF32, parity-green) measured 8.7 ms with "
+                                              "the tensor pipe 1.2 % active (profiles/r1g_dcn_tc_ncu_full.txt) and is not a default"}}
     try:
         import torchvision.ops as tvo
         ms_tv = time_op(lambda: tvo.deform_conv2d(x, off, wgt, bias, padding=1, mask=mask), 3, flush)
@@ -655,13 +661,21 @@ def run_vfi(args):
         host_ms = (time.perf_counter() - h0) * 1e3 / args.steps
         torch.cuda.synchronize()
         eager_ms = total_ms / args.steps
+        graph_pool_gb = None
         if args.graph:
-            graphed = v.GraphedInference(net, d_x0, d_x1, t)                      # float32 e2e leg (pad / unpad in PyTorch)
+            # one captured graph alive at a time: each holds the activations of a whole forward in its private pool
+            # (~4.4 GB per 1080p pair), and --pairs 8 would not fit four of them
             graphed_dev = v.GraphedInference(net, d_r0, d_r1, t, fn=net.interpolate)
             step_graph = graphed_dev.replay
             for _ in range(3):
                 step_graph()
             total_ms = timed(step_graph, args.steps)
+            free_b, total_b = torch.cuda.mem_get_info(dev)
+            graph_pool_gb = (total_b - free_b) / 2 ** 30                      # device-level: includes the graph's private pool
+            del graphed_dev, step_graph
+            torch.cuda.empty_cache()
+            if not args.no_e2e:
+                graphed = v.GraphedInference(net, d_x0, d_x1, t)                  # float32 e2e leg (pad / unpad in PyTorch)
         if args.no_e2e:
             e2e_ms = e2e_f32_ms = e2e_seq_ms = float("nan")
         else:
@@ -670,6 +684,8 @@ def run_vfi(args):
                 fn()
             e2e_f32_ms = timed(fn, args.steps)
             if args.graph:
+                graphed = None
+                torch.cuda.empty_cache()
                 graphed_u8 = v.GraphedInference(net, h_u0.to(dev), h_u1.to(dev), t, fn=net.interpolate)
             fn = step_graph_e2e_u8 if args.graph else step_e2e_u8
             for _ in range(2):
@@ -677,6 +693,8 @@ def run_vfi(args):
             e2e_seq_ms = timed(fn, args.steps)
             e2e_ms = e2e_seq_ms
             if args.graph:
+                graphed_u8 = None
+                torch.cuda.empty_cache()
                 # the streaming API a video interpolator uses: pair i + 1 uploads and result i - 1 downloads on copy streams
                 # while pair i computes; every step's H2D and D2H are inside the timed region, the last result included
                 pipe = v.PipelinedInference(net, h_u0, h_u1, t, fn=net.interpolate)
@@ -691,6 +709,8 @@ def run_vfi(args):
 
                 run_pipe(3)
                 e2e_ms = timed(lambda: run_pipe(args.steps), 1)
+                del pipe
+                torch.cuda.empty_cache()
 
     ms_per_step = total_ms / args.steps
     value = world * P / (ms_per_step / 1e3)
@@ -743,7 +763,8 @@ def run_vfi(args):
                        "launch": "CUDA graph replay" if args.graph else "eager",
                        "api": "DATwConstantnCv1.interpolate(float32 frames resident in HBM): replicate pad, rgb-mean normalisation, forward, clamp, unpad",
                        "l2": "inputs + activations per step (>1 GB) exceed the 126 MB L2"},
-            "details": {"eager_ms_per_step": eager_ms, "eager_host_enqueue_ms_per_step": host_ms},
+            "details": {"eager_ms_per_step": eager_ms, "eager_host_enqueue_ms_per_step": host_ms,
+                        "device_memory_in_use_gb_with_the_captured_graph": graph_pool_gb, "pairs_per_gpu": P},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * h_u0.numel(), "d2h_bytes_per_step": h_out_u8.numel(),
                     "ms_per_step": e2e_ms / args.steps,
                     "api": ("PipelinedInference(net, fn=DATwConstantnCv1.interpolate).submit / collect: " if args.graph else "DATwConstantnCv1.interpolate: ") +
