@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define VFI_B200_VERSION 200 /* major*10000 + minor*100 + patch */
+#define VFI_B200_VERSION 201 /* major*10000 + minor*100 + patch */
 
 typedef enum vfi_status {
     VFI_OK = 0,
