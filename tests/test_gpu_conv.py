@@ -234,3 +234,37 @@ def test_conv_transpose_up2_on_tensor_cores(tf32, cfg):
     assert y.shape == ref.shape
     assert y.is_contiguous() if not ocl else y.is_contiguous(memory_format=torch.channels_last)
     assert rel_err(y.double().cpu(), ref) <= 3e-3      # TF32 inputs
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cfg", [dict(B=2, Cin=72, Cout=72, H=30, W=20, res=0), dict(B=2, Cin=72, Cout=72, H=31, W=21, res=1),
+                                 dict(B=1, Cin=72, Cout=64, H=17, W=27, res=0), dict(B=3, Cin=32, Cout=8, H=15, W=9, res=0),
+                                 dict(B=1, Cin=72, Cout=136, H=29, W=18, res=0)])
+def test_conv3x3_tma_store_stays_inside_the_output_view(tf32, cfg):
+    """Round-2 epilogue (output tile in shared memory -> one TMA store per tile; the shared-memory tiles are wider than the
+    channel count, csrc/conv3x3.cu:conv_tile_pitch): the store must drop the padding channels, the rows / columns of ragged
+    edge tiles and the dummy tile of an odd tile count.  The output is a channel slice in the middle of a wider
+    channels-last buffer with guard bands before and after it; every element outside the view must keep its sentinel."""
+    from videoframeinterpolation_b200 import conv as vc
+    B, Cin, Cout, H, W, res = (cfg[k] for k in ("B", "Cin", "Cout", "H", "W", "res"))
+    g = torch.Generator().manual_seed(11)
+    conv = nn.Conv2d(Cin, Cout, 3, 1, 1)
+    with torch.no_grad():
+        conv.weight.copy_(torch.randn(conv.weight.shape, generator=g) * 0.1)
+        conv.bias.copy_(torch.randn(Cout, generator=g))
+    conv = conv.cuda()
+    x = torch.randn(B, Cin, H, W, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    r = torch.randn(B, Cout, H, W, generator=g).cuda().contiguous(memory_format=torch.channels_last) if res else None
+    lead, trail, ctot = 4, 8, Cout + 12
+    guard = 4096
+    SENT = 12345.0
+    flat = torch.full((guard + B * H * W * ctot + guard,), SENT, device="cuda")
+    buf = flat[guard:guard + B * H * W * ctot].view(B, H, W, ctot).permute(0, 3, 1, 2)
+    out = buf[:, lead:lead + Cout]
+    with torch.no_grad():
+        y = vc.conv3x3(conv, x, None, r, out=out)
+    torch.cuda.synchronize()
+    ref = oracle.conv3x3_tf32(x.cpu(), conv.weight.detach().cpu(), conv.bias.detach().cpu(), None, None if r is None else r.cpu(), False)
+    assert rel_err(y.double().cpu(), ref) <= 1e-5
+    assert bool((flat[:guard] == SENT).all()) and bool((flat[-guard:] == SENT).all()), "wrote outside the buffer"
+    assert bool((buf[:, :lead] == SENT).all()) and bool((buf[:, lead + Cout:] == SENT).all()), "wrote outside the channel slice"
