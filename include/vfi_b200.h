@@ -202,7 +202,9 @@ int vfi_nhwc_to_nchw_f32(const float* x, float* out, int B, int C, int H, int W,
  *   wprep    vfi_conv3x3_prep_f32(weight (Cout,Cin,3,3) contiguous) -> vfi_conv3x3_prep_bytes(Cout, Cin) bytes.
  *   out      out_channels_last = 1: NHWC with out_c_total channels per pixel; 0: NCHW (B, out_c_total, H, W);
  *            channels [0, Cout) are written.  residual (mode 1: before the activation, 2: after) has the layout of
- *            out with res_c_total channels.  bias / slope (Cout) may be NULL.
+ *            out with res_c_total channels.  bias / slope (Cout) may be NULL.  residual_mode may carry, in bits 8 and up,
+ *            the number of images Br of the residual when it is shared by groups of the batch (B % Br == 0): output
+ *            image b then adds residual image b % Br (0 = one residual image per output image).
  * vfi_conv3x3_supported: 1 when this (Cin, x_pix_stride, Cout) runs here (weights of a Cout tile must fit in shared
  * memory: Cin <= 72 for a 72-wide tile).
  * upscale = 2 fuses nn.PixelShuffle(2) behind the convolution (modules/generator.py:14-22: upconv1 -> pixel_shuffle ->

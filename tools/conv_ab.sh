@@ -4,7 +4,7 @@
 set -u
 mkdir -p gpurun_out
 for n in "$@"; do
-  unset VFI_B200_LIB VFI_CONV_OSTG VFI_CONV_RSTG VFI_CONV_STAGES
+  unset VFI_B200_LIB VFI_CONV_OSTG VFI_CONV_RSTG VFI_CONV_STAGES VFI_DAT_BATCH_FRAMES VFI_CONV_DBG
   if [ -f "$PWD/variants/libvfi_$n.so" ]; then export VFI_B200_LIB=$PWD/variants/libvfi_$n.so; elif [ "$n" != default ]; then export $n; fi
   echo "=== $n"
   timeout -s KILL 300 python -m pytest tests/test_gpu_conv.py -q -m gpu -x 2>&1 | tail -3

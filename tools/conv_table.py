@@ -33,10 +33,11 @@ rows = []
 for name, (calls, ms) in tm.summary().items():
     if not name.startswith("conv3x3 "):
         continue
-    _, hw, cc, res, up, ps = name.split()
+    _, hw, cc, res, up, ps = name.split()[:6]
     H, W = (int(a) for a in hw.split("x"))
     cin, cout = (int(a) for a in cc.split("->"))
-    fl = 2.0 * 9 * cin * cout * H * W
+    parts = name.split()
+    fl = 2.0 * 9 * cin * cout * H * W * (int(parts[6][1:]) if len(parts) > 6 else 1)      # " B2": a batch of two images
     rows.append((ms / N, calls // N, name, fl * (calls // N) / (ms / N) / 1e9, ms / calls * 1e3))
 rows.sort(reverse=True)
 tot = sum(r[0] for r in rows)

@@ -155,7 +155,8 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tenso
     """``act(residual + conv(x) + bias)`` in one kernel; x must satisfy :func:`eligible`.  ``upscale=2`` returns
     ``act(pixel_shuffle(conv(x) + bias, 2))`` (prelu_weight then has Cout/4 entries).  ``in_slice=(lo, hi, pad)``: x
     holds input channels [lo, hi) of conv followed by ``pad`` zero-weighted channels (one term of a convolution split
-    over its input channels; add the terms through ``residual``).  ``out``: a (B, Cout, H, W) channels-last view (e.g.
+    over its input channels; add the terms through ``residual``).  ``residual`` may have fewer images than x (B % Br == 0):
+    image b adds residual image b % Br (a term shared by both frames of a pair batch).  ``out``: a (B, Cout, H, W) channels-last view (e.g.
     a channel slice of a wider buffer) to write into.  ``roll``: output channel j is channel (j + roll) % Cout of
     ``conv`` (bias and the slopes of ``prelu`` are rolled with it; no residual)."""
     dev = _lib.require_cuda(x, residual)
@@ -189,6 +190,9 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tenso
         else:
             res = residual.contiguous()
         mode = 2 if residual_after_act else 1
+        if residual.shape[0] != B:      # one residual shared by groups of the batch: image b adds residual image b % Br
+            assert B % residual.shape[0] == 0 and tuple(residual.shape[1:]) == (Cout, H, W), "residual batch must divide B"
+            mode |= residual.shape[0] << 8
     if prelu is not None:
         prelu_weight = prelu.weight
     slope = None
@@ -204,7 +208,7 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor, prelu_weight: Optional[torch.Tenso
     _flops[0] += 2 * 9 * (Cin if in_slice is None else in_slice[1] - in_slice[0]) * Cout * B * H * W
     tag = None
     if _lib._timer is not None and getattr(_lib._timer, "detailed", False):     # per-shape rows for tools/conv_table.py
-        tag = f"conv3x3 {H}x{W} {Cin}->{Cout} res{mode} up{upscale} ps{ps}"
+        tag = f"conv3x3 {H}x{W} {Cin}->{Cout} res{mode & 3} up{upscale} ps{ps}" + (f" B{B}" if B > 1 else "")
     _lib.call("vfi_conv3x3_f32", dev, x.data_ptr(), wp.data_ptr(), _lib.ptr(bias), _lib.ptr(slope), _lib.ptr(res), out.data_ptr(),
               B, H, W, Cin, ps, Cout, 1 if out_channels_last else 0, out_c, res_c, mode, upscale, _lib.stream_ptr(dev), tag=tag)
     return out

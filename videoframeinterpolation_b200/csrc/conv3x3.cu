@@ -82,6 +82,7 @@ struct ConvArgs {
     float* out;
     int B, H, W, nstage_tile, nchunk, cn;   // nstage_tile = stages (16 channels) per tile, nchunk = 8-channel k-steps per tile
     int res_mode;         // 0 none, 1 add before the activation, 2 add after it
+    int res_B;            // images in the residual: output image b adds residual image b % res_B (B unless broadcast)
     int vec;              // NHWC out/res: 1 = 16-byte aligned pixel rows (float4), 2 = 32-byte aligned (256-bit accesses)
     int64_t out_sb, out_sy, out_sx, out_sc;   // element strides of out
     int64_t res_sb, res_sy, res_sx, res_sc;
@@ -256,7 +257,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                 mbar_wait(&rempty[i & 1], ((i >> 1) & 1) ^ 1);
                 if (elect_one()) {
                     mbar_arrive_expect_tx(&rfull[i & 1], (uint32_t)rfloats * 4);
-                    tma_load_4d(rbuf + (i & 1) * rfloats, &rmap, &rfull[i & 1], 0, ty * kCvTH, tx * kCvTW, b);
+                    tma_load_4d(rbuf + (i & 1) * rfloats, &rmap, &rfull[i & 1], 0, ty * kCvTH, tx * kCvTW, b % a.res_B);
                 }
                 __syncwarp();
             }
@@ -350,7 +351,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
                 const int b = tile / tiles_per_img, r = tile - b * tiles_per_img;
                 const int ty = r / a.tiles_x, tx = r - ty * a.tiles_x;
                 mbar_arrive_expect_tx(&rfull[slot], (uint32_t)rfloats * 4);     // (outside the tensor: zeros, bytes still count)
-                tma_load_4d(rbuf + slot * rfloats, &rmap, &rfull[slot], 0, ty * kCvTH, tx * kCvTW, b);
+                tma_load_4d(rbuf + slot * rfloats, &rmap, &rfull[slot], 0, ty * kCvTH, tx * kCvTW, b % a.res_B);
             };
             if (RSTG && lane == 0) {
                 if (unit0 < n_units) fetch_residual(unit0, 0);
@@ -405,7 +406,7 @@ __global__ void __launch_bounds__(kCvThreads, 1) conv3x3_tc_kernel(const ConvArg
             const int y = ty * kCvTH + ly - 1, x = tx * kCvTW + lx;
             const bool valid = ly >= 1 && ly <= kCvTH && y < a.H && x < a.W && tile < a.n_tiles && !(a.dbg & 2);
             float* o = a.out + b * a.out_sb + y * a.out_sy + x * a.out_sx;
-            const float* rp = a.res ? a.res + b * a.res_sb + y * a.res_sy + x * a.res_sx : nullptr;
+            const float* rp = a.res ? a.res + (b % a.res_B) * a.res_sb + y * a.res_sy + x * a.res_sx : nullptr;
             // kCvEpiWarps / 4 warps share each TMEM lane quadrant and take every (kCvEpiWarps / 4)-th 8-channel chunk
             auto emit = [&](const float (&p0)[8], const float (&p1)[8], const float (&p2)[8], const int c0) {
                 float t[8];
@@ -709,8 +710,13 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
     VFI_REQUIRE(vfi_conv3x3_supported(Cin, x_pix_stride, Cout, upscale),
                 "vfi_conv3x3_f32: unsupported Cin %d / pixel stride %d / Cout %d / upscale %d", Cin, x_pix_stride, Cout, upscale);
     VFI_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "vfi_conv3x3_f32: x must be 16-byte aligned");
+    // bits 8.. of residual_mode: number of images in the residual when it is broadcast over the batch (0 = B)
+    const int res_images = residual_mode >> 8;
+    residual_mode &= 0xFF;
     VFI_REQUIRE(residual_mode >= 0 && residual_mode <= 2 && (residual_mode == 0 || residual), "vfi_conv3x3_f32: residual_mode %d",
                 residual_mode);
+    VFI_REQUIRE(res_images >= 0 && (res_images == 0 || (residual_mode != 0 && B % res_images == 0)),
+                "vfi_conv3x3_f32: %d residual images do not divide the batch %d", res_images, B);
     VFI_REQUIRE(upscale == 1 || residual_mode == 0, "vfi_conv3x3_f32: a residual cannot be combined with the fused PixelShuffle");
     const int up = upscale, up2 = up * up, Cs = Cout / up2;      // Cs = channels after the shuffle
     VFI_REQUIRE(out_c_total >= Cs && (residual_mode == 0 || res_c_total >= Cout), "vfi_conv3x3_f32: channel totals");
@@ -735,6 +741,7 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
     a.nstage_tile = t.nstage_tile;
     a.nchunk = t.nchunkP;
     a.res_mode = residual_mode;
+    a.res_B = res_images ? res_images : B;
     a.bias_stride = up2;
     a.tiles_x = (W + kCvTW - 1) / kCvTW; a.tiles_y = (H + kCvTH - 1) / kCvTH;
     a.n_tiles = B * a.tiles_x * a.tiles_y;
@@ -785,7 +792,7 @@ extern "C" int vfi_conv3x3_f32(const float* x, const float* wprep, const float* 
             CUtensorMap rmap = xmap, omap = xmap;      // placeholders when the direct paths run
             if (a.staged) {
                 // (channel, y, x, image) view of this Cout tile of the residual; box = one output tile [8 x][14 y][cn]
-                const uint64_t dims[4] = {(uint64_t)a.cn, (uint64_t)H, (uint64_t)W, (uint64_t)B};
+                const uint64_t dims[4] = {(uint64_t)a.cn, (uint64_t)H, (uint64_t)W, (uint64_t)a.res_B};
                 const uint32_t box[4] = {(uint32_t)conv_tile_pitch(a.cn), (uint32_t)kCvTH, (uint32_t)kCvTW, 1};
                 const uint64_t sr[3] = {(uint64_t)a.res_sy * 4, (uint64_t)a.res_sx * 4, (uint64_t)a.res_sb * 4};
                 const int rc2 = make_tmap_f32_nd(&rmap, a.res, 4, dims, sr, box, 0);

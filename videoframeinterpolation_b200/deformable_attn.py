@@ -309,7 +309,14 @@ class Attn(nn.Module):
 
 
 def movement_feats_pair(me, feat_t, feat0, feat1, ft0, ft1):
-    """Both movement features with the first two convs split over their input channels (a convolution is linear
+    """(movement features of frame 0, of frame 1): views of :func:`movement_feats_batched`'s result."""
+    mv = movement_feats_batched(me, feat_t, feat0, feat1, ft0, ft1)
+    b = feat_t.shape[0]
+    return mv[:b], mv[b:]
+
+
+def movement_feats_batched(me, feat_t, feat0, feat1, ft0, ft1):
+    """Both movement features, as ONE tensor of 2b images, with the first two convs split over their input channels (a convolution is linear
     in them), all passes on the tensor-core kernel:
         conv0(cat(feat_t, warped, flow)) = conv0_a(feat_t) + conv0_b(cat(warped, flow))
     The feat_t term is shared by the two frames, the concat (and cuDNN's channel padding of its 146 channels)
@@ -318,17 +325,30 @@ def movement_feats_pair(me, feat_t, feat0, feat1, ft0, ft1):
     C = feat_t.shape[1]
     b, _, fh, fw = feat_t.shape
     shared = _conv.conv3x3(c0, feat_t, in_slice=(0, C, 0))                       # + bias, no activation
-    outs = []
-    for feat_x, ftx in ((feat0, ft0), (feat1, ft1)):
-        wf = torch.empty((b, fh, fw, C + 4), dtype=torch.float32, device=feat_t.device).permute(0, 3, 1, 2)
-        _bwarp_forward(feat_x, ftx, out=wf[:, :C])
-        wf[:, C:C + 2] = ftx
-        wf[:, C + 2:] = 0.0
-        y = _conv.conv3x3(c0, wf, p0.weight, residual=shared, use_bias=False, in_slice=(C, 2 * C + 2, 2))
-        r = _conv.conv3x3(c1, y[:, :C], in_slice=(0, C, 0))
-        z = _conv.conv3x3(c1, y[:, C:], p1.weight, residual=r, use_bias=False, in_slice=(C, 2 * C, 0))
-        outs.append(me[2](z))
-    return outs
+    if os.environ.get("VFI_DAT_BATCH_FRAMES", "1") == "0":                       # A/B switch: one pass per frame
+        outs = []
+        for feat_x, ftx in ((feat0, ft0), (feat1, ft1)):
+            wf = torch.empty((b, fh, fw, C + 4), dtype=torch.float32, device=feat_t.device).permute(0, 3, 1, 2)
+            _bwarp_forward(feat_x, ftx, out=wf[:, :C])
+            wf[:, C:C + 2] = ftx
+            wf[:, C + 2:] = 0.0
+            y = _conv.conv3x3(c0, wf, p0.weight, residual=shared, use_bias=False, in_slice=(C, 2 * C + 2, 2))
+            r = _conv.conv3x3(c1, y[:, :C], in_slice=(0, C, 0))
+            z = _conv.conv3x3(c1, y[:, C:], p1.weight, residual=r, use_bias=False, in_slice=(C, 2 * C, 0))
+            outs.append(me[2](z))
+        return torch.cat(outs, dim=0)
+    # both frames as one batch of 2b images (frame 0 first): half the launches, and the 1/4 / 1/8-resolution levels fill
+    # the machine better; the shared term is broadcast by the conv kernel (residual image = b % batch)
+    wf = torch.empty((2 * b, fh, fw, C + 4), dtype=torch.float32, device=feat_t.device).permute(0, 3, 1, 2)
+    _bwarp_forward(feat0, ft0, out=wf[:b, :C])
+    _bwarp_forward(feat1, ft1, out=wf[b:, :C])
+    wf[:b, C:C + 2] = ft0
+    wf[b:, C:C + 2] = ft1
+    wf[:, C + 2:] = 0.0
+    y = _conv.conv3x3(c0, wf, p0.weight, residual=shared, use_bias=False, in_slice=(C, 2 * C + 2, 2))
+    r = _conv.conv3x3(c1, y[:, :C], in_slice=(0, C, 0))
+    z = _conv.conv3x3(c1, y[:, C:], p1.weight, residual=r, use_bias=False, in_slice=(C, 2 * C, 0))
+    return me[2](z)                                                              # (2b, C, fh, fw): [:b] frame 0, [b:] frame 1
 
 
 def movement_split_ok(me, feat_t, feat0):
@@ -412,15 +432,23 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
         if torch.is_grad_enabled():
             with torch.no_grad():
                 return self.forward(feat_t, feat0, feat1, ft0, ft1)
+        nb = feat_t.shape[0]
+        mvb = None                      # both frames' movement features as one batch of 2 nb images (frame 0 first)
         if self._split_ok(feat_t, feat0):
-            mv0, mv1 = self._movement_feats_pair(feat_t, feat0, feat1, ft0, ft1)
+            mvb = movement_feats_batched(self.movement_extractor, feat_t, feat0, feat1, ft0, ft1)
+            mv0, mv1 = mvb[:nb], mvb[nb:]
+            if os.environ.get("VFI_DAT_BATCH_FRAMES", "1") == "0":       # A/B switch: per-frame launches after the extractor
+                mvb = None
         else:
             mv0 = self._get_movement_feats(feat_t, feat0, ft0)
             mv1 = self._get_movement_feats(feat_t, feat1, ft1)
         if fused_supported(self.in_c, self.n_groups, self.n_heads):
             # bias-free conv: the fused kernel adds conv_res_offset.bias itself (same fp32 order: conv + bias, then tanh)
             co = self.conv_res_offset
-            if _conv.eligible(co, mv0) and _conv.eligible(co, mv1):
+            if mvb is not None and _conv.eligible(co, mvb):
+                raw = _conv.conv3x3(co, mvb, use_bias=False)                    # one pass per Cout tile for both frames
+                raw0, raw1 = raw[:nb], raw[nb:]
+            elif _conv.eligible(co, mv0) and _conv.eligible(co, mv1):
                 raw0, raw1 = _conv.conv3x3(co, mv0, use_bias=False), _conv.conv3x3(co, mv1, use_bias=False)
             else:
                 raw0 = F.conv2d(mv0, co.weight, None, co.stride, co.padding)
@@ -439,6 +467,9 @@ class CrossDeformableAttentionBlockwFlow(nn.Module):
         out = self.mlp.forward_residual(attended)
         if not self.pred_res_flow:
             return out
+        if mvb is not None:
+            rf = _conv.conv_transpose_up2(self.conv_res_flow, mvb, out_channels_last=False)
+            return out, flow_up2_add(rf[:nb], ft0), flow_up2_add(rf[nb:], ft1)
         up_ft0 = flow_up2_add(_conv.conv_transpose_up2(self.conv_res_flow, mv0, out_channels_last=False), ft0)
         up_ft1 = flow_up2_add(_conv.conv_transpose_up2(self.conv_res_flow, mv1, out_channels_last=False), ft1)
         return out, up_ft0, up_ft1
