@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define VFI_B200_VERSION 201 /* major*10000 + minor*100 + patch */
+#define VFI_B200_VERSION 202 /* major*10000 + minor*100 + patch */
 
 typedef enum vfi_status {
     VFI_OK = 0,
@@ -75,6 +75,14 @@ int vfi_bwarp_f32(const float* img, const float* flow, const float* lin_x, const
                   int B, int C, int H, int W,
                   const int64_t img_strides[4], const int64_t flow_strides[4], const int64_t out_strides[4],
                   const int* frame_ext, void* stream);
+
+/* a1 + the channel concat of modules/deformable_attn.py:69 (`torch.cat((feat_t, bwarp(feat_x, ftx), ftx), dim=1)`, the input
+ * of the movement extractor): channels-last only; writes the C warped channels of every pixel AND (flow_x, flow_y, 0, 0)
+ * into channels [C, C + 4) of the same output pixel (out_strides[3] >= C + 4), i.e. warp, concat and the zero padding of
+ * the 4-aligned NHWC layout in one pass.  VFI_ERR_UNSUPPORTED for other layouts (use vfi_bwarp_f32 + copies). */
+int vfi_bwarp_flowcat_f32(const float* img, const float* flow, const float* lin_x, const float* lin_y, float* out,
+                          int B, int C, int H, int W, const int64_t img_strides[4], const int64_t flow_strides[4],
+                          const int64_t out_strides[4], const int* frame_ext, void* stream);
 
 /* ---- a2-a5: forward splatting -- modules/softsplat.py:237-360, modules/warp.py:18-114 -------------
  * One call = pre-scale (weight mode) + summation splat of `in` (B,C,H,W) and of the weight channel.

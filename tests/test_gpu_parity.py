@@ -306,3 +306,21 @@ def test_conv_epilogue_bit_identical_to_torch_ops(vfi, cl, shape, monkeypatch):
         assert torch.equal(conv_bias_act(conv, x, prelu, residual=x), prelu(x + (y + b)))
         assert torch.equal(conv_bias_act(conv, x, prelu, residual=x, residual_after_act=True), x + prelu(y + b))
         assert torch.equal(conv_bias_act(conv, x), y + b)
+
+
+@pytest.mark.parametrize("shape", [(2, 72, 37, 52), (1, 8, 19, 23)])
+def test_bwarp_flowcat_equals_bwarp_plus_concat(vfi, shape):
+    """vfi_bwarp_flowcat_f32 (warp + `torch.cat((.., bwarp(feat_x, ftx), ftx))` of modules/deformable_attn.py:69 + the zero
+    padding of the 4-aligned NHWC layout in one pass): bit-identical to vfi_bwarp_f32 followed by the copies, nothing
+    written past channel C + 4."""
+    from videoframeinterpolation_b200.warp import _bwarp_forward
+    B, C, H, W = shape
+    img = det.normal(f"bfc.{shape}", shape).cuda().contiguous(memory_format=torch.channels_last)
+    fl = det.flow_field(f"bfc.f.{shape}", B, H, W, sigma=4.0).cuda()
+    buf = torch.full((B, H, W, C + 8), 777.0, device="cuda").permute(0, 3, 1, 2)
+    _bwarp_forward(img, fl, out=buf[:, :C], flowcat=True)
+    ref = _bwarp_forward(img, fl)
+    assert torch.equal(buf[:, :C], ref)
+    assert torch.equal(buf[:, C:C + 2], fl) and bool((buf[:, C + 2:C + 4] == 0).all()) and bool((buf[:, C + 4:] == 777.0).all())
+    with pytest.raises(Exception):
+        _bwarp_forward(img.contiguous(), fl, out=torch.empty(B, C, H, W, device="cuda"), flowcat=True)     # planar: unsupported

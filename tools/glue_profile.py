@@ -17,7 +17,7 @@ with torch.no_grad():
     for _ in range(3):
         net.interpolate(x0, x1, t)
     torch.cuda.synchronize()
-    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True) as prof:
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True, record_shapes=True) as prof:
         net.interpolate(x0, x1, t)
         torch.cuda.synchronize()
 evs = prof.events()
@@ -43,3 +43,11 @@ tot = sum(r[1] for r in rows.values())
 print(f"non-vfi kernels of one forward: {sum(r[0] for r in rows.values())} launches, {tot / 1e3:.3f} ms")
 for (where, op, kn), (n, us) in sorted(rows.items(), key=lambda kv: -kv[1][1])[:70]:
     print(f"{us:8.1f} us {n:3d}x  {op:32s} {kn:60s} {where}")
+
+print("largest elementwise glue launches (op, input shapes, us):")
+glue = []
+for e in evs:
+    if e.device_type == torch.autograd.DeviceType.CPU and e.kernels and e.name in ("aten::copy_", "aten::add_", "aten::cat", "aten::fill_", "aten::add", "aten::gelu"):
+        glue.append((sum(k.duration for k in e.kernels), e.name, str(e.input_shapes)[:110]))
+for us, nm, shp in sorted(glue, reverse=True)[:28]:
+    print(f"{us:8.1f} us  {nm:12s} {shp}")

@@ -26,6 +26,7 @@ SIGNATURES = {
     "vfi_last_error_string": (ctypes.c_char_p, []),
     "vfi_device_supported": (c_int, []),
     "vfi_bwarp_f32": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p] * 3 + [c_void_p, c_void_p]),
+    "vfi_bwarp_flowcat_f32": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p] * 3 + [c_void_p, c_void_p]),
     "vfi_splat_f32": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "vfi_splat_workspace_bytes": (c_size_t, [c_int] * 4),
     "vfi_splat_normalize_f32": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_int, c_float, c_float, c_void_p]),

@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(256) bwarp_planar_kernel(const float* __restri
 __global__ void __launch_bounds__(256) bwarp_cl_kernel(const float* __restrict__ img, const float* __restrict__ flow,
                                                        const float* __restrict__ lin_x, const float* __restrict__ lin_y,
                                                        float* __restrict__ out, int B, int C, int H, int W, Str4 si,
-                                                       Str4 sf, Str4 so, FrameExt fe) {
+                                                       Str4 sf, Str4 so, FrameExt fe, int flowcat) {
     const int cv = C >> 2;
     const int64_t total = (int64_t)B * H * W * cv;
     for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
@@ -141,6 +141,8 @@ __global__ void __launch_bounds__(256) bwarp_cl_kernel(const float* __restrict__
         r.z = a.z * g.w_nw + bq.z * g.w_ne + c.z * g.w_sw + d.z * g.w_se;
         r.w = a.w * g.w_nw + bq.w * g.w_ne + c.w * g.w_sw + d.w * g.w_se;
         st_stream4(out + b * so.n + y * so.h + x * so.w + c4, r);
+        // flowcat: the thread of the pixel's last channel quad also writes (flow_x, flow_y, 0, 0) behind the C warped channels
+        if (flowcat && c4 == C - 4) st_stream4(out + b * so.n + y * so.h + x * so.w + C, make_float4(__ldg(fp), __ldg(fp + sf.c), 0.0f, 0.0f));
     }
 }
 
@@ -416,7 +418,7 @@ extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* l
     if (channels_last) {
         const int64_t total = (int64_t)B * H * W * (C / 4);
         const int blocks = (int)min64(ceil_div(total, 256), (int64_t)kNumSMs * 32);
-        bwarp_cl_kernel<<<blocks, 256, 0, st>>>(img, flow, lin_x, lin_y, out, B, C, H, W, si, sf, so, fe);
+        bwarp_cl_kernel<<<blocks, 256, 0, st>>>(img, flow, lin_x, lin_y, out, B, C, H, W, si, sf, so, fe, 0);
         VFI_CHECK_LAUNCH("bwarp_cl_kernel");
         return VFI_OK;
     }
@@ -453,5 +455,28 @@ extern "C" int vfi_bwarp_f32(const float* img, const float* flow, const float* l
     dim3 grid((unsigned)ceil_div(W, 32), (unsigned)ceil_div(H, 8), (unsigned)(B * n_chunks));
     bwarp_planar_kernel<<<grid, dim3(32, 8), 0, st>>>(img, flow, lin_x, lin_y, out, C, H, W, c_chunk, n_chunks, si, sf, so, fe);
     VFI_CHECK_LAUNCH("bwarp_planar_kernel");
+    return VFI_OK;
+}
+
+extern "C" int vfi_bwarp_flowcat_f32(const float* img, const float* flow, const float* lin_x, const float* lin_y, float* out,
+                                     int B, int C, int H, int W, const int64_t img_strides[4], const int64_t flow_strides[4],
+                                     const int64_t out_strides[4], const int* frame_ext, void* stream) {
+    using namespace vfi;
+    if (B == 0) return VFI_OK;
+    VFI_REQUIRE(img && flow && lin_x && lin_y && out && img_strides && flow_strides && out_strides, "vfi_bwarp_flowcat_f32: null pointer");
+    VFI_REQUIRE(B >= 0 && C >= 4 && C % 4 == 0 && H >= 1 && W >= 1, "vfi_bwarp_flowcat_f32: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    const Str4 si{img_strides[0], img_strides[1], img_strides[2], img_strides[3]};
+    const Str4 sf{flow_strides[0], flow_strides[1], flow_strides[2], flow_strides[3]};
+    const Str4 so{out_strides[0], out_strides[1], out_strides[2], out_strides[3]};
+    const FrameExt fe = frame_ext_of(frame_ext, H, W);
+    VFI_REQUIRE(frame_ext_ok(fe, H, W), "vfi_bwarp_flowcat_f32: the crop does not lie inside the frame");
+    auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    const bool channels_last = si.c == 1 && so.c == 1 && aligned16(img) && aligned16(out) && si.w % 4 == 0 && si.h % 4 == 0 &&
+                               si.n % 4 == 0 && so.w % 4 == 0 && so.h % 4 == 0 && so.n % 4 == 0 && so.w >= C + 4;
+    if (!channels_last) VFI_UNSUPPORTED("vfi_bwarp_flowcat_f32: channels-last img / out with 16-byte aligned pixels and >= C + 4 output channels per pixel");
+    const int64_t total = (int64_t)B * H * W * (C / 4);
+    const int blocks = (int)min64(ceil_div(total, 256), (int64_t)kNumSMs * 32);
+    bwarp_cl_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(img, flow, lin_x, lin_y, out, B, C, H, W, si, sf, so, fe, 1);
+    VFI_CHECK_LAUNCH("bwarp_cl_kernel");
     return VFI_OK;
 }

@@ -28,6 +28,16 @@ def default_args(**over):
     return SimpleNamespace(**d)
 
 
+def _batch_pair(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """(2B, ...) batch of a then b: a view when b already follows a in memory with the same strides (the two halves of one
+    allocation, as ``interpolate`` makes them), else a copy."""
+    if (a.shape == b.shape and a.stride() == b.stride() and a.dtype == b.dtype and a.dim() == 4 and a.shape[0] >= 1
+            and a.untyped_storage().data_ptr() == b.untyped_storage().data_ptr()
+            and b.storage_offset() == a.storage_offset() + a.shape[0] * a.stride(0)):
+        return a.as_strided((2 * a.shape[0],) + tuple(a.shape[1:]), a.stride(), a.storage_offset())
+    return torch.cat((a, b), dim=0)
+
+
 class DCNInterFeatBuilderwithT(nn.Module):
     """Coarsest-level query builder: two DCN blocks blended, t / 1-t planes appended (modules/query_builder.py:7-36)."""
 
@@ -88,7 +98,7 @@ class DATwConstantnCv1(nn.Module):
             # inference: both frames through the encoder as one batch (the same convolutions on twice the pixels: half
             # the launches, and the 1/4 .. 1/16-resolution levels fill the machine better); per-frame pyramids are views
             nb = x0.shape[0]
-            fb = self.feature_encoder(torch.cat((x0, x1), dim=0))
+            fb = self.feature_encoder(_batch_pair(x0, x1))
             f0, f1 = [f[:nb] for f in fb], [f[nb:] for f in fb]
         q4, ft0_4, ft1_4 = self.coarse_query_builder(f0[3], f1[3], t)
         s3 = conv_transpose_up2(self.lv4_to_lv3, torch.cat((q4, ft0_4, ft1_4), dim=1))
@@ -132,8 +142,8 @@ class DATwConstantnCv1(nn.Module):
         B, _, H, W = img0.shape
         pad = InputPadder((H, W), divisor)._pad            # [left, right, top, bottom]
         Hp, Wp = H + pad[2] + pad[3], W + pad[0] + pad[1]
-        x0 = torch.empty((B, Hp, Wp, 4), dtype=torch.float32, device=dev)
-        x1 = torch.empty_like(x0)
+        x01 = torch.empty((2 * B, Hp, Wp, 4), dtype=torch.float32, device=dev)     # one buffer: the encoder takes both frames as a batch
+        x0, x1 = x01[:B], x01[B:]
         mean = torch.empty((B,), dtype=torch.float32, device=dev)
         ws = torch.empty((B,), dtype=torch.float64, device=dev)
         st = _lib.stream_ptr(dev)

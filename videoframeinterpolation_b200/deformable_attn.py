@@ -340,11 +340,15 @@ def movement_feats_batched(me, feat_t, feat0, feat1, ft0, ft1):
     # both frames as one batch of 2b images (frame 0 first): half the launches, and the 1/4 / 1/8-resolution levels fill
     # the machine better; the shared term is broadcast by the conv kernel (residual image = b % batch)
     wf = torch.empty((2 * b, fh, fw, C + 4), dtype=torch.float32, device=feat_t.device).permute(0, 3, 1, 2)
-    _bwarp_forward(feat0, ft0, out=wf[:b, :C])
-    _bwarp_forward(feat1, ft1, out=wf[b:, :C])
-    wf[:b, C:C + 2] = ft0
-    wf[b:, C:C + 2] = ft1
-    wf[:, C + 2:] = 0.0
+    if feat0.stride(1) == 1 and feat1.stride(1) == 1 and C % 4 == 0 and feat0.data_ptr() % 16 == 0 and feat1.data_ptr() % 16 == 0:
+        _bwarp_forward(feat0, ft0, out=wf[:b, :C], flowcat=True)                 # warp + flow channels + zero pad in one pass
+        _bwarp_forward(feat1, ft1, out=wf[b:, :C], flowcat=True)
+    else:
+        _bwarp_forward(feat0, ft0, out=wf[:b, :C])
+        _bwarp_forward(feat1, ft1, out=wf[b:, :C])
+        wf[:b, C:C + 2] = ft0
+        wf[b:, C:C + 2] = ft1
+        wf[:, C + 2:] = 0.0
     y = _conv.conv3x3(c0, wf, p0.weight, residual=shared, use_bias=False, in_slice=(C, 2 * C + 2, 2))
     r = _conv.conv3x3(c1, y[:, :C], in_slice=(0, C, 0))
     z = _conv.conv3x3(c1, y[:, C:], p1.weight, residual=r, use_bias=False, in_slice=(C, 2 * C, 0))

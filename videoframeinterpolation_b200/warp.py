@@ -53,8 +53,10 @@ def bwarp(img: torch.Tensor, flow: torch.Tensor) -> torch.Tensor:
     return _bwarp_forward(img, flow)
 
 
-def _bwarp_forward(img: torch.Tensor, flow: torch.Tensor, out: torch.Tensor = None) -> torch.Tensor:
-    """``out``: optional (B,C,H,W) fp32 view to write into (any strides, e.g. a channel slice of a wider buffer)."""
+def _bwarp_forward(img: torch.Tensor, flow: torch.Tensor, out: torch.Tensor = None, flowcat: bool = False) -> torch.Tensor:
+    """``out``: optional (B,C,H,W) fp32 view to write into (any strides, e.g. a channel slice of a wider buffer).
+    ``flowcat``: out is the first C channels of a channels-last buffer with >= C + 4 channels per pixel; the kernel also
+    writes (flow_x, flow_y, 0, 0) into channels [C, C + 4) (vfi_bwarp_flowcat_f32)."""
     dev = _lib.require_cuda(img, flow)
     B, _, H, W = flow.shape
     assert img.shape[0] == B and tuple(img.shape[2:]) == (H, W), "img / flow shape mismatch"
@@ -67,8 +69,9 @@ def _bwarp_forward(img: torch.Tensor, flow: torch.Tensor, out: torch.Tensor = No
     else:
         out = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
     ext, lin_x, lin_y = _lib.frame_ext(H, W, dev)
-    _lib.call("vfi_bwarp_f32", dev, img.data_ptr(), flow.data_ptr(), lin_x.data_ptr(), lin_y.data_ptr(), out.data_ptr(), B, C, H, W,
-              _lib.strides4(img), _lib.strides4(flow), _lib.strides4(out), ext, _lib.stream_ptr(dev))
+    _lib.call("vfi_bwarp_flowcat_f32" if flowcat else "vfi_bwarp_f32", dev, img.data_ptr(), flow.data_ptr(), lin_x.data_ptr(),
+              lin_y.data_ptr(), out.data_ptr(), B, C, H, W, _lib.strides4(img), _lib.strides4(flow), _lib.strides4(out), ext,
+              _lib.stream_ptr(dev))
     return out
 
 
