@@ -135,9 +135,15 @@ class DeformableConv2d(nn.Module):
         self.regular_conv = nn.Conv2d(in_channels // groups, out_channels, kernel_size, stride=1, padding=padding)
 
     def forward(self, x, movement_feat):
-        flow = self.offset_flow_conv(movement_feat)                               # B, 2, h, w
-        warped = bwarp(x, flow)
-        head = self.conv_offset_mask(torch.cat((warped, movement_feat, flow), dim=1))
+        if torch.is_grad_enabled():
+            flow = self.offset_flow_conv(movement_feat)                           # B, 2, h, w
+            warped = bwarp(x, flow)
+            head = self.conv_offset_mask(torch.cat((warped, movement_feat, flow), dim=1))
+        else:       # inference: conv + one fused bias / PReLU epilogue per layer (tensor-core kernel where eligible)
+            from .blocks import conv_bias_act, run_conv_chain
+            flow = conv_bias_act(self.offset_flow_conv, movement_feat)
+            warped = bwarp(x, flow)
+            head = run_conv_chain(self.conv_offset_mask, torch.cat((warped, movement_feat, flow), dim=1))
         n_off = head.shape[1] // 3 * 2
         res_offset = 2.0 * torch.tanh(head[:, :n_off])
         # base offset: the flow flipped to (dy, dx) and tiled over (group, tap) -- modules/dcnv2.py:57
